@@ -1,0 +1,213 @@
+"""Shared test/bench helpers: ctypes bindings of the CPU oracle (oracle/liboracle.so), of the
+compiled reference (oracle/_ref/libpolar_ref.so, optional) and seeded AWGN/BPSK workloads.
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs.  The product package never imports this module.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+KIND_ENC, KIND_FASTSSC_I8, KIND_FASTSSC_F32, KIND_SCL_I8, KIND_SCL_F32 = range(5)
+NODE_NAMES = ["F", "G", "C", "G_R1", "G_0R", "R0", "R1", "REP", "REP2", "SPC", "ZERO_SPC", "ZERO_ONE"]
+
+_c = ctypes
+_vp, _i, _l, _d = _c.c_void_p, _c.c_int, _c.c_long, _c.c_double
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+def build_oracle():
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "all"])
+
+
+_oracle = None
+_ref = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        p = os.path.join(ORACLE_DIR, "liboracle.so")
+        if not os.path.exists(p):
+            subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "liboracle.so"])
+        lib = _c.CDLL(p)
+        lib.oracle_crc_generate.argtypes = [_i, _vp, _i]
+        lib.oracle_crc_check.argtypes = [_i, _vp, _i]
+        lib.oracle_quantize.argtypes = [_vp, _vp, _i]
+        lib.oracle_f_i8.argtypes = [_c.c_int8, _c.c_int8]
+        lib.oracle_f_i8.restype = _c.c_int8
+        lib.oracle_g_i8.argtypes = [_c.c_int8, _c.c_int8, _c.c_int8]
+        lib.oracle_g_i8.restype = _c.c_int8
+        lib.oracle_rep_sum_i8.argtypes = [_vp, _i]
+        lib.oracle_rep_sum_i8.restype = _c.c_int8
+        lib.oracle_encode.argtypes = [_i, _vp, _i, _i, _i, _vp, _vp, _l]
+        lib.oracle_decode.argtypes = [_i, _i, _vp, _i, _i, _i, _i, _vp, _l, _vp, _vp]
+        lib.oracle_tree_stats.argtypes = [_i, _i, _vp, _i, _vp, _vp]
+        _oracle = lib
+    return _oracle
+
+
+def have_ref():
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libpolar_ref.so"))
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        lib = _c.CDLL(os.path.join(ORACLE_DIR, "_ref", "libpolar_ref.so"))
+        lib.polar_ref_frozen_bits.argtypes = [_i, _i, _c.c_float, _c.c_char_p, _vp]
+        lib.polar_ref_code_create.argtypes = [_i, _i, _vp, _i, _i, _i, _i]
+        lib.polar_ref_code_create.restype = _vp
+        lib.polar_ref_code_destroy.argtypes = [_vp]
+        lib.polar_ref_encode.argtypes = [_vp, _vp, _vp, _l]
+        lib.polar_ref_decode.argtypes = [_vp, _vp, _l, _vp, _vp, _i, _i]
+        lib.polar_ref_decode.restype = _d
+        lib.polar_ref_crc.argtypes = [_i, _vp, _i, _i]
+        _ref = lib
+    return _ref
+
+
+# ---------------------------------------------------------------- reference wrappers
+def ref_frozen_bits(N, K, dsnr=0.0, ctype="BB"):
+    out = np.zeros(N, np.uint32)
+    n = ref().polar_ref_frozen_bits(N, K, dsnr, ctype.encode(), _ptr(out))
+    if n < 0:
+        raise RuntimeError("reference frozen_bits threw")
+    return out[:n].copy()
+
+
+def ref_encode(N, frozen, info, systematic=1, crc=0):
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    info = np.ascontiguousarray(info, np.uint8).copy()
+    nF = info.shape[0]
+    code = np.zeros((nF, max(N // 8, 1)), np.uint8)
+    h = ref().polar_ref_code_create(KIND_ENC, N, _ptr(frozen), len(frozen), 1, systematic, crc)
+    rc = ref().polar_ref_encode(h, _ptr(info), _ptr(code), nF)
+    ref().polar_ref_code_destroy(h)
+    if rc:
+        raise RuntimeError("reference encode threw")
+    return code, info
+
+
+def ref_decode(kind, N, frozen, llr, L=1, systematic=1, crc=0, threads=1, repeat=1):
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    llr = np.ascontiguousarray(llr)
+    nF = llr.shape[0]
+    K = N - len(frozen)
+    out = np.zeros((nF, (K + 7) // 8), np.uint8)
+    ok = np.zeros(nF, np.uint8)
+    h = ref().polar_ref_code_create(kind, N, _ptr(frozen), len(frozen), L, systematic, crc)
+    t = ref().polar_ref_decode(h, _ptr(llr), nF, _ptr(out), _ptr(ok), threads, repeat)
+    ref().polar_ref_code_destroy(h)
+    if t < 0:
+        raise RuntimeError("reference decode threw")
+    return out, ok, t
+
+
+# ---------------------------------------------------------------- oracle wrappers
+def oracle_encode(N, frozen, info, systematic=1, crc=0):
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    info = np.ascontiguousarray(info, np.uint8).copy()
+    nF = info.shape[0]
+    code = np.zeros((nF, (N + 7) // 8), np.uint8)
+    oracle().oracle_encode(N, _ptr(frozen), len(frozen), systematic, crc, _ptr(info), _ptr(code), nF)
+    return code, info
+
+
+def oracle_decode(kind, N, frozen, llr, L=1, systematic=1, crc=0):
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    llr = np.ascontiguousarray(llr)
+    nF = llr.shape[0]
+    K = N - len(frozen)
+    out = np.zeros((nF, (K + 7) // 8), np.uint8)
+    ok = np.zeros(nF, np.uint8)
+    rc = oracle().oracle_decode(kind, N, _ptr(frozen), len(frozen), L, systematic, crc, _ptr(llr), nF,
+                                _ptr(out), _ptr(ok))
+    if rc:
+        raise RuntimeError("oracle decode failed rc=%d" % rc)
+    return out, ok
+
+
+def oracle_tree_stats(kind, N, frozen):
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    counts = np.zeros(16, np.int64)
+    sizes = np.zeros(16, np.int64)
+    rc = oracle().oracle_tree_stats(kind, N, _ptr(frozen), len(frozen), _ptr(counts), _ptr(sizes))
+    assert rc == 0
+    return {NODE_NAMES[i]: (int(counts[i]), int(sizes[i])) for i in range(len(NODE_NAMES))}
+
+
+def oracle_crc_generate(bits, data):
+    d = np.ascontiguousarray(data, np.uint8).copy()
+    oracle().oracle_crc_generate(bits, _ptr(d), len(d))
+    return d
+
+
+def oracle_crc_check(bits, data):
+    d = np.ascontiguousarray(data, np.uint8)
+    return bool(oracle().oracle_crc_check(bits, _ptr(d), len(d)))
+
+
+def oracle_quantize(llr):
+    llr = np.ascontiguousarray(llr, np.float32)
+    out = np.zeros(llr.shape, np.int8)
+    flat_in, flat_out = llr.reshape(-1, llr.shape[-1]), out.reshape(-1, llr.shape[-1])
+    for r in range(flat_in.shape[0]):
+        oracle().oracle_quantize(flat_in[r].ctypes.data, flat_out[r].ctypes.data, llr.shape[-1])
+    return out
+
+
+# ---------------------------------------------------------------- workloads
+def unpack_bits(packed, nbits):
+    return np.unpackbits(np.ascontiguousarray(packed, np.uint8), axis=-1, bitorder="big")[..., :nbits]
+
+
+def awgn_llrs(N, frozen, nFrames, ebn0_db=2.0, crc=0, seed=0xB200, systematic=1, encode=None,
+              fmt="i8"):
+    """payload -> CRC -> encode -> BPSK (0 -> +1) -> AWGN -> LLR.
+    sigma = 1/sqrt(2 (K/N) 10^(EbN0/10)) (simulator.cpp:832-838); int8 LLR = clamp(rne(10 y))
+    (setup.cpp:58, bitcontainer.cpp:487-497); fp32 LLR = 4 (K/N) 10^(EbN0/10) y ... the reference
+    scales by 4*EsN0-ish factors (simulator.cpp:377-378); we use 2 y / sigma^2.
+    Returns (llr, info_with_crc)."""
+    K = N - len(frozen)
+    rng = np.random.default_rng(seed)
+    info = rng.integers(0, 256, size=(nFrames, (K + 7) // 8), dtype=np.uint8)
+    if K % 8:
+        info[:, -1] &= (0xFF << (8 - K % 8)) & 0xFF
+    enc = encode or oracle_encode
+    code, info = enc(N, frozen, info, systematic, crc)
+    bits = unpack_bits(code, N).astype(np.float32)
+    x = 1.0 - 2.0 * bits
+    esn0 = (K / N) * 10.0 ** (ebn0_db / 10.0)
+    sigma = 1.0 / np.sqrt(2.0 * esn0)
+    y = x + sigma * rng.standard_normal(size=x.shape, dtype=np.float32)
+    if fmt == "i8":
+        llr = np.clip(np.rint(10.0 * y), -128, 127).astype(np.int8)
+    else:
+        llr = (2.0 / (sigma * sigma) * y).astype(np.float32)
+    return llr, info
+
+
+def pcbench_llrs(N, nFrames, seed=1, fmt="i8"):
+    """pcbench-style inputs: iid N(0, 0.5) floats, not codewords (main_benchmark.cpp:224); after
+    int8 rounding they are mostly {-1,0,1}: the tie-break stress case."""
+    rng = np.random.default_rng(seed)
+    y = (0.5 * rng.standard_normal(size=(nFrames, N))).astype(np.float32)
+    if fmt == "i8":
+        return np.clip(np.rint(y), -128, 127).astype(np.int8)
+    return y
+
+
+def stress_llrs(N, nFrames, seed=2, scale=40.0):
+    """Large-magnitude iid int8 LLRs: exercises saturation (+-127/-128) in G / REP / SPC."""
+    rng = np.random.default_rng(seed)
+    y = scale * rng.standard_normal(size=(nFrames, N))
+    return np.clip(np.rint(y), -128, 127).astype(np.int8)
