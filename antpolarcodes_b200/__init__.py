@@ -1,0 +1,351 @@
+"""antpolarcodes_b200 -- B200 (sm_100a) batched polar-code engine.
+
+Python mirror of the reference's pypolar surface (python/bindings/*.cc): ``PolarEncoder``,
+``PolarDecoder``, ``Detector`` and ``frozen_bits`` keep the reference's names, argument meaning and
+error behaviour, and gain batched methods (``encode_batch`` / ``decode_batch``) that take
+``[nFrames, ...]`` numpy arrays (host) or torch CUDA tensors (device resident, zero copy).
+
+Everything computes in ``libpolar_cuda.so`` (hand-written CUDA, C ABI in include/polar_cuda.h).
+There is no CPU fallback: importing works without a GPU, creating a code does not.
+"""
+import ctypes as _c
+import os as _os
+
+import numpy as _np
+
+_HERE = _os.path.dirname(_os.path.abspath(__file__))
+_LIB_PATH = _os.path.join(_HERE, "libpolar_cuda.so")
+
+KIND_ENC, KIND_FASTSSC_I8, KIND_FASTSSC_F32, KIND_SCL_I8, KIND_SCL_F32 = range(5)
+MEM_HOST, MEM_DEVICE = 0, 1
+LLR_I8, LLR_F32 = 0, 1
+
+EXPORTS = [
+    "polar_cuda_last_error", "polar_cuda_device_count", "polar_cuda_version", "polar_cuda_code_create",
+    "polar_cuda_code_destroy", "polar_cuda_decode_batch", "polar_cuda_encode_batch",
+    "polar_cuda_crc_generate", "polar_cuda_crc_check", "polar_cuda_frozen_bits", "polar_cuda_code_info",
+    "polar_cuda_code_schedule", "polar_cuda_code_launches", "polar_cuda_test_fg",
+]
+
+
+class CodeInfo(_c.Structure):
+    _fields_ = [("kind", _c.c_int), ("N", _c.c_int), ("K", _c.c_int), ("listSize", _c.c_int),
+                ("systematic", _c.c_int), ("crcBits", _c.c_int), ("nOps", _c.c_int),
+                ("warpsPerBlock", _c.c_int), ("blocksPerSM", _c.c_int), ("smemPerWarp", _c.c_int),
+                ("gridBlocks", _c.c_int), ("laneOpsPerFrame", _c.c_double), ("bytesPerFrame", _c.c_double),
+                ("opCount", _c.c_long * 32), ("opSize", _c.c_long * 32)]
+
+
+_lib = None
+
+
+def lib():
+    """The loaded C-ABI library.  Raises (loudly) if the CUDA extension has not been built."""
+    global _lib
+    if _lib is None:
+        if not _os.path.exists(_LIB_PATH):
+            raise ImportError("libpolar_cuda.so is missing: run `python antpolarcodes_b200/build.py` "
+                              "(or __graft_entry__.build()); there is no CPU fallback")
+        l = _c.CDLL(_LIB_PATH)
+        vp, i, sz = _c.c_void_p, _c.c_int, _c.c_size_t
+        l.polar_cuda_last_error.restype = _c.c_char_p
+        l.polar_cuda_code_create.argtypes = [i, i, i, vp, i, i, i, i, _c.POINTER(vp)]
+        l.polar_cuda_code_destroy.argtypes = [vp]
+        l.polar_cuda_decode_batch.argtypes = [vp, vp, i, i, sz, vp, vp, vp]
+        l.polar_cuda_encode_batch.argtypes = [vp, vp, i, sz, vp, vp]
+        l.polar_cuda_crc_generate.argtypes = [i, vp, i]
+        l.polar_cuda_crc_check.argtypes = [i, vp, i]
+        l.polar_cuda_frozen_bits.argtypes = [i, i, _c.c_float, _c.c_char_p, vp]
+        l.polar_cuda_code_info.argtypes = [vp, _c.POINTER(CodeInfo)]
+        l.polar_cuda_code_schedule.argtypes = [vp, vp, i]
+        l.polar_cuda_code_launches.argtypes = [vp]
+        l.polar_cuda_code_launches.restype = _c.c_long
+        l.polar_cuda_test_fg.argtypes = [vp, vp, vp, i, vp, vp]
+        _lib = l
+    return _lib
+
+
+def _check(rc):
+    if rc < 0:
+        msg = lib().polar_cuda_last_error().decode()
+        if rc == -1:
+            raise ValueError(msg)        # std::invalid_argument / std::logic_error in the reference
+        raise RuntimeError(msg)
+    return rc
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _buf(x):
+    """(pointer, mem) of a numpy array or torch tensor (must be contiguous)."""
+    if _is_torch(x):
+        if not x.is_contiguous():
+            raise RuntimeError("tensor must be contiguous")
+        return x.data_ptr(), (MEM_DEVICE if x.is_cuda else MEM_HOST)
+    if not x.flags["C_CONTIGUOUS"]:
+        raise RuntimeError("array must be C-contiguous")
+    return x.ctypes.data, MEM_HOST
+
+
+def frozen_bits(blockLength, infoLength, designSNR, constructorType="BB"):
+    """Construction::frozen_bits (frozen_bits_python.cc:24-29): sorted frozen indices."""
+    out = _np.zeros(max(int(blockLength), 1), _np.uint32)
+    n = _check(lib().polar_cuda_frozen_bits(int(blockLength), int(infoLength), float(designSNR),
+                                            str(constructorType).encode(), out.ctypes.data))
+    return out[:n].copy()
+
+
+class Detector:
+    """ErrorDetection::Detector created by ErrorDetection::create(size, type) (detector_python.cc:26-56)."""
+
+    def __init__(self, size=0, type="crc"):
+        t = str(type).lower()
+        if "crc" not in t:
+            if "cmac" in t:
+                raise RuntimeError("cmac detector is outside the GPU hot path")
+            raise RuntimeError("Unknown Error detector requested!")
+        if size not in (0, 8, 16, 32):
+            raise ValueError("CRC INVALID SIZE!")
+        self._bits = int(size)
+
+    def getCheckBitCount(self):
+        return self._bits
+
+    def getType(self):
+        return "CRC" if self._bits else "DUMMY"
+
+    def generate(self, data):
+        d = _np.ascontiguousarray(data, _np.uint8).copy()
+        _check(lib().polar_cuda_crc_generate(self._bits, d.ctypes.data, d.size))
+        return d
+
+    def check(self, data):
+        d = _np.ascontiguousarray(data, _np.uint8)
+        return bool(_check(lib().polar_cuda_crc_check(self._bits, d.ctypes.data, d.size)))
+
+
+class _Code:
+    def __init__(self, kind, N, frozen, L, systematic, crc, device=0):
+        self._h = _c.c_void_p()
+        f = _np.ascontiguousarray(frozen, _np.uint32)
+        _check(lib().polar_cuda_code_create(int(device), kind, int(N), f.ctypes.data, len(f), int(L),
+                                            int(bool(systematic)), int(crc), _c.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().polar_cuda_code_destroy(self._h)
+            self._h = _c.c_void_p()
+
+    __del__ = close
+
+    def info(self):
+        ci = CodeInfo()
+        _check(lib().polar_cuda_code_info(self._h, _c.byref(ci)))
+        return ci
+
+    def schedule(self):
+        n = _check(lib().polar_cuda_code_schedule(self._h, None, 0))
+        ops = _np.zeros(n, _np.uint32)
+        lib().polar_cuda_code_schedule(self._h, ops.ctypes.data, n)
+        return ops
+
+    def launches(self):
+        return int(lib().polar_cuda_code_launches(self._h))
+
+
+class PolarEncoder:
+    """Encoding::ButterflyFipPacked behind the pypolar PolarEncoder surface (encoder_python.cc:28-61)."""
+
+    def __init__(self, blockLength, frozenBitPositions, device=0):
+        self._N = int(blockLength)
+        self._frozen = _np.ascontiguousarray(frozenBitPositions, _np.uint32).copy()
+        self._sys, self._crc, self._dev, self._code = True, 0, device, None
+
+    def _get(self):
+        if self._code is None:
+            self._code = _Code(KIND_ENC, self._N, self._frozen, 1, self._sys, self._crc, self._dev)
+        return self._code
+
+    def _reset(self):
+        if self._code is not None:
+            self._code.close()
+        self._code = None
+
+    def blockLength(self):
+        return self._N
+
+    def infoLength(self):
+        return self._N - len(self._frozen)
+
+    def frozenBits(self):
+        return self._frozen.copy()
+
+    def setSystematic(self, flag):
+        self._sys = bool(flag)
+        self._reset()
+
+    def isSystematic(self):
+        return self._sys
+
+    def setErrorDetection(self, size=0, type="crc"):
+        self._crc = Detector(size, type).getCheckBitCount()
+        self._reset()
+
+    def getErrorDetectionMode(self):
+        return "%s-%d" % ("CRC" if self._crc else "DUMMY", self._crc)
+
+    def encode_vector(self, info):
+        """uint8[K/8] -> uint8[N/8] (one frame).  The caller's array is NOT modified (the pybind wrapper
+        of the reference mutates its argument in place; use encode_batch for that behaviour)."""
+        a = _np.ascontiguousarray(info, _np.uint8)
+        if a.ndim != 1:
+            raise RuntimeError("Number of dimensions must be one")
+        if a.size != (self.infoLength() + 7) // 8:
+            raise RuntimeError("Input vector size mismatch!")
+        return self.encode_batch(a.reshape(1, -1).copy())[0]
+
+    def encode_batch(self, info, out=None, stream=0):
+        """[nFrames, K/8] uint8 -> [nFrames, N/8] uint8.  CRC bytes are written into `info` in place
+        (butterfly_fip_packed.cpp:47-50).  numpy arrays are staged through the device, torch CUDA tensors
+        are used where they are."""
+        kb, nb = (self.infoLength() + 7) // 8, max(self._N // 8, 1)
+        if info.ndim != 2 or info.shape[1] != kb:
+            raise RuntimeError("Input vector size mismatch!")
+        n = info.shape[0]
+        if out is None:
+            if _is_torch(info):
+                import torch
+                out = torch.empty((n, nb), dtype=torch.uint8, device=info.device)
+            else:
+                out = _np.empty((n, nb), _np.uint8)
+        ip, mem = _buf(info)
+        op, mem2 = _buf(out)
+        if mem != mem2:
+            raise RuntimeError("info and out must live in the same memory space")
+        _check(lib().polar_cuda_encode_batch(self._get()._h, ip, mem, n, op, stream))
+        return out
+
+
+class PolarDecoder:
+    """Decoding::create(blockLength, listSize, frozenBits, decoderType) behind the pypolar PolarDecoder
+    surface (decoder_python.cc:21-74).  listSize 1 -> Fast-SSC, listSize > 1 -> SCL; "char" = int8
+    arithmetic (FastSscFipChar / SclFipChar), "float" = fp32.  Like the reference's makeDecoder
+    (decoder.cpp:85) a fresh decoder checks CRC8 until setErrorDetection is called."""
+
+    def __init__(self, blockLength, listSize, frozenBitPositions, decoderType="char", device=0):
+        t = str(decoderType).lower()
+        if "char" in t:
+            flt = False
+        elif "float" in t:
+            flt = True
+        elif "mixed" in t or "scan" in t:
+            raise RuntimeError("decoder type '%s' is outside the GPU hot path" % decoderType)
+        else:
+            raise ValueError("Unknown PolarDecoder type!")
+        self._N, self._L = int(blockLength), int(listSize)
+        self._frozen = _np.ascontiguousarray(frozenBitPositions, _np.uint32).copy()
+        if self._L <= 1:
+            self._kind = KIND_FASTSSC_F32 if flt else KIND_FASTSSC_I8
+        else:
+            self._kind = KIND_SCL_F32 if flt else KIND_SCL_I8
+        self._sys, self._crc, self._dev, self._code = True, 8, device, None
+
+    def _get(self):
+        if self._code is None:
+            self._code = _Code(self._kind, self._N, self._frozen, max(self._L, 1), self._sys, self._crc, self._dev)
+        return self._code
+
+    def _reset(self):
+        if self._code is not None:
+            self._code.close()
+        self._code = None
+
+    def blockLength(self):
+        return self._N
+
+    def infoLength(self):
+        return self._N - len(self._frozen)
+
+    def listSize(self):
+        return max(self._L, 1)
+
+    def frozenBits(self):
+        return self._frozen.copy()
+
+    def setSystematic(self, flag):
+        self._sys = bool(flag)
+        self._reset()
+
+    def isSystematic(self):
+        return self._sys
+
+    def setErrorDetection(self, size=0, type="crc"):
+        self._crc = Detector(size, type).getCheckBitCount()
+        self._reset()
+
+    def getErrorDetectionMode(self):
+        return "%s-%d" % ("CRC" if self._crc else "DUMMY", self._crc)
+
+    def info(self):
+        return self._get().info()
+
+    def decode_vector(self, llr):
+        """float32[N] or int8[N] -> uint8[K/8]; the detector verdict is dropped, as in decoder_python.cc."""
+        a = _np.ascontiguousarray(llr)
+        if a.ndim != 1:
+            raise RuntimeError("Number of dimensions must be one")
+        if a.size != self._N:
+            raise RuntimeError("Input vector size mismatch!")
+        out, _ = self.decode_batch(a.reshape(1, -1))
+        return out[0]
+
+    def decode_batch(self, llr, out=None, ok=None, stream=0):
+        """[nFrames, N] int8 / float32 LLRs -> ([nFrames, ceil(K/8)] uint8, [nFrames] uint8 verdicts)."""
+        if llr.ndim != 2 or llr.shape[1] != self._N:
+            raise RuntimeError("Input vector size mismatch!")
+        n, kb = llr.shape[0], (self.infoLength() + 7) // 8
+        if _is_torch(llr):
+            import torch
+            if llr.dtype == torch.int8:
+                lt = LLR_I8
+            elif llr.dtype == torch.float32:
+                lt = LLR_F32
+            else:
+                raise RuntimeError("LLRs must be int8 or float32")
+            if out is None:
+                out = torch.empty((n, kb), dtype=torch.uint8, device=llr.device)
+            if ok is None:
+                ok = torch.empty((n,), dtype=torch.uint8, device=llr.device)
+        else:
+            if llr.dtype == _np.int8:
+                lt = LLR_I8
+            elif llr.dtype == _np.float32:
+                lt = LLR_F32
+            else:
+                raise RuntimeError("LLRs must be int8 or float32")
+            llr = _np.ascontiguousarray(llr)
+            if out is None:
+                out = _np.empty((n, kb), _np.uint8)
+            if ok is None:
+                ok = _np.empty((n,), _np.uint8)
+        lp, mem = _buf(llr)
+        op, m2 = _buf(out)
+        kp, m3 = _buf(ok)
+        if not (mem == m2 == m3):
+            raise RuntimeError("llr, out and ok must live in the same memory space")
+        _check(lib().polar_cuda_decode_batch(self._get()._h, lp, lt, mem, n, op, kp, stream))
+        return out, ok
+
+
+def test_fg(a, b, bits):
+    """Element-wise device F / G (golden-vector hook)."""
+    a = _np.ascontiguousarray(a, _np.int8)
+    b = _np.ascontiguousarray(b, _np.int8)
+    bits = _np.ascontiguousarray(bits, _np.int8)
+    f = _np.empty_like(a)
+    g = _np.empty_like(a)
+    _check(lib().polar_cuda_test_fg(a.ctypes.data, b.ctypes.data, bits.ctypes.data, a.size, f.ctypes.data,
+                                    g.ctypes.data))
+    return f, g

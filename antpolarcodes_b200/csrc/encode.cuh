@@ -1,0 +1,152 @@
+// Bit-packed polar encoder for sm_100a (replaces Encoding::ButterflyFipPacked::encode,
+// src/polarcode/encoding/butterfly_fip_packed.cpp:45-70).
+//
+// One frame = N/32 words = one word per lane (N <= 1024: 32/(N/32) frames per warp; N > 1024: several
+// words per lane).  Per frame: CRC generate in place (Detector::generate, via the linear table of
+// crc_host.h) -> scatter the K info bits to the non-frozen positions (bitcontainer.cpp:886-898) ->
+// F^{(x)n}: stages 0-4 are shift/mask XORs inside the word, stages >= 5 are __shfl_xor_sync exchanges
+// (butterfly_fip.cpp:31-63) -> systematic: mask the frozen positions and transform again (:52-57) ->
+// MSB-first bytes with coalesced 4-byte stores.
+#pragma once
+#include "primitives.cuh"
+
+namespace polar {
+
+struct EncodeParams {
+    uint8_t* info;          // nFrames x kb, CRC trailer written in place
+    uint8_t* code;          // nFrames x nb
+    const uint2* wordTab;   // per code word: x = mask of info positions, y = number of info bits before it
+    const uint32_t* genTab; // per info bit: CRC contribution
+    uint32_t genInit;
+    long long nFrames;
+    int N, lgN, K, kb, nb, crcBits, systematic;
+};
+
+POLAR_DEV uint32_t inword_transform(uint32_t v)
+{
+    v ^= (v >> 1) & 0x55555555u;
+    v ^= (v >> 2) & 0x33333333u;
+    v ^= (v >> 4) & 0x0F0F0F0Fu;
+    v ^= (v >> 8) & 0x00FF00FFu;
+    v ^= (v >> 16) & 0x0000FFFFu;
+    return v;
+}
+
+// WPL = words per lane (1 for N <= 1024, N/1024 above)
+template <int WPL>
+__global__ void __launch_bounds__(256) encode_kernel(const __grid_constant__ EncodeParams p)
+{
+    __shared__ __align__(16) uint8_t sinfo[8][512];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpsPerBlock = blockDim.x >> 5;
+    const int W = p.N >= 32 ? p.N >> 5 : 1;          // words per frame
+    const int lpf = W < 32 ? W : 32;                  // lanes per frame
+    const int lgLpf = 31 - __clz(lpf);
+    const int fpw = 32 / lpf;                         // frames per warp
+    const int fi = lane >> lgLpf, g = lane & (lpf - 1);
+    uint8_t* myInfo = &sinfo[warp][fi * p.kb];
+    const int trailerBit = p.crcBits == 8 ? 8 * (p.kb - 1) : p.crcBits == 16 ? 8 * (p.kb - 2)
+                         : p.crcBits == 32 ? 32 * ((p.kb >> 2) - 1) : 8 * p.kb;
+
+    const long long totalGroups = (long long)gridDim.x * warpsPerBlock;
+    const long long nGroups = (p.nFrames + fpw - 1) / fpw;
+    for (long long grp = (long long)blockIdx.x * warpsPerBlock + warp; grp < nGroups; grp += totalGroups) {
+        const long long frame = grp * fpw + fi;
+        const bool live = frame < p.nFrames;
+        uint8_t* ginfo = p.info + frame * p.kb;
+        // stage the info bytes of this lane group's frame
+        if (live)
+            for (int i = g; i < p.kb; i += lpf) myInfo[i] = ginfo[i];
+        __syncwarp();
+        if (p.crcBits) {
+            uint32_t crc = 0;
+            if (live)
+                for (int k = g; k < trailerBit; k += lpf)
+                    if ((myInfo[k >> 3] >> (7 - (k & 7))) & 1) crc ^= __ldg(p.genTab + k);
+            for (int d = 1; d < lpf; d <<= 1) crc ^= __shfl_xor_sync(FULL_MASK, crc, d);
+            crc ^= p.genInit;
+            __syncwarp();
+            if (live && g == 0) {
+                const int t = trailerBit >> 3;
+                if (p.crcBits == 8) {
+                    myInfo[t] = (uint8_t)crc;
+                } else if (p.crcBits == 16) { // big-endian trailer: crc16.cpp:35-43
+                    myInfo[t] = (uint8_t)(crc >> 8);
+                    myInfo[t + 1] = (uint8_t)crc;
+                } else {                       // native little-endian u32: crc32.cpp:55-66
+                    for (int i = 0; i < 4; ++i) myInfo[t + i] = (uint8_t)(crc >> (8 * i));
+                }
+                for (int i = 0; i < p.crcBits / 8; ++i) ginfo[t + i] = myInfo[t + i];
+            }
+            __syncwarp();
+        }
+        // scatter: deposit the next popc(mask) info bits into the mask positions of each word
+        uint32_t word[WPL], mask[WPL];
+#pragma unroll
+        for (int j = 0; j < WPL; ++j) {
+            const uint2 t = __ldg(p.wordTab + (j * 32 + g));
+            mask[j] = t.x;
+            uint32_t m = t.x, v = 0;
+            int k = (int)t.y;
+            while (m) {
+                const int b = __ffs(m) - 1;
+                m &= m - 1;
+                v |= (uint32_t)((myInfo[k >> 3] >> (7 - (k & 7))) & 1) << b;
+                ++k;
+            }
+            word[j] = live ? v : 0u;
+        }
+        for (int pass = 0; pass < (p.systematic ? 2 : 1); ++pass) {
+#pragma unroll
+            for (int j = 0; j < WPL; ++j) {
+                if (pass) word[j] &= mask[j];
+                word[j] = inword_transform(word[j]);
+            }
+            for (int d = 1; d < lpf; d <<= 1) {
+#pragma unroll
+                for (int j = 0; j < WPL; ++j) {
+                    const uint32_t other = __shfl_xor_sync(FULL_MASK, word[j], d);
+                    if (!(g & d)) word[j] ^= other;
+                }
+            }
+#pragma unroll
+            for (int dj = 1; dj < WPL; dj <<= 1)
+#pragma unroll
+                for (int j = 0; j < WPL; ++j)
+                    if (!(j & dj)) word[j] ^= word[j + dj];
+        }
+        if (live) {
+            uint8_t* gcode = p.code + frame * p.nb;
+#pragma unroll
+            for (int j = 0; j < WPL; ++j) {
+                const uint32_t o = __byte_perm(__brev(word[j]), 0u, 0x0123u);
+                if (p.N >= 32) {
+                    reinterpret_cast<uint32_t*>(gcode)[j * 32 + g] = o;
+                } else {
+                    for (int i = 0; i < p.nb; ++i) gcode[i] = (uint8_t)(o >> (8 * i));
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+inline int launch_encode(const EncodeParams& p, int numSMs, cudaStream_t st)
+{
+    const int W = p.N >= 32 ? p.N >> 5 : 1;
+    const int fpw = W < 32 ? 32 / W : 1;
+    const long long groups = (p.nFrames + fpw - 1) / fpw;
+    const int warpsPerBlock = 8;
+    long long blocks = (groups + warpsPerBlock - 1) / warpsPerBlock;
+    const long long cap = (long long)numSMs * 8;
+    if (blocks > cap) blocks = cap;
+    const int wpl = W <= 32 ? 1 : W / 32;
+    switch (wpl) {
+    case 1: encode_kernel<1><<<(int)blocks, warpsPerBlock * 32, 0, st>>>(p); break;
+    case 2: encode_kernel<2><<<(int)blocks, warpsPerBlock * 32, 0, st>>>(p); break;
+    case 4: encode_kernel<4><<<(int)blocks, warpsPerBlock * 32, 0, st>>>(p); break;
+    default: return -1;
+    }
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+} // namespace polar

@@ -1,0 +1,422 @@
+// libpolar_cuda: C ABI (include/polar_cuda.h) over the sm_100a kernels.
+#include "../../include/polar_cuda.h"
+
+#include "construct.h"
+#include "crc_host.h"
+#include "decode_params.h"
+#include "encode.cuh"
+#include "fastssc_i8.cuh"
+#include "schedule.h"
+#include "scl_i8.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace polar;
+
+namespace {
+
+thread_local std::string g_lastError;
+
+int fail(int code, const std::string& msg)
+{
+    g_lastError = msg;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                                \
+    do {                                                                                              \
+        cudaError_t e__ = (expr);                                                                     \
+        if (e__ != cudaSuccess)                                                                       \
+            return fail(POLAR_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));           \
+    } while (0)
+
+typedef void (*DecodeKernel)(const DecodeParams, const Schedule);
+
+} // namespace
+
+struct polar_code {
+    int device = 0, kind = 0, N = 0, lgN = 0, K = 0, kb = 0, L = 1, systematic = 1, crcBits = 0;
+    std::vector<uint32_t> frozen;
+    std::vector<uint32_t> ops;
+    ScheduleStats stats;
+    Schedule sched;
+    // device tables
+    uint16_t* dInfoPos = nullptr;  // K
+    uint2* dWordTab = nullptr;     // per code word: info-position mask, info bits before it (encoder)
+    uint32_t* dSynTab = nullptr;   // K
+    uint32_t* dGenTab = nullptr;   // K
+    uint32_t synInit = 0, genInit = 0;
+    // launch geometry
+    DecodeKernel kernel = nullptr;
+    DecodeParams geo{};            // geometry fields only
+    int warpsPerBlock = 0, blocksPerSM = 0, numSMs = 0;
+    size_t smemPerBlock = 0;
+    // staging buffers for HOST-memory calls
+    void* dLlr = nullptr;
+    uint8_t* dOut = nullptr;
+    uint8_t* dOk = nullptr;
+    uint8_t* dInfo = nullptr;
+    size_t stageFrames = 0;
+    int stageLlrBytes = 0;
+    long launches = 0;
+};
+
+namespace {
+
+template <int L>
+DecodeKernel scl_kernel_for() { return scl_i8_kernel<L>; }
+
+DecodeKernel pick_scl_kernel(int L)
+{
+    switch (L) {
+    case 1: return scl_kernel_for<1>();
+    case 2: return scl_kernel_for<2>();
+    case 4: return scl_kernel_for<4>();
+    case 8: return scl_kernel_for<8>();
+    case 16: return scl_kernel_for<16>();
+    case 32: return scl_kernel_for<32>();
+    }
+    return nullptr;
+}
+
+int setup_decoder_geometry(polar_code* c)
+{
+    DecodeParams& g = c->geo;
+    g.N = c->N;
+    g.lgN = c->lgN;
+    g.K = c->K;
+    g.kb = c->kb;
+    g.crcBits = c->crcBits;
+    g.systematic = c->systematic;
+    g.listSize = c->L;
+    g.chanW = c->N / 4;
+    const bool scl = (c->kind == POLAR_KIND_SCL_I8);
+    const int L = scl ? c->L : 1;
+    int slot = llr_woff(c->lgN);
+    if (scl) {
+        const int want = (32 / L) % 32; // slot stride == lanes-per-path (mod 32): conflict-free banks
+        while ((slot % 32) != want) ++slot;
+    }
+    g.slotW = slot;
+    g.bitW = bit_woff(c->lgN) + std::max(1, c->N / 32);
+    g.bitSlotW = scl ? ((2 * g.bitW) | 1) : g.bitW;
+    const int epi = (c->K + 31) / 32 + std::max(1, c->N / 32);
+    g.scratchW = std::max(8 * L, epi) + 4;
+    int total = g.chanW + L * g.slotW + L * g.bitSlotW + g.scratchW;
+    total = (total + 3) & ~3;
+    g.warpW = total;
+
+    c->kernel = scl ? pick_scl_kernel(L) : (DecodeKernel)fastssc_i8_kernel;
+    if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, c->device));
+    c->numSMs = prop.multiProcessorCount;
+    const size_t perWarp = (size_t)g.warpW * 4;
+    if (perWarp > (size_t)prop.sharedMemPerBlockOptin)
+        return fail(POLAR_E_UNSUPPORTED, "code does not fit in shared memory (N x listSize too large)");
+    int bestWarps = 0, bestW = 1, bestB = 1;
+    for (int w : { 8, 4, 2, 1 }) {
+        const size_t smem = perWarp * w;
+        if (smem > (size_t)prop.sharedMemPerBlockOptin) continue;
+        CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int nb = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)c->kernel, w * 32, smem));
+        if (nb * w > bestWarps) { bestWarps = nb * w; bestW = w; bestB = nb; }
+    }
+    if (!bestWarps) return fail(POLAR_E_UNSUPPORTED, "kernel cannot be resident with this shared memory footprint");
+    c->warpsPerBlock = bestW;
+    c->blocksPerSM = bestB;
+    c->smemPerBlock = perWarp * bestW;
+    CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)c->smemPerBlock));
+    return POLAR_OK;
+}
+
+int ensure_staging(polar_code* c, size_t nFrames, int llrBytesPerElem)
+{
+    if (nFrames <= c->stageFrames && llrBytesPerElem <= c->stageLlrBytes) return POLAR_OK;
+    cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
+    c->dLlr = nullptr; c->dOut = c->dOk = c->dInfo = nullptr;
+    c->stageFrames = 0;
+    const size_t f = std::max(nFrames, (size_t)1);
+    const int eb = std::max(llrBytesPerElem, c->stageLlrBytes);
+    if (c->kind == POLAR_KIND_ENC) {
+        CUDA_TRY(cudaMalloc(&c->dInfo, f * c->kb));
+        CUDA_TRY(cudaMalloc(&c->dOut, f * (size_t)std::max(1, c->N / 8)));
+    } else {
+        CUDA_TRY(cudaMalloc(&c->dLlr, f * c->N * (size_t)eb));
+        CUDA_TRY(cudaMalloc(&c->dOut, f * c->kb));
+        CUDA_TRY(cudaMalloc(&c->dOk, f));
+    }
+    c->stageFrames = f;
+    c->stageLlrBytes = eb;
+    return POLAR_OK;
+}
+
+} // namespace
+
+// ---------------------------------------------------------------- C ABI
+extern "C" {
+
+const char* polar_cuda_last_error(void) { return g_lastError.c_str(); }
+
+int polar_cuda_version(void) { return 100; }
+
+int polar_cuda_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int polar_cuda_code_destroy(polar_code_t c)
+{
+    if (!c) return POLAR_OK;
+    cudaSetDevice(c->device);
+    cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab);
+    cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
+    delete c;
+    return POLAR_OK;
+}
+
+int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, int nFrozen, int listSize,
+                           int systematic, int crcBits, polar_code_t* out)
+{
+    if (!out) return fail(POLAR_E_ARG, "out is null");
+    *out = nullptr;
+    if (kind < POLAR_KIND_ENC || kind > POLAR_KIND_SCL_F32) return fail(POLAR_E_ARG, "unknown kind");
+    if (N < 8 || N > 4096 || (N & (N - 1))) return fail(POLAR_E_ARG, "block length must be a power of two in [8, 4096]");
+    if (nFrozen < 0 || nFrozen > N || (nFrozen && !frozen)) return fail(POLAR_E_ARG, "bad frozen set");
+    if (crcBits != 0 && crcBits != 8 && crcBits != 16 && crcBits != 32) return fail(POLAR_E_ARG, "CRC INVALID SIZE!");
+    const int K = N - nFrozen;
+    if (crcBits && (K % 8 != 0 || K < crcBits))
+        return fail(POLAR_E_ARG, "with a CRC, K must be a multiple of 8 and at least the CRC size");
+    if (crcBits == 32 && K / 8 < 4) return fail(POLAR_E_ARG, "CRC32 needs at least 4 info bytes");
+    if (K < 1) return fail(POLAR_E_ARG, "no information bits");
+    if (kind == POLAR_KIND_FASTSSC_F32 || kind == POLAR_KIND_SCL_F32)
+        return fail(POLAR_E_UNSUPPORTED, "fp32 decoders are not built yet");
+    if (cudaSetDevice(device) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(POLAR_E_CUDA, "cudaSetDevice failed (no CUDA device?)");
+    }
+    polar_code* c = new polar_code;
+    c->device = device; c->kind = kind; c->N = N; c->K = K; c->kb = (K + 7) / 8;
+    c->L = (kind == POLAR_KIND_SCL_I8) ? listSize : 1;
+    c->systematic = systematic ? 1 : 0; c->crcBits = crcBits;
+    while ((1 << c->lgN) < N) ++c->lgN;
+    c->frozen.assign(frozen, frozen + nFrozen);
+    int rc = POLAR_OK;
+    do {
+        const char* err = nullptr;
+        if (kind != POLAR_KIND_ENC) {
+            TreeKind tk = (kind == POLAR_KIND_SCL_I8) ? TREE_SCL_I8 : TREE_FASTSSC_I8;
+            if (!compile_schedule(tk, N, c->frozen, c->L, c->ops, c->stats, &err)) { rc = fail(POLAR_E_ARG, err); break; }
+            memset(&c->sched, 0, sizeof(c->sched));
+            memcpy(c->sched.ops, c->ops.data(), c->ops.size() * sizeof(uint32_t));
+        } else {
+            for (size_t i = 0; i < c->frozen.size(); ++i)
+                if (c->frozen[i] >= (uint32_t)N || (i && c->frozen[i] <= c->frozen[i - 1])) {
+                    rc = fail(POLAR_E_ARG, "frozen indices must be sorted, unique and < N");
+                    break;
+                }
+            if (rc) break;
+        }
+        // info-position LUT (bitcontainer.cpp:68-84) and its inverse
+        std::vector<uint16_t> infoPos;
+        const int nWords = std::max(1, N / 32);
+        std::vector<uint2> wordTab(nWords, make_uint2(0u, 0u));
+        {
+            std::vector<uint8_t> fm(N, 0);
+            for (uint32_t f : c->frozen) fm[f] = 1;
+            for (int i = 0; i < N; ++i) {
+                if ((i & 31) == 0) wordTab[i >> 5].y = (uint32_t)infoPos.size();
+                if (!fm[i]) { wordTab[i >> 5].x |= 1u << (i & 31); infoPos.push_back((uint16_t)i); }
+            }
+        }
+        CrcTables t = build_crc_tables(crcBits, K);
+        c->synInit = t.synInit; c->genInit = t.genInit;
+        cudaError_t e;
+        if ((e = cudaMalloc(&c->dInfoPos, K * sizeof(uint16_t))) != cudaSuccess ||
+            (e = cudaMalloc(&c->dWordTab, nWords * sizeof(uint2))) != cudaSuccess ||
+            (e = cudaMalloc(&c->dSynTab, K * sizeof(uint32_t))) != cudaSuccess ||
+            (e = cudaMalloc(&c->dGenTab, K * sizeof(uint32_t))) != cudaSuccess ||
+            (e = cudaMemcpy(c->dInfoPos, infoPos.data(), K * sizeof(uint16_t), cudaMemcpyHostToDevice)) != cudaSuccess ||
+            (e = cudaMemcpy(c->dWordTab, wordTab.data(), nWords * sizeof(uint2), cudaMemcpyHostToDevice)) != cudaSuccess ||
+            (e = cudaMemcpy(c->dSynTab, t.syn.data(), K * sizeof(uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess ||
+            (e = cudaMemcpy(c->dGenTab, t.gen.data(), K * sizeof(uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
+            rc = fail(POLAR_E_CUDA, std::string("table upload: ") + cudaGetErrorString(e));
+            break;
+        }
+        if (kind != POLAR_KIND_ENC) {
+            rc = setup_decoder_geometry(c);
+        } else {
+            cudaDeviceProp prop;
+            if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { rc = fail(POLAR_E_CUDA, "cudaGetDeviceProperties"); break; }
+            c->numSMs = prop.multiProcessorCount;
+        }
+    } while (0);
+    if (rc) { polar_cuda_code_destroy(c); return rc; }
+    *out = c;
+    return POLAR_OK;
+}
+
+int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int mem, size_t nFrames,
+                            uint8_t* info_out, uint8_t* ok_out, void* stream)
+{
+    if (!c) return fail(POLAR_E_ARG, "null code handle");
+    if (c->kind == POLAR_KIND_ENC) return fail(POLAR_E_ARG, "handle is an encoder");
+    if (nFrames == 0) return POLAR_OK;
+    if (!llr || !info_out) return fail(POLAR_E_ARG, "null buffer");
+    if (llrType != POLAR_LLR_I8 && llrType != POLAR_LLR_F32) return fail(POLAR_E_ARG, "bad llr type");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int eb = llrType == POLAR_LLR_F32 ? 4 : 1;
+    DecodeParams p = c->geo;
+    p.infoPos = c->dInfoPos;
+    p.crcTab = c->dSynTab;
+    p.crcInit = c->synInit;
+    p.nFrames = (long long)nFrames;
+    p.llrIsFloat = llrType == POLAR_LLR_F32;
+    uint8_t* okDev = ok_out;
+    if (mem == POLAR_MEM_HOST) {
+        int rc = ensure_staging(c, nFrames, eb);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpyAsync(c->dLlr, llr, nFrames * c->N * (size_t)eb, cudaMemcpyHostToDevice, st));
+        p.llr = c->dLlr; p.out = c->dOut; p.ok = c->dOk;
+    } else {
+        if (!okDev) { // the kernels always write the verdict
+            int rc = ensure_staging(c, nFrames, 0);
+            if (rc) return rc;
+            okDev = c->dOk;
+        }
+        p.llr = llr; p.out = info_out; p.ok = okDev;
+    }
+    const long long blocksNeeded = ((long long)nFrames + c->warpsPerBlock - 1) / c->warpsPerBlock;
+    const int grid = (int)std::min<long long>(blocksNeeded, (long long)c->blocksPerSM * c->numSMs);
+    c->kernel<<<grid, c->warpsPerBlock * 32, c->smemPerBlock, st>>>(p, c->sched);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    if (mem == POLAR_MEM_HOST) {
+        CUDA_TRY(cudaMemcpyAsync(info_out, c->dOut, nFrames * (size_t)c->kb, cudaMemcpyDeviceToHost, st));
+        if (ok_out) CUDA_TRY(cudaMemcpyAsync(ok_out, c->dOk, nFrames, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    return POLAR_OK;
+}
+
+int polar_cuda_encode_batch(polar_code_t c, uint8_t* info, int mem, size_t nFrames, uint8_t* code_out, void* stream)
+{
+    if (!c) return fail(POLAR_E_ARG, "null code handle");
+    if (c->kind != POLAR_KIND_ENC) return fail(POLAR_E_ARG, "handle is not an encoder");
+    if (nFrames == 0) return POLAR_OK;
+    if (!info || !code_out) return fail(POLAR_E_ARG, "null buffer");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    EncodeParams p{};
+    p.N = c->N; p.lgN = c->lgN; p.K = c->K; p.kb = c->kb; p.nb = std::max(1, c->N / 8);
+    p.crcBits = c->crcBits; p.systematic = c->systematic;
+    p.wordTab = c->dWordTab; p.genTab = c->dGenTab; p.genInit = c->genInit;
+    p.nFrames = (long long)nFrames;
+    if (mem == POLAR_MEM_HOST) {
+        int rc = ensure_staging(c, nFrames, 0);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpyAsync(c->dInfo, info, nFrames * (size_t)c->kb, cudaMemcpyHostToDevice, st));
+        p.info = c->dInfo; p.code = c->dOut;
+    } else {
+        p.info = info; p.code = code_out;
+    }
+    int rc = launch_encode(p, c->numSMs, st);
+    c->launches++;
+    if (rc) return fail(POLAR_E_CUDA, std::string("encode launch: ") + cudaGetErrorString(cudaGetLastError()));
+    if (mem == POLAR_MEM_HOST) {
+        CUDA_TRY(cudaMemcpyAsync(code_out, c->dOut, nFrames * (size_t)p.nb, cudaMemcpyDeviceToHost, st));
+        if (c->crcBits) CUDA_TRY(cudaMemcpyAsync(info, c->dInfo, nFrames * (size_t)c->kb, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    return POLAR_OK;
+}
+
+int polar_cuda_crc_generate(int crcBits, uint8_t* data, int bytes)
+{
+    if (crcBits != 0 && crcBits != 8 && crcBits != 16 && crcBits != 32) return fail(POLAR_E_ARG, "CRC INVALID SIZE!");
+    if (!data || bytes < crcBits / 8 || (crcBits == 32 && bytes < 4)) return fail(POLAR_E_ARG, "buffer too short for the CRC");
+    crc_generate(crcBits, data, bytes);
+    return POLAR_OK;
+}
+
+int polar_cuda_crc_check(int crcBits, const uint8_t* data, int bytes)
+{
+    if (crcBits != 0 && crcBits != 8 && crcBits != 16 && crcBits != 32) return fail(POLAR_E_ARG, "CRC INVALID SIZE!");
+    if (!data || bytes < crcBits / 8 || (crcBits == 32 && bytes < 4)) return fail(POLAR_E_ARG, "buffer too short for the CRC");
+    return crc_check(crcBits, data, bytes) ? 1 : 0;
+}
+
+int polar_cuda_frozen_bits(int N, int K, float designSnr, const char* type, uint32_t* out)
+{
+    if (!type || !out) return fail(POLAR_E_ARG, "null argument");
+    std::vector<uint32_t> f;
+    std::string err;
+    if (!construct_frozen_bits(N, K, designSnr, type, f, err)) return fail(POLAR_E_ARG, err);
+    for (size_t i = 0; i < f.size(); ++i) out[i] = f[i];
+    return (int)f.size();
+}
+
+int polar_cuda_code_info(polar_code_t c, struct polar_code_info* info)
+{
+    if (!c || !info) return fail(POLAR_E_ARG, "null argument");
+    memset(info, 0, sizeof(*info));
+    info->kind = c->kind; info->N = c->N; info->K = c->K; info->listSize = c->L;
+    info->systematic = c->systematic; info->crcBits = c->crcBits;
+    info->nOps = (int)c->ops.size();
+    info->warpsPerBlock = c->warpsPerBlock; info->blocksPerSM = c->blocksPerSM;
+    info->smemPerWarp = c->geo.warpW * 4; info->gridBlocks = c->blocksPerSM * c->numSMs;
+    info->laneOpsPerFrame = c->stats.laneOps;
+    info->bytesPerFrame = c->kind == POLAR_KIND_ENC ? (double)(c->kb + std::max(1, c->N / 8)) : (double)(c->N + c->kb + 1);
+    for (int i = 0; i < 32 && i < (int)OP_COUNT; ++i) { info->opCount[i] = c->stats.count[i]; info->opSize[i] = c->stats.size[i]; }
+    return POLAR_OK;
+}
+
+int polar_cuda_code_schedule(polar_code_t c, uint32_t* ops, int maxOps)
+{
+    if (!c) return fail(POLAR_E_ARG, "null code handle");
+    const int n = (int)c->ops.size();
+    if (ops) memcpy(ops, c->ops.data(), sizeof(uint32_t) * std::min(n, maxOps));
+    return n;
+}
+
+long polar_cuda_code_launches(polar_code_t c) { return c ? c->launches : 0; }
+
+} // extern "C"
+
+// ---------------------------------------------------------------- primitive self-test
+namespace {
+__global__ void test_fg_kernel(const uint32_t* a, const uint32_t* b, const uint32_t* bits, int words, uint32_t* f,
+                               uint32_t* g)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= words) return;
+    f[i] = f4(a[i], b[i]);
+    g[i] = g4(a[i], b[i], nibble_to_bytemask(sign_nibble(bits[i])));
+}
+} // namespace
+
+extern "C" int polar_cuda_test_fg(const int8_t* a, const int8_t* b, const int8_t* bits, int n, int8_t* f_out,
+                                  int8_t* g_out)
+{
+    if (n <= 0 || (n & 3)) return fail(POLAR_E_ARG, "n must be a positive multiple of 4");
+    uint32_t* d[5] = {};
+    for (auto& p : d) CUDA_TRY(cudaMalloc(&p, n));
+    CUDA_TRY(cudaMemcpy(d[0], a, n, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(d[1], b, n, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(d[2], bits, n, cudaMemcpyHostToDevice));
+    const int words = n / 4;
+    test_fg_kernel<<<(words + 255) / 256, 256>>>(d[0], d[1], d[2], words, d[3], d[4]);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpy(f_out, d[3], n, cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(g_out, d[4], n, cudaMemcpyDeviceToHost));
+    for (auto& p : d) cudaFree(p);
+    return POLAR_OK;
+}

@@ -1,0 +1,106 @@
+// Packed int8x4 primitives for the sm_100a polar decoders.
+//
+// Four int8 LLRs live in one 32-bit word (element i of a stage block = byte i%4 of word i/4).
+// sm_100a has no byte-SIMD ALU except VABSDIFF4.U8, but it does have 16x2 SIMD min/max/add
+// (VIMNMX.{S,U}16x2, VIMNMX3, VIADD.16x2, VIADDMNMX.S16x2 -- the DPX family), so the F/G
+// butterflies below are written against exactly those instructions.  The semantics are the
+// reference's int8 kernels, bit for bit:
+//   f: include/polarcode/decoding/fip_char.h:44-65   (min-sum, |.| clamped to [1,127], 0 is "+")
+//   g: include/polarcode/decoding/fip_char.h:67-73   (saturating b+a / b-a selected by bit sign)
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace polar {
+
+#define POLAR_DEV __device__ __forceinline__
+
+static constexpr uint32_t FULL_MASK = 0xffffffffu;
+
+// prmt.b32 in default mode: selector nibble bit 3 replicates the sign of the selected byte.
+POLAR_DEV uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+}
+
+// bytes 0,2 (resp. 1,3) of x sign-extended into the two 16-bit halves
+POLAR_DEV uint32_t sext_even(uint32_t x) { return prmt(x, 0u, 0xA280u); }
+POLAR_DEV uint32_t sext_odd(uint32_t x) { return prmt(x, 0u, 0xB391u); }
+// low bytes of the four halves of (even, odd) back into one word
+POLAR_DEV uint32_t pack_even_odd(uint32_t e, uint32_t o) { return prmt(e, o, 0x6240u); }
+
+// |x| per byte as unsigned (|-128| = 128): one LOP3 + one VABSDIFF4.U8
+POLAR_DEV uint32_t uabs4(uint32_t x) { return __vabsdiffu4(x ^ 0x80808080u, 0x80808080u); }
+
+// 4 sign bits of the bytes of x -> low nibble (bit k = sign of byte k)
+POLAR_DEV uint32_t sign_nibble(uint32_t x) { return ((x & 0x80808080u) * 0x00204081u) >> 28; }
+
+// low nibble (bit k) -> 0xFF in byte k
+POLAR_DEV uint32_t nibble_to_bytemask(uint32_t nib)
+{
+    return (((nib & 0xFu) * 0x00204081u) & 0x01010101u) * 0xFFu;
+}
+
+// min-sum f on four int8 pairs.  16 ALU ops per 4 elements.
+POLAR_DEV uint32_t f4(uint32_t a, uint32_t b)
+{
+    const uint32_t ma = uabs4(a), mb = uabs4(b); // 0..128
+    // even bytes: clamp(min(ma,mb),1,127) in u16x2
+    uint32_t e = __vimin3_u16x2(ma & 0x00FF00FFu, mb & 0x00FF00FFu, 0x007F007Fu);
+    e = __vmaxu2(e, 0x00010001u);
+    // odd bytes: the 16-bit unsigned order is decided by the high byte first, low-byte garbage is harmless
+    uint32_t o = __vimin3_u16x2(ma, mb, 0x7F007F00u);
+    o = __vmaxu2(o, 0x01000100u);
+    const uint32_t m = (o & 0xFF00FF00u) | e; // e already has clean high bytes
+    // apply sign(a)*sign(b): negate the bytes whose signs differ.  m in [1,127] so (m^0xFF)+1 never carries.
+    const uint32_t sh = ((a ^ b) & 0x80808080u) >> 7;
+    return (m ^ (sh * 0xFFu)) + sh;
+}
+
+// g on four int8 pairs: bit ? sat(b - a) : sat(b + a); `neg` has 0xFF in the bytes whose left bit is 1.
+POLAR_DEV uint32_t g4(uint32_t a, uint32_t b, uint32_t neg)
+{
+    const uint32_t me = prmt(neg, 0u, 0x2200u), mo = prmt(neg, 0u, 0x3311u);
+    uint32_t ae = sext_even(a), ao = sext_odd(a);
+    const uint32_t be = sext_even(b), bo = sext_odd(b);
+    // conditional two's-complement negate in 16 bits (-(-128) = +128 is representable here)
+    ae = __vadd2(ae ^ me, me & 0x00010001u);
+    ao = __vadd2(ao ^ mo, mo & 0x00010001u);
+    uint32_t re = __vmaxs2(__viaddmin_s16x2(be, ae, 0x007F007Fu), 0xFF80FF80u);
+    uint32_t ro = __vmaxs2(__viaddmin_s16x2(bo, ao, 0x007F007Fu), 0xFF80FF80u);
+    return pack_even_odd(re, ro);
+}
+
+// saturating a + b on four int8 pairs (g with an all-zero left block: fip_char.h:112-131; REP accumulate)
+POLAR_DEV uint32_t adds4(uint32_t a, uint32_t b)
+{
+    uint32_t re = __vmaxs2(__viaddmin_s16x2(sext_even(a), sext_even(b), 0x007F007Fu), 0xFF80FF80u);
+    uint32_t ro = __vmaxs2(__viaddmin_s16x2(sext_odd(a), sext_odd(b), 0x007F007Fu), 0xFF80FF80u);
+    return pack_even_odd(re, ro);
+}
+
+// exact sums of min(x,0) / max(x,0) over the four bytes (IDP.4A)
+POLAR_DEV int sum_neg4(uint32_t x, int acc)
+{
+    const uint32_t m = nibble_to_bytemask(sign_nibble(x));
+    return __dp4a((int)(x & m), 0x01010101, acc);
+}
+POLAR_DEV int sum_pos4(uint32_t x, int acc)
+{
+    const uint32_t m = nibble_to_bytemask(sign_nibble(x));
+    return __dp4a((int)(x & ~m), 0x01010101, acc);
+}
+
+// |max(x,-127)| of byte k of w (scl_fip_char.cpp:449,618)
+POLAR_DEV int abs127_byte(uint32_t w, int k)
+{
+    int v = (int)(int8_t)(w >> (8 * k));
+    v = max(v, -127);
+    return abs(v);
+}
+
+POLAR_DEV int sat8i(int v) { return min(max(v, -128), 127); }
+
+} // namespace polar

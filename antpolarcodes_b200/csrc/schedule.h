@@ -1,0 +1,63 @@
+// Flat decoder schedules: the host compiles a frozen set into a linear program of node ops
+// (the reference builds a tree of virtual node objects instead: fastssc_fip_char.cpp:496-569,
+// scl_fip_char.cpp:729-755).  The program travels to the kernel as a __grid_constant__ kernel
+// parameter, i.e. it sits in the constant bank and every warp reads it with uniform loads.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace polar {
+
+enum OpCode : uint32_t {
+    OP_END = 0,
+    // inner-node steps (every decoder kind)
+    OP_F,           // child llr  = f(parent first half, second half)
+    OP_G,           // child llr  = g(parent halves, left bits)
+    OP_COMBINE,     // parent bits = [left ^ right | right]
+    // Fast-SSC shortcuts (L = 1 only)
+    OP_G_R1,        // right child is rate-1: fused g + hard decision + combine (ROneNode)
+    OP_G_0R,        // left child is rate-0: child llr = sat(a + b)              (ZeroRNode)
+    OP_COMBINE_0R,  // parent bits = [right | right]
+    OP_SC_R0, OP_SC_R1, OP_SC_REP, OP_SC_REP2, OP_SC_SPC, OP_SC_ZERO_SPC, OP_SC_ZERO_ONE,
+    // list-decoder leaves
+    OP_SCL_R0, OP_SCL_R1, OP_SCL_REP, OP_SCL_SPC,
+    OP_COUNT
+};
+
+// op word: code[5:0] | stage[9:6] | lgPaths[12:10] | flags[15:13] | pos[31:16]
+//   stage   : log2 of the block the op produces / decodes (children stage for F/G/COMBINE)
+//   lgPaths : log2 of the live path count entering the op (list decoders)
+//   flags   : bit0 = the node is a right child (its bits go to bit array B), bit1 = "long form"
+//   pos     : absolute bit position of the block within the codeword (Fast-SSC, in units of 1 bit)
+static constexpr uint32_t OPF_RIGHT = 1u, OPF_LONG = 2u;
+inline constexpr uint32_t make_op(uint32_t code, uint32_t stage, uint32_t lgPaths, uint32_t flags, uint32_t pos)
+{
+    return code | (stage << 6) | (lgPaths << 10) | (flags << 13) | (pos << 16);
+}
+#define POLAR_OP_CODE(w) ((w) & 63u)
+#define POLAR_OP_STAGE(w) (((w) >> 6) & 15u)
+#define POLAR_OP_LGP(w) (((w) >> 10) & 7u)
+#define POLAR_OP_FLAGS(w) (((w) >> 13) & 7u)
+#define POLAR_OP_POS(w) ((w) >> 16)
+
+static constexpr int MAX_OPS = 3072;
+struct Schedule {
+    uint32_t ops[MAX_OPS];
+};
+
+struct ScheduleStats {
+    long count[OP_COUNT] = {};
+    long size[OP_COUNT] = {};   // sum of block sizes (elements) per op kind
+    double laneOps = 0;         // algorithmic lane-ops per frame (SURVEY 8d weights)
+    double pathElems = 0;       // sum over F/G/C ops of h * paths
+};
+
+// tree flavours (node-selection rules differ per reference decoder)
+enum TreeKind { TREE_FASTSSC_I8 = 0, TREE_FASTSSC_F32 = 1, TREE_SCL_I8 = 2, TREE_SCL_F32 = 3 };
+
+// frozen: sorted ascending frozen indices.  listSize must be a power of two <= 32.
+// Returns false (and sets err) if the code cannot be scheduled.
+bool compile_schedule(TreeKind kind, int N, const std::vector<uint32_t>& frozen, int listSize,
+                      std::vector<uint32_t>& ops, ScheduleStats& stats, const char** err);
+
+} // namespace polar

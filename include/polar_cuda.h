@@ -1,0 +1,105 @@
+/* libpolar_cuda -- C ABI of the B200 (sm_100a) batched polar-code engine.
+ *
+ * This is the drop-in boundary: the reference (david13pod/antPolarCodes) has no FFI of its own,
+ * its hot path sits behind three C++ interfaces.  Each entry point below names the reference
+ * interface it replaces; the C++ subclasses in antpolarcodes_b200/csrc/host/ (FastSscCudaChar,
+ * SclCudaChar, ButterflyCudaPacked, ...) and the Python mirror call nothing but these.
+ *
+ *   Encoder::encode_vector(void* info, void* code)          src/polarcode/encoding/encoder.cpp:79-90
+ *   Decoder::decode_vector(const char* or float* llr, void*) src/polarcode/decoding/decoder.cpp:154-181
+ *   Detector::generate / check                              include/polarcode/errordetection/errordetector.h:24-70
+ *   Construction::frozen_bits(N, K, dSNR, type)             src/polarcode/construction/constructor.cpp:41-63
+ *
+ * Conventions (same as the reference): LLR >= 0 <=> bit 0; every packed buffer is MSB first
+ * (bit i in byte i/8 at mask 0x80 >> (i%8)); K = N - |frozen| includes the CRC bits; frozen
+ * indices are sorted ascending.  All functions return 0 on success or a negative POLAR_E_* code;
+ * polar_cuda_last_error() gives the message of the calling thread's last failure.
+ */
+#ifndef POLAR_CUDA_H
+#define POLAR_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct polar_code* polar_code_t;
+
+enum polar_kind {
+    POLAR_KIND_ENC = 0,         /* Encoding::ButterflyFipPacked   butterfly_fip_packed.h:25   */
+    POLAR_KIND_FASTSSC_I8 = 1,  /* Decoding::FastSscFipChar       fastssc_fip_char.h:298      */
+    POLAR_KIND_FASTSSC_F32 = 2, /* Decoding::FastSscAvxFloat      fastssc_avx_float.h:283     */
+    POLAR_KIND_SCL_I8 = 3,      /* Decoding::SclFipChar           scl_fip_char.h:391          */
+    POLAR_KIND_SCL_F32 = 4      /* Decoding::SclAvxFloat          scl_avx_float.h:407         */
+};
+
+enum polar_mem { POLAR_MEM_HOST = 0, POLAR_MEM_DEVICE = 1 };
+enum polar_llr { POLAR_LLR_I8 = 0, POLAR_LLR_F32 = 1 };
+
+enum polar_error {
+    POLAR_OK = 0,
+    POLAR_E_ARG = -1,      /* invalid argument (std::invalid_argument in the C++ layer) */
+    POLAR_E_UNSUPPORTED = -2,
+    POLAR_E_CUDA = -3,     /* CUDA runtime failure (std::runtime_error) */
+    POLAR_E_NOMEM = -4
+};
+
+const char* polar_cuda_last_error(void);
+int polar_cuda_device_count(void);
+int polar_cuda_version(void);
+
+/* Compile a code for one device: builds the Fast-SSC / SCL node schedule, the info-position
+ * LUT and the CRC syndrome table and uploads them.  Replaces the decoder / encoder constructors
+ * (blockLength, [listSize,] frozenBits) + setSystematic + setErrorDetection.
+ *   listSize : power of two in [1,32] (ignored for ENC / FASTSSC kinds)
+ *   crcBits  : 0 (Dummy detector), 8, 16 or 32 (ErrorDetection::create(bits,"crc")) */
+int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, int nFrozen, int listSize,
+                           int systematic, int crcBits, polar_code_t* out);
+int polar_cuda_code_destroy(polar_code_t code);
+
+/* Decoder::decode_vector over nFrames independent frames.
+ *   llr      : nFrames x N LLRs, int8 or float (float into an int8 decoder is quantised like
+ *              CharContainer::insertLlr, bitcontainer.cpp:468-516)
+ *   info_out : nFrames x ceil(K/8) bytes;  ok_out : nFrames bytes (the bool decode() returns)
+ *   mem      : where llr / info_out / ok_out live (all three the same)
+ *   stream   : cudaStream_t (0 = default stream).  HOST buffers are copied synchronously;
+ *              DEVICE buffers are processed asynchronously on the stream. */
+int polar_cuda_decode_batch(polar_code_t code, const void* llr, int llrType, int mem, size_t nFrames,
+                            uint8_t* info_out, uint8_t* ok_out, void* stream);
+
+/* Encoder::encode_vector over nFrames frames.  info: nFrames x K/8 bytes; like the reference the
+ * trailing CRC bytes of every info block are overwritten in place.  code_out: nFrames x N/8. */
+int polar_cuda_encode_batch(polar_code_t code, uint8_t* info, int mem, size_t nFrames, uint8_t* code_out,
+                            void* stream);
+
+/* Detector::generate / Detector::check on the host (same arithmetic the kernels fuse). */
+int polar_cuda_crc_generate(int crcBits, uint8_t* data, int bytes);
+int polar_cuda_crc_check(int crcBits, const uint8_t* data, int bytes); /* 1 = pass, 0 = fail */
+
+/* Construction::frozen_bits: type "BB" (Bhattacharyya), "BE" (beta expansion) or "5G".
+ * Writes N-K sorted indices to out; returns the count or a negative error. */
+int polar_cuda_frozen_bits(int N, int K, float designSnr, const char* type, uint32_t* out);
+
+/* Introspection for tests, bench and the roofline. */
+struct polar_code_info {
+    int kind, N, K, listSize, systematic, crcBits;
+    int nOps;                 /* schedule length */
+    int warpsPerBlock, blocksPerSM, smemPerWarp, gridBlocks;
+    double laneOpsPerFrame;   /* algorithmic ALU lane-ops per frame */
+    double bytesPerFrame;     /* algorithmic HBM bytes per frame */
+    long opCount[32], opSize[32]; /* indexed by polar::OpCode */
+};
+int polar_cuda_code_info(polar_code_t code, struct polar_code_info* info);
+int polar_cuda_code_schedule(polar_code_t code, uint32_t* ops, int maxOps); /* returns op count */
+/* number of kernel launches issued through this handle so far (bench's gpu_launches) */
+long polar_cuda_code_launches(polar_code_t code);
+
+/* Primitive self-test hooks (golden vectors of decodingtest.cpp:504-737): element-wise F / G over
+ * n int8 values on the device, through the very device functions the decoders use. */
+int polar_cuda_test_fg(const int8_t* a, const int8_t* b, const int8_t* bits, int n, int8_t* f_out,
+                       int8_t* g_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
