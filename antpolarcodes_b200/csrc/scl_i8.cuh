@@ -480,6 +480,7 @@ POLAR_DEV void warp_polar_transform(uint32_t* x, int N, int lane)
     const int W = N >> 5;
     for (int w = lane; w < max(W, 1); w += 32) {
         uint32_t v = x[w];
+        if (N < 32) v &= (1u << N) - 1u; // bits beyond a short block are not ours
         v ^= (v >> 1) & 0x55555555u;
         v ^= (v >> 2) & 0x33333333u;
         v ^= (v >> 4) & 0x0F0F0F0Fu;

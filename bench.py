@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""bench.py -- info-bit Gbit/s of the batched polar decoders on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload scl8|fastssc|scl32]
+
+A "step" is one decode pass over one batch of synthetic noisy codewords (AWGN/BPSK, Eb/N0 = 2 dB,
+int8 LLRs).  Headline workload = BASELINE configs[2]: SCL L=8 + CRC16, N=1024 K=512,
+5G reliability-table frozen set.  `value` is timed with the LLRs resident in HBM; `e2e` is the same
+decode through the public API with pinned HOST buffers (H2D of the LLRs and D2H of the decoded bytes
+inside the timed region).  Rank 0 also times the unmodified reference (oracle/_ref) on the host cores
+on a bounded sample (`cpu_baseline`); `--impl reference` times only that.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    # name: (N, K, construction, L, crc, frames per step per GPU, e2e frames per step)
+    "scl8": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 19, e2e_frames=1 << 18,
+                 label="SCL L=8 + CRC16, N=1024 K=512, 5G frozen set, int8 LLR, Eb/N0=2dB"),
+    "fastssc": dict(N=1024, K=512, ctype="BB", L=1, crc=0, frames=1 << 20, e2e_frames=1 << 19,
+                    label="Fast-SSC int8, N=1024 K=512, BB frozen set, Eb/N0=2dB"),
+    "scl32": dict(N=2048, K=1024, ctype="BB", L=32, crc=32, frames=1 << 16, e2e_frames=1 << 16,
+                  label="SCL L=32 + CRC32, N=2048 K=1024, BB frozen set, int8 LLR, Eb/N0=2dB"),
+}
+METRIC = "info-bit Gbps (N=1024 K=512, SCL L=8+CRC16)"
+EBN0_DB = 2.0
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d.get("hbm_gbs", 6650.0)), float(d.get("sm_max_mhz", 1965.0)), "measured"
+    return 6650.0, 1965.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_llrs_on_device(torch, ap, wl, frozen, frames, seed, device):
+    """payload -> CRC -> (our) encoder -> BPSK -> AWGN -> int8 LLR = clamp(rne(10 y)); all on the device."""
+    N, K, crc = wl["N"], wl["K"], wl["crc"]
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    enc = ap.PolarEncoder(N, frozen, device=device.index)
+    enc.setSystematic(True)
+    enc.setErrorDetection(crc)
+    llr = torch.empty((frames, N), dtype=torch.int8, device=device)
+    info_all = torch.empty((frames, K // 8), dtype=torch.uint8, device=device)
+    sigma = 1.0 / np.sqrt(2.0 * (K / N) * 10.0 ** (EBN0_DB / 10.0))
+    shifts = torch.arange(7, -1, -1, device=device, dtype=torch.uint8)
+    chunk = 1 << 16
+    for lo in range(0, frames, chunk):
+        n = min(chunk, frames - lo)
+        info = torch.randint(0, 256, (n, K // 8), dtype=torch.uint8, device=device, generator=g)
+        code = enc.encode_batch(info)
+        torch.cuda.synchronize(device)
+        bits = ((code.unsqueeze(-1) >> shifts) & 1).reshape(n, N).to(torch.float32)
+        y = (1.0 - 2.0 * bits) + sigma * torch.randn((n, N), device=device, generator=g)
+        llr[lo:lo + n] = torch.clamp(torch.round(10.0 * y), -128, 127).to(torch.int8)
+        info_all[lo:lo + n] = info
+    return llr, info_all
+
+
+def ref_threads():
+    return os.cpu_count() or 1
+
+
+def time_reference(wl, frozen, llr_host, seconds_target, threads):
+    """The unmodified reference decoders (oracle/_ref) on the host cores, one decoder object per thread."""
+    from polar_testlib import KIND_FASTSSC_I8, KIND_SCL_I8, ref_decode
+    kind = KIND_SCL_I8 if wl["L"] > 1 else KIND_FASTSSC_I8
+    n = llr_host.shape[0]
+    _, _, t1 = ref_decode(kind, wl["N"], frozen, llr_host, wl["L"], 1, wl["crc"], threads, 1)
+    rep = max(1, int(seconds_target / max(t1, 1e-6)))
+    _, _, t = ref_decode(kind, wl["N"], frozen, llr_host, wl["L"], 1, wl["crc"], threads, rep)
+    return n * rep * wl["K"] / t / 1e9, n * rep, t
+
+
+def run_reference_arm(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from polar_testlib import awgn_llrs, have_ref, ref_frozen_bits
+    import antpolarcodes_b200 as ap
+    frozen = ap.frozen_bits(wl["N"], wl["K"], 0.0, wl["ctype"])
+    threads = ref_threads()
+    sample = max(4 * threads, 1024)
+    llr, _ = awgn_llrs(wl["N"], frozen, sample, EBN0_DB, wl["crc"])
+    if not have_ref():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libpolar_ref.so not present"}))
+        return
+    per_step = 20.0 / max(args.steps + args.warmup, 1)
+    vals, ms = [], []
+    for s in range(args.warmup + args.steps):
+        v, nfr, t = time_reference(wl, frozen, llr, min(per_step, 4.0), threads)
+        if s >= args.warmup:
+            vals.append(v)
+            ms.append(t * 1e3)
+    v = float(np.mean(vals))
+    line = {"metric": METRIC if args.workload == "scl8" else wl["label"], "value": v, "unit": "Gbit/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(ms)), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic", "impl": "reference",
+            "config": {"workload": wl["label"], "frames_per_step": "bounded sample (%d frames x repeats)" % sample},
+            "cpu_baseline": {"value": v, "unit": "Gbit/s", "cores": threads, "kind": "reference",
+                             "sample": "%d AWGN frames cycled for ~%.1f s per step, one SclFipChar/FastSscFipChar object per thread" % (sample, min(per_step, 4.0))},
+            "e2e": {"value": v, "unit": "Gbit/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_ours(args, wl):
+    import torch
+    import torch.distributed as dist
+    import antpolarcodes_b200 as ap
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    N, K, L, crc = wl["N"], wl["K"], wl["L"], wl["crc"]
+    frames = args.frames or wl["frames"]
+    e2e_frames = min(args.e2e_frames or wl["e2e_frames"], frames)
+    frozen = ap.frozen_bits(N, K, 0.0, wl["ctype"])
+    dec = ap.PolarDecoder(N, L, frozen, "char", device=local)
+    dec.setErrorDetection(crc)
+    dec.setSystematic(True)
+    info = dec.info()
+
+    # frames are sharded by rank: every rank decodes its own `frames` frames (weak scaling), no
+    # data-path collective
+    llr, sent = make_llrs_on_device(torch, ap, wl, frozen, frames, 0xB200 + rank, device)
+    out = torch.empty((frames, K // 8), dtype=torch.uint8, device=device)
+    ok = torch.empty((frames,), dtype=torch.uint8, device=device)
+    stream = torch.cuda.current_stream(device)
+    sp = stream.cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    def step():
+        dec.decode_batch(llr, out, ok, stream=sp)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    launches0 = dec._get().launches()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    barrier()
+    ev[0].record(stream)
+    for s in range(args.steps):
+        step()
+        ev[s + 1].record(stream)
+    barrier()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    kernel_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    launches = dec._get().launches() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+
+    # correctness of what was timed: frame errors vs the transmitted payload + verdicts
+    frame_err = int((out != sent).any(dim=1).sum().item())
+    ok_count = int(ok.sum().item())
+
+    # e2e: pinned host LLRs -> C ABI with HOST pointers (H2D + kernel + D2H inside the timed region)
+    h_llr = torch.empty((e2e_frames, N), dtype=torch.int8).pin_memory()
+    h_llr.copy_(llr[:e2e_frames])
+    h_out = torch.empty((e2e_frames, K // 8), dtype=torch.uint8).pin_memory()
+    h_ok = torch.empty((e2e_frames,), dtype=torch.uint8).pin_memory()
+    for _ in range(max(1, min(args.warmup, 3))):
+        dec.decode_batch(h_llr, h_out, h_ok, stream=sp)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        dec.decode_batch(h_llr, h_out, h_ok, stream=sp)
+    e1.record(stream)
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    e2e_match = bool((h_out == out[:e2e_frames].cpu()).all().item())
+
+    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=device)
+    errs = torch.tensor([frame_err, ok_count, frames], dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(errs, op=dist.ReduceOp.SUM)  # the BLER counter allreduce
+    total_ms, e2e_ms = float(t[0].item()), float(t[1].item())
+
+    if rank == 0:
+        hbm_peak, sm_max, which = peaks()
+        value = world * frames * args.steps * K / (total_ms * 1e-3) / 1e9
+        e2e_val = world * e2e_frames * args.steps * K / (e2e_ms * 1e-3) / 1e9
+        k_ms = float(np.mean(kernel_ms))
+        fps = frames / (k_ms * 1e-3)
+        sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
+        alu_peak_max = 148 * 128 * sm_max * 1e6 / 1e12     # T lane-ops/s at max clock
+        alu_peak_run = 148 * 128 * sm_mhz * 1e6 / 1e12
+        alu = fps * info.laneOpsPerFrame / 1e12
+        hbm = fps * info.bytesPerFrame / 1e9
+        alu_bound = (info.laneOpsPerFrame / (alu_peak_max * 1e12)) > (info.bytesPerFrame / (hbm_peak * 1e9))
+        roof = {"bound": "alu_issue" if alu_bound else "hbm",
+                "achieved": alu if alu_bound else hbm, "peak": alu_peak_max if alu_bound else hbm_peak,
+                "unit": "Tlane-op/s" if alu_bound else "GB/s",
+                "frac": (alu / alu_peak_max) if alu_bound else hbm / hbm_peak, "traffic": None,
+                "peak_source": which + (" sm_max_mhz x 148 SM x 128 lanes" if alu_bound else " hbm copy"),
+                "frac_at_run_clock": alu / alu_peak_run,
+                "alu": {"lane_ops_per_frame": info.laneOpsPerFrame, "achieved_T": alu, "peak_T": alu_peak_max},
+                "hbm": {"bytes_per_frame": info.bytesPerFrame, "achieved_GBs": hbm, "peak_GBs": hbm_peak,
+                        "frac": hbm / hbm_peak},
+                "kernel_ms": k_ms, "frames_per_launch": frames}
+        cpu = None
+        try:
+            from polar_testlib import have_ref
+            if have_ref():
+                th = ref_threads()
+                sample = max(4 * th, 1024)
+                v, nfr, tt = time_reference(wl, frozen, np.ascontiguousarray(h_llr[:sample].numpy()), 12.0, th)
+                cpu = {"value": v, "unit": "Gbit/s", "cores": th, "kind": "reference",
+                       "sample": "%d frames of this workload, decoded %d times in %.1f s by %d threads (one reference decoder object each)" % (sample, nfr // sample, tt, th)}
+        except Exception as e:  # the baseline is a reported number, never a reason to lose the bench line
+            cpu = {"value": None, "unit": "Gbit/s", "cores": 0, "kind": "reference", "sample": "failed: %r" % (e,)}
+        line = {"metric": METRIC if args.workload == "scl8" else wl["label"], "value": value, "unit": "Gbit/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+                "config": {"workload": wl["label"], "frames_per_step_per_gpu": frames, "e2e_frames_per_step_per_gpu": e2e_frames,
+                           "list_size": L, "crc_bits": crc, "cache": "inputs larger than L2 (%d MiB of LLRs per step)" % (frames * N >> 20),
+                           "warps_per_block": info.warpsPerBlock, "blocks_per_sm": info.blocksPerSM,
+                           "smem_per_warp": info.smemPerWarp, "schedule_ops": info.nOps, "parallelism": "frames sharded x%d" % world},
+                "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": e2e_frames * N,
+                        "d2h_bytes_per_step": e2e_frames * (K // 8 + 1), "matches_device_run": e2e_match},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+                "check": {"frames": int(errs[2].item()), "frame_errors_vs_sent": int(errs[0].item()),
+                          "detector_pass": int(errs[1].item())}}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap_ = argparse.ArgumentParser()
+    ap_.add_argument("--gpus", type=int, default=1)
+    ap_.add_argument("--steps", type=int, default=10)
+    ap_.add_argument("--warmup", type=int, default=3)
+    ap_.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap_.add_argument("--workload", default="scl8", choices=sorted(WORKLOADS))
+    ap_.add_argument("--frames", type=int, default=0)
+    ap_.add_argument("--e2e-frames", type=int, default=0, dest="e2e_frames")
+    args = ap_.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

@@ -88,7 +88,10 @@ extern "C" void oracle_quantize(const float* llr, int8_t* out, int N)
     for (int i = 0; i < N; ++i) {
         float x = llr[i];
         if (N >= 8) {
-            if (std::isnan(x)) { out[i] = (N >= 32) ? -128 : (int8_t)-128; continue; }
+            // N >= 32: cvtps_epi32 first (NaN and |x| >= 2^31 give INT_MIN, the "integer indefinite"),
+            // then signed saturation -> -128.  8 <= N < 32: clamp first (max_ps/min_ps send NaN to -128).
+            if (std::isnan(x)) { out[i] = -128; continue; }
+            if (N >= 32 && x >= 2147483648.0f) { out[i] = -128; continue; }
             float c = x < -128.f ? -128.f : (x > 127.f ? 127.f : x);
             out[i] = (int8_t)std::nearbyintf(c); // default rounding mode = nearest-even
         } else {

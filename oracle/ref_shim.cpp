@@ -12,6 +12,7 @@
 //   PolarCode::Decoding::SclAvxFloat          (src/polarcode/decoding/scl_avx_float.cpp:696-750)
 //   PolarCode::ErrorDetection::create         (src/polarcode/errordetection/errordetector.cpp:23-67)
 // No reference source is copied here; this file only calls the public API.
+#include <polarcode/bitcontainer.h>
 #include <polarcode/construction/constructor.h>
 #include <polarcode/decoding/decoder.h>
 #include <polarcode/decoding/fastssc_avx_float.h>
@@ -180,6 +181,14 @@ int polar_ref_crc(int crcBits, uint8_t* data, int bytes, int mode)
     } catch (...) {
         return -1;
     }
+}
+
+// CharContainer::insertLlr(const float*) (bitcontainer.cpp:505-516): the float -> int8 quantiser
+void polar_ref_quantize(const float* llr, int8_t* out, int N)
+{
+    CharContainer c(N);
+    c.insertLlr(llr);
+    c.getSoftBits(out);
 }
 
 int polar_ref_hw_threads() { return (int)std::thread::hardware_concurrency(); }
