@@ -24,7 +24,7 @@ EXPORTS = [
     "polar_cuda_last_error", "polar_cuda_device_count", "polar_cuda_version", "polar_cuda_code_create",
     "polar_cuda_code_destroy", "polar_cuda_decode_batch", "polar_cuda_encode_batch",
     "polar_cuda_crc_generate", "polar_cuda_crc_check", "polar_cuda_frozen_bits", "polar_cuda_code_info",
-    "polar_cuda_code_schedule", "polar_cuda_code_launches", "polar_cuda_test_fg",
+    "polar_cuda_code_schedule", "polar_cuda_code_launches", "polar_cuda_test_fg", "polar_cuda_schedule_stats",
 ]
 
 

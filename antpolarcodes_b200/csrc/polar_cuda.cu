@@ -389,6 +389,28 @@ int polar_cuda_code_schedule(polar_code_t c, uint32_t* ops, int maxOps)
 
 long polar_cuda_code_launches(polar_code_t c) { return c ? c->launches : 0; }
 
+int polar_cuda_schedule_stats(int kind, int N, const uint32_t* frozen, int nFrozen, int listSize, long* counts,
+                              long* sizes, double* laneOpsPerFrame)
+{
+    if (kind != POLAR_KIND_FASTSSC_I8 && kind != POLAR_KIND_SCL_I8 && kind != POLAR_KIND_FASTSSC_F32 &&
+        kind != POLAR_KIND_SCL_F32)
+        return fail(POLAR_E_ARG, "kind has no schedule");
+    if (nFrozen < 0 || (nFrozen && !frozen)) return fail(POLAR_E_ARG, "bad frozen set");
+    const TreeKind tk = kind == POLAR_KIND_FASTSSC_I8 ? TREE_FASTSSC_I8 : kind == POLAR_KIND_SCL_I8 ? TREE_SCL_I8
+                      : kind == POLAR_KIND_FASTSSC_F32 ? TREE_FASTSSC_F32 : TREE_SCL_F32;
+    std::vector<uint32_t> f(frozen, frozen + nFrozen), ops;
+    ScheduleStats st;
+    const char* err = nullptr;
+    const bool isScl = (tk == TREE_SCL_I8 || tk == TREE_SCL_F32);
+    if (!compile_schedule(tk, N, f, isScl ? listSize : 1, ops, st, &err)) return fail(POLAR_E_ARG, err);
+    for (int i = 0; i < 32; ++i) {
+        if (counts) counts[i] = i < (int)OP_COUNT ? st.count[i] : 0;
+        if (sizes) sizes[i] = i < (int)OP_COUNT ? st.size[i] : 0;
+    }
+    if (laneOpsPerFrame) *laneOpsPerFrame = st.laneOps;
+    return (int)ops.size();
+}
+
 } // extern "C"
 
 // ---------------------------------------------------------------- primitive self-test

@@ -91,6 +91,11 @@ struct polar_code_info {
 };
 int polar_cuda_code_info(polar_code_t code, struct polar_code_info* info);
 int polar_cuda_code_schedule(polar_code_t code, uint32_t* ops, int maxOps); /* returns op count */
+/* Pure-host schedule compiler (no device needed): node histogram of the program the kernels would run,
+ * i.e. of the tree createDecoder() builds (fastssc_fip_char.cpp:496-569, scl_fip_char.cpp:729-755).
+ * counts / sizes: 32 entries indexed by polar::OpCode; returns the op count or a negative error. */
+int polar_cuda_schedule_stats(int kind, int N, const uint32_t* frozen, int nFrozen, int listSize, long* counts,
+                              long* sizes, double* laneOpsPerFrame);
 /* number of kernel launches issued through this handle so far (bench's gpu_launches) */
 long polar_cuda_code_launches(polar_code_t code);
 
