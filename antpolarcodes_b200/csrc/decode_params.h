@@ -5,23 +5,28 @@
 namespace polar {
 
 struct DecodeParams {
-    const void* llr;          // nFrames x N, int8 or float
+    const void* llr;          // nFrames x N int8 (float inputs are quantised by a pre-pass)
     uint8_t* out;             // nFrames x kb
     uint8_t* ok;              // nFrames
     const uint16_t* infoPos;  // K code positions of the information bits, ascending
-    const uint32_t* crcTab;   // K syndrome contributions (see crc_tables.h)
+    const uint32_t* crcTab;   // K syndrome contributions (see crc_host.h)
+    uint32_t* spill;          // L2-resident scratch for the top LLR stage (list decoders), or null
     long long nFrames;
     uint32_t crcInit;         // syndrome of the all-zero info block
     int N, lgN, K, kb;        // kb = ceil(K/8)
-    int crcBits, systematic, llrIsFloat;
+    int crcBits, systematic;
     int listSize;
-    // shared-memory geometry per warp, in 32-bit words
-    int chanW;                // N/4
-    int slotW;                // llr slot stride
-    int bitW;                 // words of one bit array (all stages)
-    int bitSlotW;             // bit slot stride (two arrays + pad)
-    int scratchW;
+    // shared-memory geometry, in 32-bit words
+    int slotW;                // list decoders: LLR slot stride (one path, stages below spillStage)
+    int bitBW;                // list decoders: offset of bit array "B" inside a bit slot
+    int bitSlotW;             // list decoders: bit slot stride (arrays A and B)
+    int frameW;               // list decoders: stride between the frames of one warp
+    int scratchW;             // per-warp scratch
     int warpW;                // total words per warp
+    int spillStage;           // LLR stage kept in `spill` instead of shared memory (lgN = none)
+    int spillWarpW;           // words of `spill` per resident warp
+    // Fast-SSC (one frame per thread): rows of 32 words
+    int llrRows, bitRows, tileRow, outRow, chanRow;
 };
 
 // word offset of stage s inside an llr slot (stage s block = 2^s int8, at least one word)

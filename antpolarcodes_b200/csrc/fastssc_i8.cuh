@@ -1,145 +1,276 @@
-// Fast-SSC int8 decoder for sm_100a: one frame per warp, the whole node program in the constant bank.
+// Fast-SSC int8 decoder for sm_100a: one frame per THREAD, 32 frames per warp in lockstep, the whole node
+// program in the constant bank.
 //
 // Restates PolarCode::Decoding::FastSscFipChar (src/polarcode/decoding/fastssc_fip_char.cpp) bit-exactly,
 // including the stepwise-saturating REP sums (avxconvenience.h:92-101,202-210), the "first minimum,
 // threshold 127" SPC search (:274-319, avxconvenience.cpp:13-56) and the arithmetic-negate flip that
 // silently fails for 0 and -128 (:301).  Partial sums are packed sign bits at absolute code positions.
+//
+// B200 mapping: the schedule is the same for every frame, so the 32 lanes of a warp never diverge: each
+// lane walks its own frame through the node program.  A lane's data sits in shared memory as "rows" of 32
+// words (word r of lane l at [r][l]): every access is bank-conflict free whatever the row index.  The channel
+// LLRs are never staged: the two top-level steps pull them through a padded 32x33 transpose tile (coalesced
+// 128-byte row reads), the second time out of L2.  Decoded bytes leave through a shared-memory image of the
+// warp's 32 output rows, i.e. as fully coalesced stores.
 #pragma once
+#include "decode_common.cuh"
 #include "decode_params.h"
 #include "primitives.cuh"
 #include "schedule.h"
-#include "scl_i8.cuh" // load_channel_llrs / gather_info_and_syndrome / store_info / warp_polar_transform
 
 namespace polar {
 
 struct ScCtx {
-    uint32_t* chan;
-    uint32_t* llr;
-    uint32_t* bits;
-    uint32_t* scr;
-    int lane, lgN;
+    uint32_t* sm;          // this warp's shared memory
+    const uint32_t* chan;  // channel rows (global), N/4 words per frame
+    long long frame0, lastFrame;
+    int lane, lgN, nw;     // nw = N/4
+    int bitRow, tileRow, chanRow;
 };
 
-POLAR_DEV const uint32_t* sc_llr(const ScCtx& c, int s) { return s == c.lgN ? c.chan : c.llr + llr_woff(s); }
+#define SC_ROW(c, row) (c).sm[((row) << 5) + (c).lane]
 
-POLAR_DEV uint32_t or8(uint32_t v)
-{
-    v |= __shfl_xor_sync(FULL_MASK, v, 1);
-    v |= __shfl_xor_sync(FULL_MASK, v, 2);
-    v |= __shfl_xor_sync(FULL_MASK, v, 4);
-    return v;
-}
+// LLR block of stage s: rows of the stage buffers, or the staged channel (degenerate one-leaf codes)
+POLAR_DEV int sc_llr_row(const ScCtx& c, int s) { return s == c.lgN ? c.chanRow : llr_woff(s); }
 
-// Write (or XOR) the sign bits of a block of n = 2^s values into bits[pos .. pos+n).  getWord(w) returns
-// LLR word w of the block.  dup: also copy to [pos+n, pos+2n) (Zero-SPC / Zero-One leaves).
-template <class GetWord>
-POLAR_DEV void sc_put_signs(ScCtx& c, int s, int pos, bool doXor, bool dup, uint32_t flipBit, bool doFlip,
-                            GetWord getWord)
+// Source views of a parent block split in halves a = [0, words), b = [words, 2*words)
+struct ScRows { // both halves in the lane's own rows
+    const ScCtx& c;
+    int row, words;
+    POLAR_DEV uint32_t a(int w) const { return SC_ROW(c, row + w); }
+    POLAR_DEV uint32_t b(int w) const { return SC_ROW(c, row + words + w); }
+};
+struct ScTiles { // a chunk [w0, w0+cw) of both halves in the transpose tiles
+    const uint32_t* ta;
+    const uint32_t* tb;
+    int w0;
+    POLAR_DEV uint32_t a(int w) const { return ta[w - w0]; }
+    POLAR_DEV uint32_t b(int w) const { return tb[w - w0]; }
+};
+
+// tile[r*33 + i] = channel word (w0 + i) of frame (frame0 + r), i < cw <= 32
+POLAR_DEV void sc_load_tile(const ScCtx& c, uint32_t* tile, int w0, int cw)
 {
-    const int lane = c.lane;
-    if (s >= 5) {
-        const int words = 1 << (s - 2);
-        for (int w0 = 0; w0 < words; w0 += 32) {
-            const int w = w0 + lane; // words is a multiple of 8, w0 of 32: groups of 8 lanes share a bit word
-            uint32_t v = (w < words) ? sign_nibble(getWord(w)) << (4 * (lane & 7)) : 0u;
-            v = or8(v);
-            if ((lane & 7) == 0 && w < words) {
-                const int bw = w >> 3;
-                if (doFlip && (int)(flipBit >> 5) == bw) v ^= 1u << (flipBit & 31u);
-                uint32_t* d = c.bits + (pos >> 5) + bw;
-                if (doXor) *d ^= v; else *d = v;
-                if (dup) d[1 << (s - 5)] = v;
-            }
-        }
-    } else {
-        const int n = 1 << s, words = n >= 4 ? n >> 2 : 1;
-        uint32_t v = 0;
-        if (lane < words) {
-            uint32_t nib = sign_nibble(getWord(lane));
-            if (n < 4) nib &= (1u << n) - 1u;
-            v = nib << (4 * lane);
-        }
-        v = or8(v);
-        if (lane == 0) {
-            if (doFlip) v ^= 1u << flipBit;
-            const uint32_t mask = (1u << n) - 1u; // n <= 16
-            uint32_t* d = c.bits + (pos >> 5);
-            const int sh = pos & 31;
-            uint32_t wd = *d;
-            if (doXor) wd ^= v << sh; else wd = (wd & ~(mask << sh)) | (v << sh);
-            if (dup) wd = (wd & ~(mask << (sh + n))) | (v << (sh + n));
-            *d = wd;
+    if (c.lane < cw) {
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) {
+            const long long f = min(c.frame0 + r, c.lastFrame);
+            tile[r * 33 + c.lane] = __ldg(c.chan + f * c.nw + w0 + c.lane);
         }
     }
 }
 
-// bits[pos .. pos+n) = value (0 or 1) for every position; pattern word for REP2
-POLAR_DEV void sc_fill_bits(ScCtx& c, int s, int pos, uint32_t pattern)
+// ---- per-thread steps over the word range [wb, we) of a block of `words` words per half
+template <class Src>
+POLAR_DEV void sc_f_range(ScCtx& c, const Src& src, int dstRow, int wb, int we)
+{
+    int w = wb;
+    for (; w + 3 < we; w += 4) {
+        const uint32_t a0 = src.a(w), a1 = src.a(w + 1), a2 = src.a(w + 2), a3 = src.a(w + 3);
+        const uint32_t b0 = src.b(w), b1 = src.b(w + 1), b2 = src.b(w + 2), b3 = src.b(w + 3);
+        SC_ROW(c, dstRow + w) = f4(a0, b0);
+        SC_ROW(c, dstRow + w + 1) = f4(a1, b1);
+        SC_ROW(c, dstRow + w + 2) = f4(a2, b2);
+        SC_ROW(c, dstRow + w + 3) = f4(a3, b3);
+    }
+    for (; w < we; ++w) SC_ROW(c, dstRow + w) = f4(src.a(w), src.b(w));
+}
+
+template <class Src>
+POLAR_DEV void sc_adds_range(ScCtx& c, const Src& src, int dstRow, int wb, int we)
+{
+    int w = wb;
+    for (; w + 3 < we; w += 4) {
+        const uint32_t a0 = src.a(w), a1 = src.a(w + 1), a2 = src.a(w + 2), a3 = src.a(w + 3);
+        const uint32_t b0 = src.b(w), b1 = src.b(w + 1), b2 = src.b(w + 2), b3 = src.b(w + 3);
+        SC_ROW(c, dstRow + w) = adds4(a0, b0);
+        SC_ROW(c, dstRow + w + 1) = adds4(a1, b1);
+        SC_ROW(c, dstRow + w + 2) = adds4(a2, b2);
+        SC_ROW(c, dstRow + w + 3) = adds4(a3, b3);
+    }
+    for (; w < we; ++w) SC_ROW(c, dstRow + w) = adds4(src.a(w), src.b(w));
+}
+
+// left bits of the block start at absolute bit position pos
+template <class Src>
+POLAR_DEV void sc_g_range(ScCtx& c, const Src& src, int dstRow, int pos, int wb, int we)
+{
+    int w = wb;
+    if (((we - wb) & 7) == 0 && (pos & 31) == 0) { // whole bit words: one load per 8 LLR words
+        for (; w < we; w += 8) {
+            const uint32_t lw = SC_ROW(c, c.bitRow + ((pos + 4 * w) >> 5));
+            uint32_t a[8], b[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
+#pragma unroll
+            for (int t = 0; t < 8; ++t) SC_ROW(c, dstRow + w + t) = g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t)));
+        }
+        return;
+    }
+    for (; w < we; ++w) {
+        const int bp = pos + 4 * w;
+        const uint32_t nib = SC_ROW(c, c.bitRow + (bp >> 5)) >> (bp & 31);
+        SC_ROW(c, dstRow + w) = g4(src.a(w), src.b(w), nibble_to_bytemask(nib));
+    }
+}
+
+// ROneNode (fastssc_fip_char.cpp:436-474): right = g(a, b, left bits); right bits = sign(right);
+// left bits ^= right bits.  h = 2^s >= 32 elements: whole bit words, range in LLR words (multiple of 8).
+template <class Src>
+POLAR_DEV void sc_g_r1_range(ScCtx& c, const Src& src, int s, int pos, int wb, int we)
+{
+    const int hw = 1 << (s - 5);
+    for (int w = wb; w < we; w += 8) {
+        const int j = w >> 3;
+        const uint32_t lw = SC_ROW(c, c.bitRow + (pos >> 5) + j);
+        uint32_t a[8], b[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
+        uint32_t rw = 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) rw |= sign_nibble(g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t)))) << (4 * t);
+        SC_ROW(c, c.bitRow + (pos >> 5) + hw + j) = rw;
+        SC_ROW(c, c.bitRow + (pos >> 5) + j) = lw ^ rw;
+    }
+}
+// h < 32: everything inside one bit word
+template <class Src>
+POLAR_DEV void sc_g_r1_short(ScCtx& c, const Src& src, int s, int pos)
+{
+    const int h = 1 << s, sh = pos & 31;
+    const uint32_t mask = (1u << h) - 1u;
+    const uint32_t word = SC_ROW(c, c.bitRow + (pos >> 5));
+    const uint32_t lbits = (word >> sh) & mask;
+    uint32_t rbits = 0;
+    if (s >= 2) {
+        const int words = 1 << (s - 2); // <= 4
+        for (int w = 0; w < words; ++w)
+            rbits |= sign_nibble(g4(src.a(w), src.b(w), nibble_to_bytemask(lbits >> (4 * w)))) << (4 * w);
+    } else { // h == 2: both halves in one word
+        const uint32_t x = src.a(0);
+        rbits = sign_nibble(g4(x, x >> 16, nibble_to_bytemask(lbits & 3u))) & 3u;
+    }
+    const uint32_t both = (lbits ^ rbits) | (rbits << h);
+    const uint32_t clr = (mask | (mask << h)) << sh;
+    SC_ROW(c, c.bitRow + (pos >> 5)) = (word & ~clr) | (both << sh);
+}
+
+// ---- bit helpers (block of n = 2^s bits at absolute position pos, pos % n == 0)
+// sign bits of LLR rows [row, ..) of a block of n values, bit word j
+POLAR_DEV uint32_t sc_sign_word(const ScCtx& c, int row, int s, int j)
+{
+    if (s < 2) return sign_nibble(SC_ROW(c, row)) & ((1u << (1 << s)) - 1u);
+    const int words = 1 << (s - 2);
+    uint32_t w = 0;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        const int lw = 8 * j + t;
+        if (lw < words) w |= sign_nibble(SC_ROW(c, row + lw)) << (4 * t);
+    }
+    return w;
+}
+// store bit word j of a block (n >= 32: whole word; n < 32: j == 0, field inside a word)
+POLAR_DEV void sc_put_bits(ScCtx& c, int s, int pos, int j, uint32_t v)
 {
     if (s >= 5) {
-        for (int j = c.lane; j < (1 << (s - 5)); j += 32) c.bits[(pos >> 5) + j] = pattern;
-    } else if (c.lane == 0) {
+        SC_ROW(c, c.bitRow + (pos >> 5) + j) = v;
+    } else {
         const uint32_t mask = (1u << (1 << s)) - 1u;
         const int sh = pos & 31;
-        uint32_t* d = c.bits + (pos >> 5);
-        *d = (*d & ~(mask << sh)) | ((pattern & mask) << sh);
+        const uint32_t wd = SC_ROW(c, c.bitRow + (pos >> 5));
+        SC_ROW(c, c.bitRow + (pos >> 5)) = (wd & ~(mask << sh)) | ((v & mask) << sh);
+    }
+}
+POLAR_DEV void sc_fill_bits(ScCtx& c, int s, int pos, uint32_t pattern)
+{
+    const int nbw = s >= 5 ? 1 << (s - 5) : 1;
+    for (int j = 0; j < nbw; ++j) sc_put_bits(c, s, pos, j, pattern);
+}
+// bits = sign(LLR rows) with an optional flipped position; dup: the same bits again in [pos+n, pos+2n)
+POLAR_DEV void sc_put_signs(ScCtx& c, int row, int s, int pos, bool dup, uint32_t flipIdx, bool doFlip)
+{
+    const int nbw = s >= 5 ? 1 << (s - 5) : 1;
+    for (int j = 0; j < nbw; ++j) {
+        uint32_t v = sc_sign_word(c, row, s, j);
+        if (doFlip && (int)(flipIdx >> 5) == j) v ^= 1u << (flipIdx & 31u);
+        sc_put_bits(c, s, pos, j, v);
+        if (dup) sc_put_bits(c, s, pos + (1 << s), j, v);
     }
 }
 
-// Lane b < 8 accumulates "vector position block" b of the reference's 32-byte AVX lanes:
-// acc[j] = sat(..sat(sat(0 + x[j]) + x[32+j]).. ) for j in 4b..4b+3 (fastssc_fip_char.cpp:227-232)
-POLAR_DEV uint32_t sc_rep_lane_acc(const uint32_t* src, int s, int lane)
+// ---- leaves
+// acc[t] (t < 8) = byte lanes 4t..4t+3 of the reference's 32-byte accumulator:
+// acc[j] = sat(..sat(sat(0 + x[j]) + x[32+j]).. ) (fastssc_fip_char.cpp:227-232)
+POLAR_DEV void sc_rep_acc(const ScCtx& c, int row, int s, uint32_t (&acc)[8])
 {
-    uint32_t acc = 0;
-    if (s >= 2) {
-        const int words = 1 << (s - 2);
-        if (lane < 8)
-            for (int w = lane; w < words; w += 8) acc = adds4(acc, src[w]);
-    } else if (lane == 0) {
-        acc = src[0] & 0xFFFFu;
+    const int words = s >= 2 ? 1 << (s - 2) : 1;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) acc[t] = 0u;
+    if (s < 2) {
+        acc[0] = SC_ROW(c, row) & (s == 1 ? 0xFFFFu : 0xFFu);
+    } else if (words < 8) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (t < words) acc[t] = SC_ROW(c, row + t); // sat(0 + x) = x
+    } else {
+#pragma unroll
+        for (int t = 0; t < 8; ++t) acc[t] = SC_ROW(c, row + t);
+        for (int v = 8; v < words; v += 8) {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) acc[t] = adds4(acc[t], SC_ROW(c, row + v + t));
+        }
     }
-    return acc;
 }
 
-// First position of the minimum of |x| (unsigned, |-128| = 128) over n = 2^s values; key = |x| << 16 | idx
-template <class GetWord>
-POLAR_DEV uint32_t sc_min_uabs(int s, int lane, GetWord getWord)
+// SPC decision on rows [row, ..) holding n = 2^s values (fastssc_fip_char.cpp:274-319): returns whether a
+// bit flips and which.  Long form = threshold search (start 127, strict <), short form = plain first
+// minimum with +127 pads.  The flip is an arithmetic negate, so it is void for 0 and -128.
+POLAR_DEV bool sc_spc_decide(const ScCtx& c, int row, int s, bool longForm, uint32_t& flipIdx)
 {
-    uint32_t best = 0xFFFFFFFFu;
     const int n = 1 << s, words = n >= 4 ? n >> 2 : 1;
-    for (int w = lane; w < words; w += 32) {
-        const uint32_t m = uabs4(getWord(w));
+    uint32_t px = 0, best = 0xFFFFFFFFu;
+    for (int w = 0; w < words; ++w) {
+        uint32_t x = SC_ROW(c, row + w);
+        if (s < 2) x &= 0xFFFFu;
+        px ^= x;
+        const uint32_t m = uabs4(x); // |x| as unsigned, |-128| = 128
 #pragma unroll
         for (int e = 0; e < 4; ++e)
             if (4 * w + e < n) best = min(best, (((m >> (8 * e)) & 0xFFu) << 16) | (uint32_t)(4 * w + e));
     }
-    return __reduce_min_sync(FULL_MASK, best);
-}
-
-// SPC decision on a block of n = 2^s values (fastssc_fip_char.cpp:274-319): returns whether a bit flips
-// and which.  Long form = threshold search (start 127, strict <), short form = plain first minimum with
-// +127 pads.  The flip is an arithmetic negate, so it is void for 0 and -128.
-template <class GetWord>
-POLAR_DEV bool sc_spc_decide(int s, int lane, bool longForm, GetWord getWord, uint32_t& flipIdx)
-{
-    const int n = 1 << s, words = n >= 4 ? n >> 2 : 1;
-    uint32_t px = 0;
-    for (int w = lane; w < words; w += 32) px ^= getWord(w);
-    px = __reduce_xor_sync(FULL_MASK, px);
     const bool odd = (__popc(px & 0x80808080u) & 1) != 0;
-    const uint32_t key = sc_min_uabs(s, lane, getWord);
-    uint32_t mv = key >> 16, mi = key & 0xFFFFu;
+    uint32_t mv = best >> 16, mi = best & 0xFFFFu;
     bool flip = odd;
     if (longForm) {
         if (mv >= 127u) mi = 0u;
     } else if (mv > 127u && n < 32) {
         flip = false; // a +127 pad wins: the negate lands outside the block
     }
-    const uint32_t wv = getWord((int)(mi >> 2)); // uniform address: broadcast
+    const uint32_t wv = SC_ROW(c, row + (int)(mi >> 2));
     const int v = (int)(int8_t)(wv >> (8 * (mi & 3u)));
     if (v == 0 || v == -128) flip = false;
     flipIdx = mi;
     return flip;
+}
+
+// x <- x * F^{(x)n} on the lane's packed codeword estimate (non-systematic mode:
+// fastssc_fip_char.cpp:619-622, butterfly_fip.cpp:31-63)
+POLAR_DEV void sc_polar_transform(ScCtx& c, int N)
+{
+    const int W = max(N >> 5, 1);
+    for (int w = 0; w < W; ++w) {
+        uint32_t v = SC_ROW(c, c.bitRow + w);
+        if (N < 32) v &= (1u << N) - 1u;
+        v ^= (v >> 1) & 0x55555555u;
+        v ^= (v >> 2) & 0x33333333u;
+        v ^= (v >> 4) & 0x0F0F0F0Fu;
+        v ^= (v >> 8) & 0x00FF00FFu;
+        v ^= (v >> 16) & 0x0000FFFFu;
+        SC_ROW(c, c.bitRow + w) = v;
+    }
+    for (int d = 1; d < W; d <<= 1)
+        for (int w = 0; w < W; ++w)
+            if (!(w & d)) SC_ROW(c, c.bitRow + w) ^= SC_ROW(c, c.bitRow + w + d);
 }
 
 // ---------------------------------------------------------------- the kernel
@@ -149,185 +280,211 @@ __global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__
     extern __shared__ __align__(16) uint32_t smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpsPerBlock = blockDim.x >> 5;
     ScCtx c;
-    c.chan = smem + warp * p.warpW;
-    c.llr = c.chan + p.chanW;
-    c.bits = c.llr + p.slotW;
-    c.scr = c.bits + p.bitSlotW;
+    c.sm = smem + warp * p.warpW;
+    c.chan = static_cast<const uint32_t*>(p.llr);
     c.lane = lane;
     c.lgN = p.lgN;
+    c.nw = p.N >> 2;
+    c.bitRow = p.llrRows;
+    c.tileRow = p.tileRow;
+    c.chanRow = p.chanRow;
+    c.lastFrame = p.nFrames - 1;
+    uint32_t* tileA = c.sm + (p.tileRow << 5);
+    uint32_t* tileB = tileA + 33 * 32;
+    const uint32_t* myA = tileA + lane * 33;
+    const uint32_t* myB = tileB + lane * 33;
+    const int halfW = p.N >> 3, cw = min(32, halfW); // words per half of the channel row, chunk width
 
     const long long totalWarps = (long long)gridDim.x * warpsPerBlock;
-    for (long long frame = (long long)blockIdx.x * warpsPerBlock + warp; frame < p.nFrames; frame += totalWarps) {
-        load_channel_llrs(p, frame, c.chan, lane);
-        __syncwarp();
+    const long long nGroups = (p.nFrames + 31) >> 5;
+    for (long long grp = (long long)blockIdx.x * warpsPerBlock + warp; grp < nGroups; grp += totalWarps) {
+        c.frame0 = grp << 5;
+        if (c.chanRow >= 0) { // one-leaf codes: stage the channel rows (transposed) once
+            for (int w0 = 0; w0 < c.nw; w0 += 32) {
+                const int n = min(32, c.nw - w0);
+                sc_load_tile(c, tileA, w0, n);
+                __syncwarp();
+                for (int i = 0; i < n; ++i) SC_ROW(c, c.chanRow + w0 + i) = myA[i];
+                __syncwarp();
+            }
+        }
         for (int pc = 0;; ++pc) {
             const uint32_t op = sched.ops[pc];
             const uint32_t code = POLAR_OP_CODE(op);
             if (code == OP_END) break;
             const int s = (int)POLAR_OP_STAGE(op), pos = (int)POLAR_OP_POS(op);
             const bool longForm = (POLAR_OP_FLAGS(op) & OPF_LONG) != 0;
+            const bool top = (s + 1 == c.lgN) && c.chanRow < 0; // parent block = channel row in global memory
             switch (code) {
-            case OP_F: { // fip_char.h:76-91
-                const uint32_t* src = sc_llr(c, s + 1);
-                uint32_t* dst = c.llr + llr_woff(s);
-                if (s >= 2) {
-                    const int words = 1 << (s - 2);
-                    for (int w = lane; w < words; w += 32) dst[w] = f4(src[w], src[w + words]);
-                } else if (lane == 0) {
-                    const uint32_t x = src[0];
-                    dst[0] = f4(x, x >> 16);
+            case OP_F:      // fip_char.h:76-91
+            case OP_G:      // fip_char.h:93-110
+            case OP_G_0R:   // fip_char.h:112-131
+            case OP_G_R1: { // fastssc_fip_char.cpp:436-474
+                const int dstRow = llr_woff(s);
+                if (s < 2) { // block of 2: both halves in one word (never the channel: N >= 8)
+                    const ScRows src{ c, sc_llr_row(c, s + 1), 1 };
+                    const uint32_t x = src.a(0);
+                    if (code == OP_F) SC_ROW(c, dstRow) = f4(x, x >> 16);
+                    else if (code == OP_G_0R) SC_ROW(c, dstRow) = adds4(x, x >> 16);
+                    else if (code == OP_G) {
+                        const uint32_t nib = (SC_ROW(c, c.bitRow + (pos >> 5)) >> (pos & 31)) & 3u;
+                        SC_ROW(c, dstRow) = g4(x, x >> 16, nibble_to_bytemask(nib));
+                    } else sc_g_r1_short(c, src, s, pos);
+                    break;
                 }
-                break;
-            }
-            case OP_G: { // fip_char.h:93-110
-                const uint32_t* src = sc_llr(c, s + 1);
-                uint32_t* dst = c.llr + llr_woff(s);
-                if (s >= 2) {
-                    const int words = 1 << (s - 2);
-                    for (int w = lane; w < words; w += 32) {
-                        const int bp = pos + 4 * w;
-                        const uint32_t nib = c.bits[bp >> 5] >> (bp & 31);
-                        dst[w] = g4(src[w], src[w + words], nibble_to_bytemask(nib));
+                const int words = 1 << (s - 2);
+                if (!top) {
+                    const ScRows src{ c, sc_llr_row(c, s + 1), words };
+                    if (code == OP_F) sc_f_range(c, src, dstRow, 0, words);
+                    else if (code == OP_G_0R) sc_adds_range(c, src, dstRow, 0, words);
+                    else if (code == OP_G) sc_g_range(c, src, dstRow, pos, 0, words);
+                    else if (s >= 5) sc_g_r1_range(c, src, s, pos, 0, words);
+                    else sc_g_r1_short(c, src, s, pos);
+                } else { // words == halfW
+                    for (int w0 = 0; w0 < halfW; w0 += cw) {
+                        sc_load_tile(c, tileA, w0, cw);
+                        sc_load_tile(c, tileB, halfW + w0, cw);
+                        __syncwarp();
+                        const ScTiles src{ myA, myB, w0 };
+                        if (code == OP_F) sc_f_range(c, src, dstRow, w0, w0 + cw);
+                        else if (code == OP_G_0R) sc_adds_range(c, src, dstRow, w0, w0 + cw);
+                        else if (code == OP_G) sc_g_range(c, src, dstRow, pos, w0, w0 + cw);
+                        else if (s >= 5) sc_g_r1_range(c, src, s, pos, w0, w0 + cw);
+                        else sc_g_r1_short(c, src, s, pos); // halfW <= 4: a single chunk
+                        __syncwarp();
                     }
-                } else if (lane == 0) {
-                    const uint32_t x = src[0];
-                    const uint32_t nib = (c.bits[pos >> 5] >> (pos & 31)) & 3u;
-                    dst[0] = g4(x, x >> 16, nibble_to_bytemask(nib));
                 }
-                break;
-            }
-            case OP_G_0R: { // fip_char.h:112-131
-                const uint32_t* src = sc_llr(c, s + 1);
-                uint32_t* dst = c.llr + llr_woff(s);
-                if (s >= 2) {
-                    const int words = 1 << (s - 2);
-                    for (int w = lane; w < words; w += 32) dst[w] = adds4(src[w], src[w + words]);
-                } else if (lane == 0) {
-                    const uint32_t x = src[0];
-                    dst[0] = adds4(x, x >> 16);
-                }
-                break;
-            }
-            case OP_G_R1: { // ROneNode::simplifiedRightRateOneDecode, fastssc_fip_char.cpp:436-474
-                const uint32_t* src = sc_llr(c, s + 1);
-                const int h = 1 << s;
-                auto right = [&](int w) -> uint32_t {
-                    if (s >= 2) {
-                        const int bp = pos + 4 * w;
-                        const uint32_t nib = c.bits[bp >> 5] >> (bp & 31);
-                        return g4(src[w], src[w + (1 << (s - 2))], nibble_to_bytemask(nib));
-                    }
-                    const uint32_t x = src[0];
-                    return g4(x, x >> 16, nibble_to_bytemask((c.bits[pos >> 5] >> (pos & 31)) & 3u));
-                };
-                // stash the right LLR words so that both bit updates see the same values
-                uint32_t* tmp = c.llr + llr_woff(s);
-                const int words = s >= 2 ? 1 << (s - 2) : 1;
-                for (int w = lane; w < words; w += 32) tmp[w] = right(w);
-                __syncwarp();
-                auto get = [&](int w) -> uint32_t { return tmp[w]; };
-                sc_put_signs(c, s, pos + h, false, false, 0u, false, get); // right bits = sign(g)
-                __syncwarp();
-                sc_put_signs(c, s, pos, true, false, 0u, false, get);      // left ^= right
                 break;
             }
             case OP_COMBINE: { // fip_char.h:164-207
                 if (s >= 5) {
-                    const int hw = 1 << (s - 5);
-                    for (int j = lane; j < hw; j += 32) c.bits[(pos >> 5) + j] ^= c.bits[(pos >> 5) + hw + j];
-                } else if (lane == 0) {
+                    const int hw = 1 << (s - 5), r0 = c.bitRow + (pos >> 5);
+                    for (int j = 0; j < hw; ++j) SC_ROW(c, r0 + j) ^= SC_ROW(c, r0 + hw + j);
+                } else {
                     const int h = 1 << s, sh = pos & 31;
-                    uint32_t wd = c.bits[pos >> 5];
+                    uint32_t wd = SC_ROW(c, c.bitRow + (pos >> 5));
                     wd ^= ((wd >> (sh + h)) & ((1u << h) - 1u)) << sh;
-                    c.bits[pos >> 5] = wd;
+                    SC_ROW(c, c.bitRow + (pos >> 5)) = wd;
                 }
                 break;
             }
             case OP_COMBINE_0R: { // fip_char.h:209-220
                 if (s >= 5) {
-                    const int hw = 1 << (s - 5);
-                    for (int j = lane; j < hw; j += 32) c.bits[(pos >> 5) + j] = c.bits[(pos >> 5) + hw + j];
-                } else if (lane == 0) {
+                    const int hw = 1 << (s - 5), r0 = c.bitRow + (pos >> 5);
+                    for (int j = 0; j < hw; ++j) SC_ROW(c, r0 + j) = SC_ROW(c, r0 + hw + j);
+                } else {
                     const int h = 1 << s, sh = pos & 31;
                     const uint32_t mask = (1u << h) - 1u;
-                    uint32_t wd = c.bits[pos >> 5];
+                    uint32_t wd = SC_ROW(c, c.bitRow + (pos >> 5));
                     wd = (wd & ~(mask << sh)) | (((wd >> (sh + h)) & mask) << sh);
-                    c.bits[pos >> 5] = wd;
+                    SC_ROW(c, c.bitRow + (pos >> 5)) = wd;
                 }
                 break;
             }
             case OP_SC_R0: sc_fill_bits(c, s, pos, 0u); break;
-            case OP_SC_R1: {
-                const uint32_t* src = sc_llr(c, s);
-                sc_put_signs(c, s, pos, false, false, 0u, false, [&](int w) -> uint32_t { return src[w]; });
-                break;
-            }
+            case OP_SC_R1: sc_put_signs(c, sc_llr_row(c, s), s, pos, false, 0u, false); break;
             case OP_SC_REP: { // fastssc_fip_char.cpp:225-240,265-272 + reduce_adds_epi8
-                uint32_t t = sc_rep_lane_acc(sc_llr(c, s), s, lane);
-                t = adds4(t, __shfl_down_sync(FULL_MASK, t, 4));
-                t = adds4(t, __shfl_down_sync(FULL_MASK, t, 2));
-                t = adds4(t, __shfl_down_sync(FULL_MASK, t, 1));
+                uint32_t a[8];
+                sc_rep_acc(c, sc_llr_row(c, s), s, a);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) a[t] = adds4(a[t], a[t + 4]);
+                a[0] = adds4(a[0], a[2]);
+                a[1] = adds4(a[1], a[3]);
+                uint32_t t = adds4(a[0], a[1]);
                 t = adds4(t, t >> 16);
                 t = adds4(t, t >> 8);
-                t = __shfl_sync(FULL_MASK, t, 0);
                 sc_fill_bits(c, s, pos, (t & 0x80u) ? 0xFFFFFFFFu : 0u);
                 break;
             }
             case OP_SC_REP2: { // fastssc_fip_char.cpp:249-263 + half_reduce_adds_epi8 (n >= 32)
-                uint32_t t = sc_rep_lane_acc(sc_llr(c, s), s, lane);
-                t = adds4(t, __shfl_xor_sync(FULL_MASK, t, 4));
-                t = adds4(t, __shfl_xor_sync(FULL_MASK, t, 2));
-                t = adds4(t, __shfl_xor_sync(FULL_MASK, t, 1));
+                uint32_t a[8];
+                sc_rep_acc(c, sc_llr_row(c, s), s, a);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) a[t] = adds4(a[t], a[t + 4]);
+                a[0] = adds4(a[0], a[2]);
+                a[1] = adds4(a[1], a[3]);
+                uint32_t t = adds4(a[0], a[1]);
                 t = adds4(t, __byte_perm(t, 0u, 0x1032u));
-                t = __shfl_sync(FULL_MASK, t, 0);
                 const uint32_t pat = ((t & 0x80u) ? 0x55555555u : 0u) | ((t & 0x8000u) ? 0xAAAAAAAAu : 0u);
                 sc_fill_bits(c, s, pos, pat);
                 break;
             }
             case OP_SC_SPC: { // fastssc_fip_char.cpp:274-319
-                const uint32_t* src = sc_llr(c, s);
-                auto get = [&](int w) -> uint32_t {
-                    const uint32_t x = src[w];
-                    return s >= 2 ? x : (x & 0xFFFFu);
-                };
+                const int row = sc_llr_row(c, s);
                 uint32_t fi;
-                const bool flip = sc_spc_decide(s, lane, longForm, get, fi);
-                sc_put_signs(c, s, pos, false, false, fi, flip, get);
+                const bool flip = sc_spc_decide(c, row, s, longForm, fi);
+                sc_put_signs(c, row, s, pos, false, fi, flip);
                 break;
             }
             case OP_SC_ZERO_SPC:   // fastssc_fip_char.cpp:321-388
             case OP_SC_ZERO_ONE: { // fastssc_fip_char.cpp:390-399
-                const uint32_t* src = sc_llr(c, s);
-                const int hs = s - 1; // half block
-                uint32_t* y = c.llr + llr_woff(hs);
+                const int hs = s - 1, yRow = llr_woff(hs); // y = sat(l + r) goes to the (free) child stage
                 if (hs >= 2) {
                     const int words = 1 << (hs - 2);
-                    for (int w = lane; w < words; w += 32) y[w] = adds4(src[w], src[w + words]);
-                } else if (lane == 0) {
-                    const uint32_t x = src[0];
-                    y[0] = adds4(x, x >> 16) & 0xFFFFu;
+                    if (s == c.lgN && c.chanRow < 0) { // cannot happen: one-leaf codes stage the channel
+                    }
+                    const ScRows src{ c, sc_llr_row(c, s), words };
+                    sc_adds_range(c, src, yRow, 0, words);
+                } else {
+                    const uint32_t x = SC_ROW(c, sc_llr_row(c, s));
+                    SC_ROW(c, yRow) = adds4(x, x >> 16) & 0xFFFFu;
                 }
-                __syncwarp();
-                auto get = [&](int w) -> uint32_t { return y[w]; };
                 uint32_t fi = 0;
                 bool flip = false;
-                if (code == OP_SC_ZERO_SPC) flip = sc_spc_decide(hs, lane, longForm, get, fi);
-                sc_put_signs(c, hs, pos, false, true, fi, flip, get);
+                if (code == OP_SC_ZERO_SPC) flip = sc_spc_decide(c, yRow, hs, longForm, fi);
+                sc_put_signs(c, yRow, hs, pos, true, fi, flip);
                 break;
             }
             default: break;
             }
-            __syncwarp();
         }
-        // systematic: gather; non-systematic: re-encode first (fastssc_fip_char.cpp:616-630)
-        uint32_t* outw = c.scr;
-        const uint32_t* cw = c.bits;
-        if (!p.systematic) {
-            warp_polar_transform(c.bits, p.N, lane);
+        // systematic: gather; non-systematic: re-encode first (fastssc_fip_char.cpp:616-630), then
+        // getPackedInformationBits (bitcontainer.cpp:536-564) + Detector::check, all per lane.
+        if (!p.systematic) sc_polar_transform(c, p.N);
+        __syncwarp(); // the stage rows are dead: reuse them as the image of the warp's 32 output rows
+        uint8_t* img = reinterpret_cast<uint8_t*>(c.sm);
+        uint32_t syn = 0, acc = 0;
+        int curW = -1;
+        uint32_t curV = 0;
+        const bool wordOut = (p.kb & 3) == 0;
+        for (int k = 0; k < p.K; ++k) {
+            const int pos = (int)__ldg(p.infoPos + k);
+            if ((pos >> 5) != curW) { // uniform: positions ascend
+                curW = pos >> 5;
+                curV = SC_ROW(c, c.bitRow + curW);
+            }
+            const uint32_t bit = (curV >> (pos & 31)) & 1u;
+            acc = (acc << 1) | bit;
+            if (p.crcBits) syn ^= __ldg(p.crcTab + k) & (0u - bit);
+            if (wordOut) {
+                if ((k & 31) == 31)
+                    reinterpret_cast<uint32_t*>(img)[lane * (p.kb >> 2) + (k >> 5)] = __byte_perm(acc, 0u, 0x0123u);
+            } else if ((k & 7) == 7) {
+                img[lane * p.kb + (k >> 3)] = (uint8_t)acc;
+            }
         }
-        const uint32_t syn = gather_info_and_syndrome(p, cw, outw, lane);
-        store_info(p, frame, outw, lane);
-        if (lane == 0) p.ok[frame] = syn == 0u ? 1 : 0;
+        if (wordOut) { // the last, partly filled unit is zero padded (MSB first)
+            if (p.K & 31)
+                reinterpret_cast<uint32_t*>(img)[lane * (p.kb >> 2) + (p.K >> 5)] =
+                    __byte_perm(acc << (32 - (p.K & 31)), 0u, 0x0123u);
+        } else if (p.K & 7) {
+            img[lane * p.kb + (p.K >> 3)] = (uint8_t)(acc << (8 - (p.K & 7)));
+        }
+        const bool ok = !p.crcBits || (syn ^ p.crcInit) == 0u;
+        __syncwarp();
+        // bit rows and the image may overlap only if the image is larger than the stage rows: never
+        // (8*kb <= N words <= 32 * llrRows).  Coalesced copy of the image.
+        const long long nHere = min(32LL, p.nFrames - c.frame0);
+        uint8_t* dst = p.out + c.frame0 * p.kb;
+        const long long bytes = nHere * p.kb;
+        if (wordOut) {
+            uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
+            const uint32_t* s4 = reinterpret_cast<const uint32_t*>(img);
+            for (long long i = lane; i < (bytes >> 2); i += 32) d4[i] = s4[i];
+        } else {
+            for (long long i = lane; i < bytes; i += 32) dst[i] = img[i];
+        }
+        if (c.frame0 + lane < p.nFrames) p.ok[c.frame0 + lane] = ok ? 1 : 0;
         __syncwarp();
     }
 }

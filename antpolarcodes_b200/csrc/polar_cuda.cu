@@ -10,6 +10,7 @@
 #include "scl_i8.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -54,6 +55,9 @@ struct polar_code {
     DecodeParams geo{};            // geometry fields only
     int warpsPerBlock = 0, blocksPerSM = 0, numSMs = 0;
     size_t smemPerBlock = 0;
+    uint32_t* dSpill = nullptr;    // list decoders: L2-resident scratch for the top LLR stage
+    int8_t* dQuant = nullptr;      // int8 copy of fp32 LLRs (quantiser pre-pass)
+    size_t quantBytes = 0;
     // staging buffers for HOST-memory calls
     void* dLlr = nullptr;
     uint8_t* dOut = nullptr;
@@ -82,6 +86,12 @@ DecodeKernel pick_scl_kernel(int L)
     return nullptr;
 }
 
+int env_int(const char* name, int dflt)
+{
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
 int setup_decoder_geometry(polar_code* c)
 {
     DecodeParams& g = c->geo;
@@ -92,33 +102,58 @@ int setup_decoder_geometry(polar_code* c)
     g.crcBits = c->crcBits;
     g.systematic = c->systematic;
     g.listSize = c->L;
-    g.chanW = c->N / 4;
+    g.spillStage = c->lgN;
+    g.spillWarpW = 0;
+    g.chanRow = -1;
     const bool scl = (c->kind == POLAR_KIND_SCL_I8);
     const int L = scl ? c->L : 1;
-    int slot = llr_woff(c->lgN);
-    if (scl) {
-        const int want = (32 / L) % 32; // slot stride == lanes-per-path (mod 32): conflict-free banks
-        while ((slot % 32) != want) ++slot;
-    }
-    g.slotW = slot;
-    g.bitW = bit_woff(c->lgN) + std::max(1, c->N / 32);
-    g.bitSlotW = scl ? ((2 * g.bitW) | 1) : g.bitW;
-    const int epi = (c->K + 31) / 32 + std::max(1, c->N / 32);
-    g.scratchW = std::max(8 * L, epi) + 4;
-    int total = g.chanW + L * g.slotW + L * g.bitSlotW + g.scratchW;
-    total = (total + 3) & ~3;
-    g.warpW = total;
-
-    c->kernel = scl ? pick_scl_kernel(L) : (DecodeKernel)fastssc_i8_kernel;
-    if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, c->device));
     c->numSMs = prop.multiProcessorCount;
+    if (scl) {
+        // One list per group of L lanes, 32/L frames per warp.  Per frame: L LLR slots (stages below
+        // spillStage) and L bit slots (array A: stages 0..lgN, array B: stages 0..lgN-1).  Strides are
+        // == 1 (mod L) and the frame stride == L (mod 32), so the 32 lanes of a warp -- lane = (frame, path)
+        // -- hit 32 distinct banks when every path walks its own slot.
+        const bool wantSpill = env_int("POLAR_CUDA_SPILL", 1) != 0 && c->lgN >= 7;
+        if (wantSpill) g.spillStage = c->lgN - 1;
+        int slot = llr_woff(g.spillStage);
+        while (slot % L != 1 % L) ++slot;
+        g.slotW = slot;
+        const int bitA = bit_woff(c->lgN) + std::max(1, c->N / 32);
+        g.bitBW = bitA;
+        int bslot = bitA + bit_woff(c->lgN);
+        while (bslot % L != 1 % L) ++bslot;
+        g.bitSlotW = bslot;
+        int frame = L * g.slotW + L * g.bitSlotW;
+        while (frame % 32 != L % 32) ++frame;
+        g.frameW = frame;
+        g.scratchW = (c->K + 31) / 32 + std::max(1, c->N / 32) + 4;
+        g.warpW = ((32 / L) * g.frameW + g.scratchW + 3) & ~3;
+        if (wantSpill) g.spillWarpW = 32 * (1 << (g.spillStage - 2));
+        c->kernel = pick_scl_kernel(L);
+    } else {
+        // One frame per thread; a warp's shared memory is a stack of 32-word rows.
+        g.llrRows = llr_woff(c->lgN);
+        g.bitRows = std::max(1, c->N / 32);
+        int rows = g.llrRows + g.bitRows;
+        const int tileRows = 66; // two 32x33 transpose tiles
+        if (llr_woff(c->lgN - 1) >= tileRows) g.tileRow = 0; // the lower stages are dead at both top-level steps
+        else { g.tileRow = rows; rows += tileRows; }
+        const bool rootLeaf = !c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN;
+        if (rootLeaf) { g.chanRow = rows; rows += c->N / 4; }
+        g.outRow = 0;
+        g.warpW = rows * 32;
+        c->kernel = (DecodeKernel)fastssc_i8_kernel;
+    }
+    if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
     const size_t perWarp = (size_t)g.warpW * 4;
     if (perWarp > (size_t)prop.sharedMemPerBlockOptin)
         return fail(POLAR_E_UNSUPPORTED, "code does not fit in shared memory (N x listSize too large)");
     int bestWarps = 0, bestW = 1, bestB = 1;
-    for (int w : { 8, 4, 2, 1 }) {
+    const int forceW = env_int("POLAR_CUDA_WARPS_PER_BLOCK", 0);
+    for (int w = 8; w >= 1; --w) {
+        if (forceW && w != forceW) continue;
         const size_t smem = perWarp * w;
         if (smem > (size_t)prop.sharedMemPerBlockOptin) continue;
         CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -132,6 +167,10 @@ int setup_decoder_geometry(polar_code* c)
     c->smemPerBlock = perWarp * bestW;
     CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)c->smemPerBlock));
+    if (g.spillWarpW) {
+        const size_t words = (size_t)g.spillWarpW * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
+        CUDA_TRY(cudaMalloc(&c->dSpill, words * sizeof(uint32_t)));
+    }
     return POLAR_OK;
 }
 
@@ -178,6 +217,7 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaSetDevice(c->device);
     cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab);
     cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
+    cudaFree(c->dSpill); cudaFree(c->dQuant);
     delete c;
     return POLAR_OK;
 }
@@ -279,7 +319,6 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     p.crcTab = c->dSynTab;
     p.crcInit = c->synInit;
     p.nFrames = (long long)nFrames;
-    p.llrIsFloat = llrType == POLAR_LLR_F32;
     uint8_t* okDev = ok_out;
     if (mem == POLAR_MEM_HOST) {
         int rc = ensure_staging(c, nFrames, eb);
@@ -294,7 +333,27 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
         }
         p.llr = llr; p.out = info_out; p.ok = okDev;
     }
-    const long long blocksNeeded = ((long long)nFrames + c->warpsPerBlock - 1) / c->warpsPerBlock;
+    p.spill = c->dSpill;
+    if (llrType == POLAR_LLR_F32) { // CharContainer::insertLlr(const float*): quantise once, decode the int8 copy
+        const size_t need = nFrames * (size_t)c->N;
+        if (need > c->quantBytes) {
+            cudaFree(c->dQuant);
+            c->dQuant = nullptr;
+            c->quantBytes = 0;
+            CUDA_TRY(cudaMalloc(&c->dQuant, need));
+            c->quantBytes = need;
+        }
+        const long long nWords = (long long)(need / 4);
+        const int qgrid = (int)std::min<long long>((nWords + 255) / 256, (long long)c->numSMs * 16);
+        quantize_llr_kernel<<<qgrid, 256, 0, st>>>(static_cast<const float4*>(p.llr), reinterpret_cast<uint32_t*>(c->dQuant),
+                                                  nWords, c->N >= 32 ? 1 : 0);
+        c->launches++;
+        CUDA_TRY(cudaGetLastError());
+        p.llr = c->dQuant;
+    }
+    const int framesPerWarp = c->kind == POLAR_KIND_SCL_I8 ? 32 / c->L : 32;
+    const long long warpsNeeded = ((long long)nFrames + framesPerWarp - 1) / framesPerWarp;
+    const long long blocksNeeded = (warpsNeeded + c->warpsPerBlock - 1) / c->warpsPerBlock;
     const int grid = (int)std::min<long long>(blocksNeeded, (long long)c->blocksPerSM * c->numSMs);
     c->kernel<<<grid, c->warpsPerBlock * 32, c->smemPerBlock, st>>>(p, c->sched);
     c->launches++;

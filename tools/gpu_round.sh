@@ -1,0 +1,23 @@
+#!/bin/bash
+# One gpurun call: GPU parity tests, benches of both headline workloads and (only when the tests are green)
+# the ncu launch list + one full capture of the SCL kernel.  Everything lands in gpurun_out/.
+# usage: tools/gpu_round.sh [tag]   (run from the repo root on the GPU box)
+TAG=${1:-run}
+OUT=gpurun_out
+mkdir -p $OUT
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/${TAG}_gpu.txt 2>&1
+timeout 900 python -m pytest tests -m gpu -q --timeout 300 -p no:cacheprovider --tb=short > $OUT/${TAG}_pytest.log 2>&1
+RC=$?
+tail -5 $OUT/${TAG}_pytest.log
+echo "pytest rc=$RC"
+for WL in scl8 fastssc; do
+  timeout 300 python bench.py --workload $WL --steps 5 --warmup 3 > $OUT/${TAG}_bench_$WL.json 2> $OUT/${TAG}_bench_$WL.err
+  echo "bench $WL rc=$?"; cat $OUT/${TAG}_bench_$WL.json | cut -c1-600
+done
+if [ $RC -eq 0 ] && [ "${NCU:-1}" = "1" ]; then
+  CMD="python bench.py --workload ${NCU_WL:-scl8} --steps 2 --warmup 1 --frames ${NCU_FRAMES:-131072} --e2e-frames 8192"
+  $CMD > $OUT/${TAG}_ncu_plain.log 2>&1 &&
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
+  ncu --set full --clock-control none --import-source on -k regex:${NCU_KERNEL:-scl_i8_kernel} -s 1 -c 1 -o $OUT/${TAG}_prof -f $CMD > $OUT/${TAG}_ncu_full.log 2>&1
+  echo "ncu rc=$?"
+fi
