@@ -17,14 +17,17 @@ struct DecodeParams {
     int crcBits, systematic;
     int listSize;
     // shared-memory geometry, in 32-bit words
-    int slotW;                // list decoders: LLR slot stride (one path, stages below spillStage)
-    int bitBW;                // list decoders: offset of bit array "B" inside a bit slot
-    int bitSlotW;             // list decoders: bit slot stride (arrays A and B)
+    int slotW;                // list decoders: LLR slot stride (one path, stages below smemStages)
+    int bitBW;                // list decoders: offset of bit region "B" inside a bit slot (= words of region A)
+    int bitB1;                // list decoders: offset of the odd-stage half of region B (B is a ping-pong pair)
+    int bitSlotW;             // list decoders: bit slot stride (regions A and B)
+    int rootLeaf;             // the whole code is one leaf: region A also holds stage lgN
     int frameW;               // list decoders: stride between the frames of one warp
     int scratchW;             // per-warp scratch
     int warpW;                // total words per warp
-    int spillStage;           // LLR stage kept in `spill` instead of shared memory (lgN = none)
+    int smemStages;           // LLR stages [0, smemStages) live in shared memory, [smemStages, lgN) in `spill`
     int spillWarpW;           // words of `spill` per resident warp
+    int lockstep;             // warps of a block meet at a barrier before every schedule step
     // Fast-SSC (one frame per thread): rows of 32 words
     int llrRows, bitRows, tileRow, outRow, chanRow;
 };

@@ -102,7 +102,10 @@ int setup_decoder_geometry(polar_code* c)
     g.crcBits = c->crcBits;
     g.systematic = c->systematic;
     g.listSize = c->L;
-    g.spillStage = c->lgN;
+    g.smemStages = c->lgN;
+    g.lockstep = env_int("POLAR_CUDA_LOCKSTEP", 1);
+    g.rootLeaf = 0;
+    g.bitB1 = 0;
     g.spillWarpW = 0;
     g.chanRow = -1;
     const bool scl = (c->kind == POLAR_KIND_SCL_I8);
@@ -115,22 +118,31 @@ int setup_decoder_geometry(polar_code* c)
         // spillStage) and L bit slots (array A: stages 0..lgN, array B: stages 0..lgN-1).  Strides are
         // == 1 (mod L) and the frame stride == L (mod 32), so the 32 lanes of a warp -- lane = (frame, path)
         // -- hit 32 distinct banks when every path walks its own slot.
-        const bool wantSpill = env_int("POLAR_CUDA_SPILL", 1) != 0 && c->lgN >= 7;
-        if (wantSpill) g.spillStage = c->lgN - 1;
-        int slot = llr_woff(g.spillStage);
+        // The top LLR stages live in an L2-resident scratch instead (coalesced [word][lane] layout), which is
+        // what sets the resident warp count; region A of the bit slots holds stages 0..lgN-1 (the root is
+        // assembled by the epilogue), region B is a ping-pong pair.
+        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 9 ? 2 : (c->lgN >= 7 ? 1 : 0));
+        nSpill = std::max(0, std::min(nSpill, c->lgN - 5));
+        g.smemStages = c->lgN - nSpill;
+        int slot = llr_woff(g.smemStages);
         while (slot % L != 1 % L) ++slot;
         g.slotW = slot;
-        const int bitA = bit_woff(c->lgN) + std::max(1, c->N / 32);
+        g.rootLeaf = (!c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN) ? 1 : 0;
+        const int nW = std::max(1, c->N / 32);
+        const int bitA = bit_woff(c->lgN) + (g.rootLeaf ? nW : 0);
+        auto stageWords = [](int s) { return s >= 5 ? 1 << (s - 5) : 1; };
+        const int topEven = (c->lgN - 1) & ~1, topOdd = ((c->lgN - 1) & 1) ? c->lgN - 1 : c->lgN - 2;
         g.bitBW = bitA;
-        int bslot = bitA + bit_woff(c->lgN);
+        g.bitB1 = stageWords(topEven);
+        int bslot = bitA + stageWords(topEven) + stageWords(std::max(topOdd, 1));
         while (bslot % L != 1 % L) ++bslot;
         g.bitSlotW = bslot;
         int frame = L * g.slotW + L * g.bitSlotW;
         while (frame % 32 != L % 32) ++frame;
         g.frameW = frame;
-        g.scratchW = (c->K + 31) / 32 + std::max(1, c->N / 32) + 4;
+        g.scratchW = 2 * ((c->K + 31) / 32) + nW + 4;
         g.warpW = ((32 / L) * g.frameW + g.scratchW + 3) & ~3;
-        if (wantSpill) g.spillWarpW = 32 * (1 << (g.spillStage - 2));
+        if (nSpill) g.spillWarpW = 32 * ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
         c->kernel = pick_scl_kernel(L);
     } else {
         // One frame per thread; a warp's shared memory is a stack of 32-word rows.

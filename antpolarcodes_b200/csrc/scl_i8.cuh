@@ -41,19 +41,19 @@ template <> struct Log2<1> { static constexpr int v = 0; };
 // A block of 32-bit words reachable as p[w * stride]: shared memory (stride 1), a channel row in global
 // memory (stride 1) or a column of the spill scratch (stride 32).
 struct Words {
-    uint32_t* p;
+    const uint32_t* p;
     int stride;
-    POLAR_DEV uint32_t operator()(int w) const { return p[w * stride]; }
-    POLAR_DEV void put(int w, uint32_t v) const { p[w * stride] = v; }
+    bool cg; // spill column: read at L2 (the writers use st.cg, L1 is never involved)
+    POLAR_DEV uint32_t operator()(int w) const { return cg ? __ldcg(p + w * stride) : p[w * stride]; }
 };
 
 struct SclCtx {
-    uint32_t* chan;   // this lane's frame: channel LLR row (global memory, read only)
+    const uint32_t* chan; // this lane's frame: channel LLR row (global memory, read only)
     uint32_t* llr;    // this lane's frame: LLR slots (shared memory)
     uint32_t* bits;   // this lane's frame: bit slots (shared memory)
     uint32_t* spill;  // this lane's frame: first column of the frame in the warp's spill scratch
     int gl, fb;       // lane within the frame's group, first lane of the group
-    int slotW, bitBW, bitSlotW, lgN, spillStage;
+    int slotW, bitBW, bitB1, bitSlotW, lgN, smemStages;
     int metric;
     unsigned long long llrPtr, lbPtr;
 };
@@ -69,17 +69,29 @@ POLAR_DEV unsigned long long shfl64(unsigned long long v, int src)
     return ((unsigned long long)hi << 32) | lo;
 }
 // physical slot of `path`'s block at `stage` (path state lives in lane fb + path)
-POLAR_DEV uint32_t scl_slot_of(const SclCtx& c, unsigned long long vec, int stage, int path, int lgG)
+POLAR_DEV uint32_t scl_slot_of(const SclCtx& c, unsigned long long vec, int stage, int path)
 {
-    uint32_t v = (uint32_t)(vec >> (5 * stage)) & 31u;
-    if (lgG) v = __shfl_sync(FULL_MASK, v, c.fb + path); // a lane that owns its path reads its own register
-    return v;
+    return __shfl_sync(FULL_MASK, (uint32_t)(vec >> (5 * stage)) & 31u, c.fb + path);
 }
+// word offset of a spilled stage inside the warp's scratch ([word][lane] layout, 32 columns)
+POLAR_DEV int scl_spill_woff(const SclCtx& c, int stage) { return ((1 << (stage - 2)) - (1 << (c.smemStages - 2))) << 5; }
+// any LLR block through a generic pointer (leaves; the F/G steps use typed pointers)
 POLAR_DEV Words scl_llr_block(const SclCtx& c, int stage, uint32_t slot)
 {
-    if (stage == c.lgN) return Words{ c.chan, 1 };
-    if (stage == c.spillStage) return Words{ c.spill + slot, 32 };
-    return Words{ c.llr + slot * c.slotW + llr_woff(stage), 1 };
+    if (stage == c.lgN) return Words{ c.chan, 1, false };
+    if (stage >= c.smemStages) return Words{ c.spill + scl_spill_woff(c, stage) + slot, 32, true };
+    return Words{ c.llr + slot * c.slotW + llr_woff(stage), 1, false };
+}
+// bit blocks: region A keeps every stage (left-child results wait there for the combine), region B is a
+// ping-pong pair (a right-child result is consumed by the very next combine)
+POLAR_DEV uint32_t* scl_bits_a(const SclCtx& c, uint32_t slot, int stage) { return c.bits + slot * c.bitSlotW + bit_woff(stage); }
+POLAR_DEV uint32_t* scl_bits_b(const SclCtx& c, uint32_t slot, int stage)
+{
+    return c.bits + slot * c.bitSlotW + c.bitBW + ((stage & 1) ? c.bitB1 : 0);
+}
+POLAR_DEV uint32_t* scl_bits_out(const SclCtx& c, uint32_t slot, int stage, bool isRight)
+{
+    return isRight ? scl_bits_b(c, slot, stage) : scl_bits_a(c, slot, stage);
 }
 POLAR_DEV int group_add(int v, int lgG)
 {
@@ -106,62 +118,99 @@ POLAR_DEV uint32_t list_max(uint32_t v)
 }
 
 // ---------------------------------------------------------------- inner-node steps
-template <int L>
-POLAR_DEV void scl_op_f(SclCtx& c, int s, int lgP)
+// Parent block in global memory: the channel row (read only, L1 allocating) or a spill column (L2 only).
+template <bool SG>
+POLAR_DEV uint32_t scl_ld(const uint32_t* p, bool chan)
 {
-    const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s + 1, scl_slot_of(c, c.llrPtr, s + 1, q, lgG));
-    const Words dst = scl_llr_block(c, s, (uint32_t)q);
-    if (s >= 2) {
-        const int words = 1 << (s - 2);
-        int w = g;
-        for (; w + 3 * G < words; w += 4 * G) { // four independent butterflies in flight
-            const uint32_t a0 = src(w), a1 = src(w + G), a2 = src(w + 2 * G), a3 = src(w + 3 * G);
-            const uint32_t b0 = src(w + words), b1 = src(w + G + words), b2 = src(w + 2 * G + words),
-                           b3 = src(w + 3 * G + words);
-            dst.put(w, f4(a0, b0));
-            dst.put(w + G, f4(a1, b1));
-            dst.put(w + 2 * G, f4(a2, b2));
-            dst.put(w + 3 * G, f4(a3, b3));
-        }
-        for (; w < words; w += G) dst.put(w, f4(src(w), src(w + words)));
-    } else if (g == 0) { // block of 2: both halves sit in one word
-        const uint32_t x = src(0);
-        dst.put(0, f4(x, x >> 16));
-    }
-    scl_set_own(c.llrPtr, s, c.gl);
-    __syncwarp();
+    if (!SG) return *p;
+    return chan ? __ldg(p) : __ldcg(p);
+}
+template <bool DG>
+POLAR_DEV void scl_st(uint32_t* p, uint32_t v)
+{
+    if (DG) __stcg(p, v); else *p = v;
 }
 
-template <int L>
-POLAR_DEV void scl_op_g(SclCtx& c, int s, int lgP)
+template <bool SG, bool DG>
+POLAR_DEV void scl_f_words(const uint32_t* src, int ss, bool chan, uint32_t* dst, int ds, int s, int g, int G)
 {
-    const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s + 1, scl_slot_of(c, c.llrPtr, s + 1, q, lgG));
-    const uint32_t* lb = c.bits + scl_slot_of(c, c.lbPtr, s, q, lgG) * c.bitSlotW + bit_woff(s);
-    const Words dst = scl_llr_block(c, s, (uint32_t)q);
     if (s >= 2) {
         const int words = 1 << (s - 2);
+        const uint32_t* srcb = src + words * ss;
+        int w = g;
+        for (; w + 3 * G < words; w += 4 * G) { // four independent butterflies in flight
+            uint32_t a[4], b[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                a[t] = scl_ld<SG>(src + (w + t * G) * ss, chan);
+                b[t] = scl_ld<SG>(srcb + (w + t * G) * ss, chan);
+            }
+#pragma unroll
+            for (int t = 0; t < 4; ++t) scl_st<DG>(dst + (w + t * G) * ds, f4(a[t], b[t]));
+        }
+        for (; w < words; w += G) scl_st<DG>(dst + w * ds, f4(scl_ld<SG>(src + w * ss, chan), scl_ld<SG>(srcb + w * ss, chan)));
+    } else if (g == 0) { // block of 2: both halves sit in one word
+        const uint32_t x = scl_ld<SG>(src, chan);
+        scl_st<DG>(dst, f4(x, x >> 16));
+    }
+}
+
+template <bool SG, bool DG>
+POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_t* lb, uint32_t* dst, int ds, int s,
+                           int g, int G)
+{
+    if (s >= 2) {
+        const int words = 1 << (s - 2);
+        const uint32_t* srcb = src + words * ss;
         int w = g;
         for (; w + 3 * G < words; w += 4 * G) {
-            const uint32_t a0 = src(w), a1 = src(w + G), a2 = src(w + 2 * G), a3 = src(w + 3 * G);
-            const uint32_t b0 = src(w + words), b1 = src(w + G + words), b2 = src(w + 2 * G + words),
-                           b3 = src(w + 3 * G + words);
-            const uint32_t n0 = lb[w >> 3] >> ((w & 7) * 4), n1 = lb[(w + G) >> 3] >> (((w + G) & 7) * 4);
-            const uint32_t n2 = lb[(w + 2 * G) >> 3] >> (((w + 2 * G) & 7) * 4);
-            const uint32_t n3 = lb[(w + 3 * G) >> 3] >> (((w + 3 * G) & 7) * 4);
-            dst.put(w, g4(a0, b0, nibble_to_bytemask(n0)));
-            dst.put(w + G, g4(a1, b1, nibble_to_bytemask(n1)));
-            dst.put(w + 2 * G, g4(a2, b2, nibble_to_bytemask(n2)));
-            dst.put(w + 3 * G, g4(a3, b3, nibble_to_bytemask(n3)));
+            uint32_t a[4], b[4], n[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int wt = w + t * G;
+                a[t] = scl_ld<SG>(src + wt * ss, chan);
+                b[t] = scl_ld<SG>(srcb + wt * ss, chan);
+                n[t] = lb[wt >> 3] >> ((wt & 7) * 4);
+            }
+#pragma unroll
+            for (int t = 0; t < 4; ++t) scl_st<DG>(dst + (w + t * G) * ds, g4(a[t], b[t], nibble_to_bytemask(n[t])));
         }
         for (; w < words; w += G) {
             const uint32_t nib = lb[w >> 3] >> ((w & 7) * 4);
-            dst.put(w, g4(src(w), src(w + words), nibble_to_bytemask(nib)));
+            scl_st<DG>(dst + w * ds, g4(scl_ld<SG>(src + w * ss, chan), scl_ld<SG>(srcb + w * ss, chan), nibble_to_bytemask(nib)));
         }
     } else if (g == 0) {
-        const uint32_t x = src(0);
-        dst.put(0, g4(x, x >> 16, nibble_to_bytemask(lb[0] & 3u)));
+        const uint32_t x = scl_ld<SG>(src, chan);
+        scl_st<DG>(dst, g4(x, x >> 16, nibble_to_bytemask(lb[0] & 3u)));
+    }
+}
+
+// F (lb == nullptr) or G step producing the stage-s block of every live path
+template <int L, bool ISG>
+POLAR_DEV void scl_op_fg(SclCtx& c, int s, int lgP)
+{
+    const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
+    const uint32_t slot = scl_slot_of(c, c.llrPtr, s + 1, q);
+    const uint32_t* lb = nullptr;
+    if (ISG) lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q), s);
+    if (s + 1 < c.smemStages) { // shared -> shared: the bulk of the steps
+        const uint32_t* src = c.llr + slot * c.slotW + llr_woff(s + 1);
+        uint32_t* dst = c.llr + q * c.slotW + llr_woff(s);
+        if (ISG) scl_g_words<false, false>(src, 1, false, lb, dst, 1, s, g, G);
+        else scl_f_words<false, false>(src, 1, false, dst, 1, s, g, G);
+    } else {
+        const bool chan = (s + 1 == c.lgN);
+        const uint32_t* src = chan ? c.chan : c.spill + scl_spill_woff(c, s + 1) + slot;
+        const int ss = chan ? 1 : 32;
+        if (s < c.smemStages) {
+            uint32_t* dst = c.llr + q * c.slotW + llr_woff(s);
+            if (ISG) scl_g_words<true, false>(src, ss, chan, lb, dst, 1, s, g, G);
+            else scl_f_words<true, false>(src, ss, chan, dst, 1, s, g, G);
+        } else {
+            uint32_t* dst = c.spill + scl_spill_woff(c, s) + q;
+            if (ISG) scl_g_words<true, true>(src, ss, chan, lb, dst, 32, s, g, G);
+            else scl_f_words<true, true>(src, ss, chan, dst, 32, s, g, G);
+        }
     }
     scl_set_own(c.llrPtr, s, c.gl);
     __syncwarp();
@@ -170,10 +219,11 @@ POLAR_DEV void scl_op_g(SclCtx& c, int s, int lgP)
 template <int L>
 POLAR_DEV void scl_op_combine(SclCtx& c, int s, int lgP, bool isRight)
 {
+    if (s + 1 == c.lgN) return; // the root is assembled by the epilogue, straight from its two halves
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const uint32_t* left = c.bits + scl_slot_of(c, c.lbPtr, s, q, lgG) * c.bitSlotW + bit_woff(s);
-    const uint32_t* right = c.bits + q * c.bitSlotW + c.bitBW + bit_woff(s);
-    uint32_t* out = c.bits + q * c.bitSlotW + (isRight ? c.bitBW : 0) + bit_woff(s + 1);
+    const uint32_t* left = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q), s);
+    const uint32_t* right = scl_bits_b(c, q, s);
+    uint32_t* out = scl_bits_out(c, q, s + 1, isRight);
     if (s >= 5) {
         const int hw = 1 << (s - 5);
         for (int j = g; j < hw; j += G) {
@@ -218,19 +268,14 @@ POLAR_DEV void scl_weak_search(const Words& src, int s, int lgG, int g, int (&va
         }
     }
     uint32_t tail[K];
-    if (lgG == 0) {
 #pragma unroll
-        for (int r = 0; r < K; ++r) tail[r] = T[r];
-    } else {
+    for (int r = 0; r < K; ++r) {
+        const uint32_t gm = group_min(T[0], lgG);
+        tail[r] = gm;
+        if (T[0] == gm) { // keys are unique: exactly one lane pops (or all pop the sentinel)
 #pragma unroll
-        for (int r = 0; r < K; ++r) {
-            const uint32_t gm = group_min(T[0], lgG);
-            tail[r] = gm;
-            if (T[0] == gm) { // keys are unique: exactly one lane pops (or all pop the sentinel)
-#pragma unroll
-                for (int t = 0; t + 1 < K; ++t) T[t] = T[t + 1];
-                T[K - 1] = 0xFFFFFFFFu;
-            }
+            for (int t = 0; t + 1 < K; ++t) T[t] = T[t + 1];
+            T[K - 1] = 0xFFFFFFFFu;
         }
     }
     // head: elements 0..3 can be displaced by the swaps; simulate the selection sort on them
@@ -281,54 +326,45 @@ POLAR_DEV void scl_weak_search(const Words& src, int s, int lgG, int g, int (&va
 // Keep the nOut best of M = P*F candidates in the reference's order (simplePartialSortDescending,
 // arrayfuncs.h:161-183: selection sort that SWAPS the displaced element to the winner's place, strict >,
 // so ties go to the lower current position).  Lane q < P of the group holds the candidates at list
-// positions q*F .. q*F+F-1.  Out (lane j < nOut of the group): metric and original candidate index of
-// list entry j.
-template <int L, int LGF>
-POLAR_DEV void scl_select(const SclCtx& c, const int (&cand)[1 << LGF], int lgP, int nOut, int& outMet, int& outIdx)
+// positions q*F .. q*F+F-1, F = 2^lgF <= FMAX (unused registers hold key 0).  Out (lane j < nOut of the
+// group): metric and original candidate index of list entry j.
+template <int L, int FMAX>
+POLAR_DEV void scl_select(const SclCtx& c, const int (&cand)[FMAX], int lgF, int lgP, int nOut, int& outMet, int& outIdx)
 {
-    constexpr int F = 1 << LGF;
-    const int gl = c.gl;
-    uint32_t key[F];
-    int orig[F];
+    const int gl = c.gl, F = 1 << lgF;
+    uint32_t key[FMAX];
+    int orig[FMAX];
 #pragma unroll
-    for (int k = 0; k < F; ++k) {
-        const int pos = gl * F + k;
-        key[k] = gl < (1 << lgP) ? (((uint32_t)(cand[k] + SCL_METRIC_BIAS) << 8) | (uint32_t)(255 - pos)) : 0u;
+    for (int k = 0; k < FMAX; ++k) {
+        const int pos = (gl << lgF) + k;
+        key[k] = (gl < (1 << lgP) && k < F) ? (((uint32_t)(cand[k] + SCL_METRIC_BIAS) << 8) | (uint32_t)(255 - pos)) : 0u;
         orig[k] = pos;
     }
     outMet = 0;
     outIdx = 0;
-#pragma unroll(L <= 8 ? L : 1)
-    for (int i = 0; i < L; ++i) {
-        if (i >= nOut) break;
+#pragma unroll 1
+    for (int i = 0; i < nOut; ++i) {
         uint32_t m = key[0];
 #pragma unroll
-        for (int k = 1; k < F; ++k) m = max(m, key[k]);
+        for (int k = 1; k < FMAX; ++k) m = max(m, key[k]);
         const uint32_t best = list_max<L>(m);
-        const int pos = 255 - (int)(best & 255u), wl = pos >> LGF, wk = pos & (F - 1);
-        const int il = i >> LGF, ik = i & (F - 1);
+        const int pos = 255 - (int)(best & 255u), wl = pos >> lgF, wk = pos & (F - 1);
+        const int il = i >> lgF, ik = i & (F - 1);
         int wo = orig[0], io = orig[0];
         uint32_t ikl = key[0];
 #pragma unroll
-        for (int k = 1; k < F; ++k) {
+        for (int k = 1; k < FMAX; ++k) {
             if (k == wk) wo = orig[k];
             if (k == ik) { io = orig[k]; ikl = key[k]; }
         }
         const int widx = __shfl_sync(FULL_MASK, wo, c.fb + wl);
         const uint32_t ikey = __shfl_sync(FULL_MASK, ikl, c.fb + il); // the element now at position i
         const int iidx = __shfl_sync(FULL_MASK, io, c.fb + il);
-        if (gl == wl) { // it moves to the winner's place ...
+        const uint32_t moved = (ikey & ~255u) | (uint32_t)(255 - pos);
 #pragma unroll
-            for (int k = 0; k < F; ++k)
-                if (k == wk) {
-                    key[k] = (ikey & ~255u) | (uint32_t)(255 - pos);
-                    orig[k] = iidx;
-                }
-        }
-        if (gl == il) { // ... and position i is final
-#pragma unroll
-            for (int k = 0; k < F; ++k)
-                if (k == ik) key[k] = 0u;
+        for (int k = 0; k < FMAX; ++k) {
+            if (gl == wl && k == wk) { key[k] = moved; orig[k] = iidx; } // it moves to the winner's place ...
+            if (gl == il && k == ik) key[k] = 0u;                        // ... and position i is final
         }
         if (gl == i) {
             outMet = (int)(best >> 8) - SCL_METRIC_BIAS;
@@ -371,7 +407,7 @@ template <int L>
 POLAR_DEV void scl_leaf_r0(SclCtx& c, int s, int lgP, bool isRight)
 {
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
+    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
     int acc = 0;
     if (s >= 2) {
         const int words = 1 << (s - 2);
@@ -382,7 +418,7 @@ POLAR_DEV void scl_leaf_r0(SclCtx& c, int s, int lgP, bool isRight)
     acc = group_add(acc, lgG);
     const int pun = __shfl_sync(FULL_MASK, acc, c.fb + ((c.gl << lgG) & (L - 1)));
     if (c.gl < (1 << lgP)) c.metric += pun;
-    uint32_t* out = c.bits + q * c.bitSlotW + (isRight ? c.bitBW : 0) + bit_woff(s);
+    uint32_t* out = scl_bits_out(c, q, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     for (int j = g; j < nbw; j += G) out[j] = 0u;
     scl_finish_leaf(c, s, isRight);
@@ -395,7 +431,7 @@ POLAR_DEV void scl_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
 {
     constexpr int lgL = Log2<L>::v;
     const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
+    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
     int neg = 0, pos = 0;
     if (s >= 2) {
         const int words = 1 << (s - 2);
@@ -417,11 +453,11 @@ POLAR_DEV void scl_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
     const int cand[2] = { c.metric + neg, c.metric - pos };
     const int lgPo = min(lgL, lgP + 1);
     int outMet, outIdx;
-    scl_select<L, 1>(c, cand, lgP, 1 << lgPo, outMet, outIdx);
+    scl_select<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
     scl_adopt(c, outMet, (outIdx >> 1) & (L - 1));
     const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
     const int kq = __shfl_sync(FULL_MASK, outIdx & 1, c.fb + qo);
-    uint32_t* out = c.bits + qo * c.bitSlotW + (isRight ? c.bitBW : 0) + bit_woff(s);
+    uint32_t* out = scl_bits_out(c, qo, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     const uint32_t full = s >= 5 ? 0xFFFFFFFFu : (1u << (1 << s)) - 1u;
     for (int j = go; j < nbw; j += Go) out[j] = kq ? full : 0u;
@@ -434,14 +470,10 @@ POLAR_DEV void scl_write_flipped(SclCtx& c, int s, int lgPo, bool isRight, uint3
                                  uint32_t pk23)
 {
     const int lgGo = Log2<L>::v - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
-    uint32_t fm = flipMask, p01 = pk01, p23 = pk23;
-    if (lgGo) {
-        fm = __shfl_sync(FULL_MASK, fm, c.fb + qo);
-        p01 = __shfl_sync(FULL_MASK, p01, c.fb + qo);
-        p23 = __shfl_sync(FULL_MASK, p23, c.fb + qo);
-    }
-    const Words srcn = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo, lgGo)); // through the adopted vector
-    uint32_t* out = c.bits + qo * c.bitSlotW + (isRight ? c.bitBW : 0) + bit_woff(s);
+    const uint32_t fm = __shfl_sync(FULL_MASK, flipMask, c.fb + qo);
+    const uint32_t p01 = __shfl_sync(FULL_MASK, pk01, c.fb + qo), p23 = __shfl_sync(FULL_MASK, pk23, c.fb + qo);
+    const Words srcn = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo)); // through the adopted vector
+    uint32_t* out = scl_bits_out(c, qo, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     const uint32_t f[4] = { p01 & 0xFFFFu, p01 >> 16, p23 & 0xFFFFu, p23 >> 16 };
     for (int j = go; j < nbw; j += Go) {
@@ -454,45 +486,23 @@ POLAR_DEV void scl_write_flipped(SclCtx& c, int s, int lgPo, bool isRight, uint3
     scl_finish_leaf(c, s, isRight);
 }
 
-// RateOne: scl_fip_char.cpp:423-505
+// RateOne (scl_fip_char.cpp:423-505) and SPC (:583-726) share one routine: both look for the weakest LLRs,
+// fork into 4 / 8 candidates that flip subsets of them, prune, and write sign(llr) with the chosen flips.
 template <int L>
-POLAR_DEV void scl_leaf_r1(SclCtx& c, int s, int lgP, bool isRight)
+POLAR_DEV void scl_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSpc)
 {
     constexpr int lgL = Log2<L>::v;
     const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
-    int val[2], idx[2];
-    scl_weak_search<2>(src, s, lgG, g, val, idx);
-    const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
-    const int a0 = __shfl_sync(FULL_MASK, val[0], srcLane), a1 = __shfl_sync(FULL_MASK, val[1], srcLane);
-    const uint32_t pk = __shfl_sync(FULL_MASK, (uint32_t)idx[0] | ((uint32_t)idx[1] << 16), srcLane);
-    const int m = c.metric;
-    const int cand[4] = { m, m - a0, m - a1, m - a0 - a1 };
-    const int lgPo = min(lgL, lgP + 2);
-    int outMet, outIdx;
-    scl_select<L, 2>(c, cand, lgP, 1 << lgPo, outMet, outIdx);
-    const int srcPath = (outIdx >> 2) & (L - 1);
-    const uint32_t pkSrc = __shfl_sync(FULL_MASK, pk, c.fb + srcPath);
-    scl_adopt(c, outMet, srcPath);
-    scl_write_flipped<L>(c, s, lgPo, isRight, (uint32_t)(outIdx & 3), pkSrc, 0u);
-}
-
-// SPC: scl_fip_char.cpp:583-726
-template <int L>
-POLAR_DEV void scl_leaf_spc(SclCtx& c, int s, int lgP, bool isRight)
-{
-    constexpr int lgL = Log2<L>::v;
-    const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
+    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
     uint32_t px = 0;
-    {
+    if (isSpc) {
         const int words = 1 << (s - 2); // an SPC leaf has at least 4 elements
         for (int w = g; w < words; w += G) px ^= src(w);
     }
     px = group_xor(px, lgG);
     int par = __popc(px & 0x80808080u) & 1;
     int val[4], idx[4];
-    scl_weak_search<4>(src, s, lgG, g, val, idx);
+    scl_weak_search<4>(src, s, lgG, g, val, idx); // a rate-1 leaf only uses the two weakest
     const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
     const int a0 = __shfl_sync(FULL_MASK, val[0], srcLane), a1 = __shfl_sync(FULL_MASK, val[1], srcLane);
     const int a2 = __shfl_sync(FULL_MASK, val[2], srcLane), a3 = __shfl_sync(FULL_MASK, val[3], srcLane);
@@ -500,17 +510,25 @@ POLAR_DEV void scl_leaf_spc(SclCtx& c, int s, int lgP, bool isRight)
     const uint32_t pk23 = __shfl_sync(FULL_MASK, (uint32_t)idx[2] | ((uint32_t)idx[3] << 16), srcLane);
     par = __shfl_sync(FULL_MASK, par, srcLane);
     int m = c.metric, w = 0;
-    if (par) m -= a0; else w = a0;
-    const int cand[8] = { m,           m - w - a1,  m - w - a2,  m - w - a3,
-                          m - a1 - a2, m - a1 - a3, m - a2 - a3, m - w - a1 - a2 - a3 };
-    const int lgPo = min(lgL, lgP + 3);
+    int cand[8];
+    if (isSpc) {
+        if (par) m -= a0; else w = a0;
+        cand[0] = m;           cand[1] = m - w - a1;  cand[2] = m - w - a2;  cand[3] = m - w - a3;
+        cand[4] = m - a1 - a2; cand[5] = m - a1 - a3; cand[6] = m - a2 - a3; cand[7] = m - w - a1 - a2 - a3;
+    } else {
+        cand[0] = m; cand[1] = m - a0; cand[2] = m - a1; cand[3] = m - a0 - a1;
+        cand[4] = cand[5] = cand[6] = cand[7] = 0;
+    }
+    const int lgF = isSpc ? 3 : 2;
+    const int lgPo = min(lgL, lgP + lgF);
     int outMet, outIdx;
-    scl_select<L, 3>(c, cand, lgP, 1 << lgPo, outMet, outIdx);
-    const int srcPath = (outIdx >> 3) & (L - 1), kind = outIdx & 7;
+    scl_select<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
+    const int srcPath = (outIdx >> lgF) & (L - 1), kind = outIdx & ((1 << lgF) - 1);
     const uint32_t s01 = __shfl_sync(FULL_MASK, pk01, c.fb + srcPath), s23 = __shfl_sync(FULL_MASK, pk23, c.fb + srcPath);
     const int sp = __shfl_sync(FULL_MASK, par, c.fb + srcPath);
-    // flip sets over (i0,i1,i2,i3), one nibble per candidate kind (scl_fip_char.cpp:641-692)
-    const uint32_t fm = ((sp ? 0xEDB78421u : 0xFCA69530u) >> (4 * kind)) & 15u;
+    // flip sets over (i0,i1,i2,i3), one nibble per candidate kind (scl_fip_char.cpp:641-692; :451-470 for rate 1)
+    const uint32_t table = isSpc ? (sp ? 0xEDB78421u : 0xFCA69530u) : 0x3210u;
+    const uint32_t fm = (table >> (4 * kind)) & 15u;
     scl_adopt(c, outMet, srcPath);
     scl_write_flipped<L>(c, s, lgPo, isRight, fm, s01, s23);
 }
@@ -534,15 +552,21 @@ __global__ void __launch_bounds__(256) scl_i8_kernel(const __grid_constant__ Dec
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + c.fb : nullptr;
     c.slotW = p.slotW;
     c.bitBW = p.bitBW;
+    c.bitB1 = p.bitB1;
     c.bitSlotW = p.bitSlotW;
     c.lgN = p.lgN;
-    c.spillStage = p.spillStage;
+    c.smemStages = p.smemStages;
 
-    const long long totalWarps = (long long)gridDim.x * warpsPerBlock;
+    // Every warp of a block walks the same schedule, so the block iterates together (same trip count for all
+    // its warps); with p.lockstep the warps also meet at a barrier before every step: they then fetch the
+    // same instruction lines at the same time, which is what keeps this branchy interpreter out of
+    // instruction-fetch stalls (ncu: stall_no_instruction).
     const long long nQuads = (p.nFrames + FPW - 1) / FPW;
-    for (long long quad = (long long)blockIdx.x * warpsPerBlock + warp; quad < nQuads; quad += totalWarps) {
+    for (long long qb = blockIdx.x; qb * warpsPerBlock < nQuads; qb += gridDim.x) {
+        const bool live = qb * warpsPerBlock + warp < nQuads; // a spare warp redoes the last quad and drops it
+        const long long quad = live ? qb * warpsPerBlock + warp : nQuads - 1;
         const long long myFrame = min(quad * FPW + fi, p.nFrames - 1); // tail lanes redo the last frame
-        c.chan = reinterpret_cast<uint32_t*>(const_cast<int8_t*>(static_cast<const int8_t*>(p.llr) + myFrame * p.N));
+        c.chan = reinterpret_cast<const uint32_t*>(static_cast<const int8_t*>(p.llr) + myFrame * p.N);
         c.metric = 0;
         c.llrPtr = 0ull;
         c.lbPtr = 0ull;
@@ -553,14 +577,15 @@ __global__ void __launch_bounds__(256) scl_i8_kernel(const __grid_constant__ Dec
             if (code == OP_END) break;
             const int s = (int)POLAR_OP_STAGE(op), lgP = (int)POLAR_OP_LGP(op);
             const bool isRight = (POLAR_OP_FLAGS(op) & OPF_RIGHT) != 0;
+            if (p.lockstep) __syncthreads();
             switch (code) {
-            case OP_F: scl_op_f<L>(c, s, lgP); break;
-            case OP_G: scl_op_g<L>(c, s, lgP); break;
+            case OP_F: scl_op_fg<L, false>(c, s, lgP); break;
+            case OP_G: scl_op_fg<L, true>(c, s, lgP); break;
             case OP_COMBINE: scl_op_combine<L>(c, s, lgP, isRight); break;
             case OP_SCL_R0: scl_leaf_r0<L>(c, s, lgP, isRight); lgPfinal = lgP; break;
             case OP_SCL_REP: scl_leaf_rep<L>(c, s, lgP, isRight); lgPfinal = min(lgL, lgP + 1); break;
-            case OP_SCL_R1: scl_leaf_r1<L>(c, s, lgP, isRight); lgPfinal = min(lgL, lgP + 2); break;
-            case OP_SCL_SPC: scl_leaf_spc<L>(c, s, lgP, isRight); lgPfinal = min(lgL, lgP + 3); break;
+            case OP_SCL_R1: scl_leaf_flip<L>(c, s, lgP, isRight, false); lgPfinal = min(lgL, lgP + 2); break;
+            case OP_SCL_SPC: scl_leaf_flip<L>(c, s, lgP, isRight, true); lgPfinal = min(lgL, lgP + 3); break;
             default: break;
             }
         }
@@ -568,33 +593,43 @@ __global__ void __launch_bounds__(256) scl_i8_kernel(const __grid_constant__ Dec
         // The whole warp works on one frame of the quad at a time.
         const int P = 1 << lgPfinal;
         uint32_t* outw = scr;
-        uint32_t* tmp = scr + ((p.K + 31) >> 5);
-        for (int f = 0; f < FPW; ++f) {
+        uint32_t* cw = scr + ((p.K + 31) >> 5);
+        const int top = p.lgN - 1, nW = max(p.N >> 5, 1);
+        const uint32_t slotA = (uint32_t)(c.lbPtr >> (5 * top)) & 31u; // where this lane's path keeps its left half
+        for (int f = 0; f < FPW && live; ++f) {
             const long long frame = quad * FPW + f;
             if (frame >= p.nFrames) break;
             const uint32_t* fbits = base + f * p.frameW + L * p.slotW;
             bool okFlag = false;
             for (int path = 0; path < P; ++path) {
-                const uint32_t* cw = fbits + path * p.bitSlotW + bit_woff(p.lgN); // root bits: array A, own slot
-                if (!p.systematic) {
-                    for (int w = lane; w < max(p.N >> 5, 1); w += 32) tmp[w] = cw[w];
-                    __syncwarp();
-                    warp_polar_transform(tmp, p.N, lane);
-                    cw = tmp;
+                // codeword estimate of this path: the root leaf's bits, or [left ^ right | right] of the two halves
+                const uint32_t sa = __shfl_sync(FULL_MASK, slotA, f * L + path);
+                if (p.rootLeaf) {
+                    const uint32_t* root = fbits + path * p.bitSlotW + bit_woff(p.lgN);
+                    for (int w = lane; w < nW; w += 32) cw[w] = root[w];
+                } else {
+                    const uint32_t* left = fbits + sa * p.bitSlotW + bit_woff(top);
+                    const uint32_t* right = fbits + path * p.bitSlotW + p.bitBW + ((top & 1) ? p.bitB1 : 0);
+                    if (top >= 5) {
+                        const int hw = 1 << (top - 5);
+                        for (int w = lane; w < nW; w += 32) cw[w] = w < hw ? (left[w] ^ right[w]) : right[w - hw];
+                    } else if (lane == 0) {
+                        cw[0] = (left[0] ^ right[0]) | (right[0] << (1 << top));
+                    }
                 }
+                __syncwarp();
+                if (!p.systematic) warp_polar_transform(cw, p.N, lane);
                 const uint32_t syn = gather_info_and_syndrome(p, cw, outw, lane);
                 if (syn == 0u) { okFlag = true; break; }
-                if (!p.crcBits) break;
+                if (!p.crcBits || (path == 0 && P == 1)) break;
+                // remember path 0's decision in case nobody passes (scl_fip_char.cpp:848-853)
+                if (path == 0)
+                    for (int w = lane; w < ((p.K + 31) >> 5); w += 32) cw[nW + w] = outw[w];
+                __syncwarp();
             }
-            if (!okFlag && P > 1) { // fall back to the most likely path
-                const uint32_t* cw = fbits + bit_woff(p.lgN);
-                if (!p.systematic) {
-                    for (int w = lane; w < max(p.N >> 5, 1); w += 32) tmp[w] = cw[w];
-                    __syncwarp();
-                    warp_polar_transform(tmp, p.N, lane);
-                    cw = tmp;
-                }
-                (void)gather_info_and_syndrome(p, cw, outw, lane);
+            if (!okFlag && P > 1 && p.crcBits) { // fall back to the most likely path
+                for (int w = lane; w < ((p.K + 31) >> 5); w += 32) outw[w] = cw[nW + w];
+                __syncwarp();
             }
             store_info(p, frame, outw, lane);
             if (lane == 0) p.ok[frame] = okFlag ? 1 : 0;

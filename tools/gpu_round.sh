@@ -14,10 +14,19 @@ for WL in scl8 fastssc; do
   timeout 300 python bench.py --workload $WL --steps 5 --warmup 3 > $OUT/${TAG}_bench_$WL.json 2> $OUT/${TAG}_bench_$WL.err
   echo "bench $WL rc=$?"; cat $OUT/${TAG}_bench_$WL.json | cut -c1-600
 done
+# optional A/B runs: VARIANTS="scl8:POLAR_CUDA_LOCKSTEP=0 fastssc:POLAR_CUDA_X=1"
+for V in ${VARIANTS:-}; do
+  WL=${V%%:*}; KV=${V#*:}
+  env $KV timeout 300 python bench.py --workload $WL --steps 5 --warmup 3 > $OUT/${TAG}_bench_${WL}_${KV}.json 2> $OUT/${TAG}_bench_${WL}_${KV}.err
+  echo "variant $WL $KV rc=$?"; python -c "import json,sys; d=json.load(open('$OUT/${TAG}_bench_${WL}_${KV}.json')); print(d['value'], d['e2e']['value'], d['config']['warps_per_block'], d['config']['blocks_per_sm'])"
+done
 if [ $RC -eq 0 ] && [ "${NCU:-1}" = "1" ]; then
-  CMD="python bench.py --workload ${NCU_WL:-scl8} --steps 2 --warmup 1 --frames ${NCU_FRAMES:-131072} --e2e-frames 8192"
-  $CMD > $OUT/${TAG}_ncu_plain.log 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
-  ncu --set full --clock-control none --import-source on -k regex:${NCU_KERNEL:-scl_i8_kernel} -s 1 -c 1 -o $OUT/${TAG}_prof -f $CMD > $OUT/${TAG}_ncu_full.log 2>&1
-  echo "ncu rc=$?"
+  for WL in ${NCU_WLS:-scl8 fastssc}; do
+    if [ $WL = scl8 ]; then KRN=scl_i8_kernel; FR=131072; else KRN=fastssc_i8_kernel; FR=262144; fi
+    CMD="python bench.py --workload $WL --steps 2 --warmup 1 --frames $FR --e2e-frames 8192"
+    $CMD > $OUT/${TAG}_ncu_plain_$WL.log 2>&1 &&
+    ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches_$WL.csv $CMD > $OUT/${TAG}_ncu_list_$WL.log 2>&1
+    ncu --set full --clock-control none --import-source on -k regex:$KRN -s 1 -c 1 -o $OUT/${TAG}_prof_$WL -f $CMD > $OUT/${TAG}_ncu_full_$WL.log 2>&1
+    echo "ncu $WL rc=$?"
+  done
 fi
