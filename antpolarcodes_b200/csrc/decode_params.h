@@ -10,6 +10,7 @@ struct DecodeParams {
     uint8_t* ok;              // nFrames
     const uint16_t* infoPos;  // K code positions of the information bits, ascending
     const uint32_t* crcTab;   // K syndrome contributions (see crc_host.h)
+    const uint32_t* runs;     // Fast-SSC: runs of consecutive information positions (pos | len << 16)
     uint32_t* spill;          // L2-resident scratch for the top LLR stage (list decoders), or null
     long long nFrames;
     uint32_t crcInit;         // syndrome of the all-zero info block
@@ -29,7 +30,7 @@ struct DecodeParams {
     int spillWarpW;           // words of `spill` per resident warp
     int lockstep;             // warps of a block meet at a barrier before every schedule step
     // Fast-SSC (one frame per thread): rows of 32 words
-    int llrRows, bitRows, tileRow, outRow, chanRow;
+    int llrRows, bitRows, tileRow, outRow, chanRow, nRuns;
 };
 
 // word offset of stage s inside an llr slot (stage s block = 2^s int8, at least one word)

@@ -24,21 +24,29 @@ struct ScCtx {
     uint32_t* sm;          // this warp's shared memory
     const uint32_t* chan;  // channel rows (global), N/4 words per frame
     long long frame0, lastFrame;
+    uint32_t* spill;       // this warp's rows of the L2-resident scratch (stages >= smemStages), or null
     int lane, lgN, nw;     // nw = N/4
-    int bitRow, tileRow, chanRow;
+    int bitRow, tileRow, chanRow, smemStages;
 };
 
 #define SC_ROW(c, row) (c).sm[((row) << 5) + (c).lane]
 
-// LLR block of stage s: rows of the stage buffers, or the staged channel (degenerate one-leaf codes)
-POLAR_DEV int sc_llr_row(const ScCtx& c, int s) { return s == c.lgN ? c.chanRow : llr_woff(s); }
+// LLR block of stage s as a pointer to the lane's word 0 (word w at p[w << 5]): rows of the shared-memory
+// stage buffers, rows of the spill scratch (same [row][lane] layout, coalesced 128-byte lines), or the staged
+// channel (degenerate one-leaf codes).
+POLAR_DEV uint32_t* sc_stage(const ScCtx& c, int s)
+{
+    if (s == c.lgN) return c.sm + (c.chanRow << 5) + c.lane;
+    if (s >= c.smemStages) return c.spill + ((llr_woff(s) - llr_woff(c.smemStages)) << 5) + c.lane;
+    return c.sm + (llr_woff(s) << 5) + c.lane;
+}
 
 // Source views of a parent block split in halves a = [0, words), b = [words, 2*words)
-struct ScRows { // both halves in the lane's own rows
-    const ScCtx& c;
-    int row, words;
-    POLAR_DEV uint32_t a(int w) const { return SC_ROW(c, row + w); }
-    POLAR_DEV uint32_t b(int w) const { return SC_ROW(c, row + words + w); }
+struct ScRows { // both halves in the lane's own rows (shared memory or spill)
+    const uint32_t* p;
+    int words;
+    POLAR_DEV uint32_t a(int w) const { return p[w << 5]; }
+    POLAR_DEV uint32_t b(int w) const { return p[(w + words) << 5]; }
 };
 struct ScTiles { // a chunk [w0, w0+cw) of both halves in the transpose tiles
     const uint32_t* ta;
@@ -52,48 +60,59 @@ struct ScTiles { // a chunk [w0, w0+cw) of both halves in the transpose tiles
 POLAR_DEV void sc_load_tile(const ScCtx& c, uint32_t* tile, int w0, int cw)
 {
     if (c.lane < cw) {
-#pragma unroll 8
-        for (int r = 0; r < 32; ++r) {
-            const long long f = min(c.frame0 + r, c.lastFrame);
-            tile[r * 33 + c.lane] = __ldg(c.chan + f * c.nw + w0 + c.lane);
+        const uint32_t* src = c.chan + c.frame0 * c.nw + w0 + c.lane;
+        if (c.frame0 + 31 <= c.lastFrame) { // 16 row loads in flight before the first store
+#pragma unroll 1
+            for (int r0 = 0; r0 < 32; r0 += 16) {
+                uint32_t v[16];
+#pragma unroll
+                for (int r = 0; r < 16; ++r) v[r] = __ldg(src + (long long)(r0 + r) * c.nw);
+#pragma unroll
+                for (int r = 0; r < 16; ++r) tile[(r0 + r) * 33 + c.lane] = v[r];
+            }
+        } else {
+            for (int r = 0; r < 32; ++r) {
+                const long long f = min(c.frame0 + r, c.lastFrame);
+                tile[r * 33 + c.lane] = __ldg(c.chan + f * c.nw + w0 + c.lane);
+            }
         }
     }
 }
 
 // ---- per-thread steps over the word range [wb, we) of a block of `words` words per half
 template <class Src>
-POLAR_DEV void sc_f_range(ScCtx& c, const Src& src, int dstRow, int wb, int we)
+POLAR_DEV void sc_f_range(const Src& src, uint32_t* dst, int wb, int we)
 {
     int w = wb;
     for (; w + 3 < we; w += 4) {
         const uint32_t a0 = src.a(w), a1 = src.a(w + 1), a2 = src.a(w + 2), a3 = src.a(w + 3);
         const uint32_t b0 = src.b(w), b1 = src.b(w + 1), b2 = src.b(w + 2), b3 = src.b(w + 3);
-        SC_ROW(c, dstRow + w) = f4(a0, b0);
-        SC_ROW(c, dstRow + w + 1) = f4(a1, b1);
-        SC_ROW(c, dstRow + w + 2) = f4(a2, b2);
-        SC_ROW(c, dstRow + w + 3) = f4(a3, b3);
+        dst[(w) << 5] = f4(a0, b0);
+        dst[(w + 1) << 5] = f4(a1, b1);
+        dst[(w + 2) << 5] = f4(a2, b2);
+        dst[(w + 3) << 5] = f4(a3, b3);
     }
-    for (; w < we; ++w) SC_ROW(c, dstRow + w) = f4(src.a(w), src.b(w));
+    for (; w < we; ++w) dst[(w) << 5] = f4(src.a(w), src.b(w));
 }
 
 template <class Src>
-POLAR_DEV void sc_adds_range(ScCtx& c, const Src& src, int dstRow, int wb, int we)
+POLAR_DEV void sc_adds_range(const Src& src, uint32_t* dst, int wb, int we)
 {
     int w = wb;
     for (; w + 3 < we; w += 4) {
         const uint32_t a0 = src.a(w), a1 = src.a(w + 1), a2 = src.a(w + 2), a3 = src.a(w + 3);
         const uint32_t b0 = src.b(w), b1 = src.b(w + 1), b2 = src.b(w + 2), b3 = src.b(w + 3);
-        SC_ROW(c, dstRow + w) = adds4(a0, b0);
-        SC_ROW(c, dstRow + w + 1) = adds4(a1, b1);
-        SC_ROW(c, dstRow + w + 2) = adds4(a2, b2);
-        SC_ROW(c, dstRow + w + 3) = adds4(a3, b3);
+        dst[(w) << 5] = adds4(a0, b0);
+        dst[(w + 1) << 5] = adds4(a1, b1);
+        dst[(w + 2) << 5] = adds4(a2, b2);
+        dst[(w + 3) << 5] = adds4(a3, b3);
     }
-    for (; w < we; ++w) SC_ROW(c, dstRow + w) = adds4(src.a(w), src.b(w));
+    for (; w < we; ++w) dst[(w) << 5] = adds4(src.a(w), src.b(w));
 }
 
 // left bits of the block start at absolute bit position pos
 template <class Src>
-POLAR_DEV void sc_g_range(ScCtx& c, const Src& src, int dstRow, int pos, int wb, int we)
+POLAR_DEV void sc_g_range(ScCtx& c, const Src& src, uint32_t* dst, int pos, int wb, int we)
 {
     int w = wb;
     if (((we - wb) & 7) == 0 && (pos & 31) == 0) { // whole bit words: one load per 8 LLR words
@@ -103,14 +122,14 @@ POLAR_DEV void sc_g_range(ScCtx& c, const Src& src, int dstRow, int pos, int wb,
 #pragma unroll
             for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
 #pragma unroll
-            for (int t = 0; t < 8; ++t) SC_ROW(c, dstRow + w + t) = g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t)));
+            for (int t = 0; t < 8; ++t) dst[(w + t) << 5] = g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t)));
         }
         return;
     }
     for (; w < we; ++w) {
         const int bp = pos + 4 * w;
         const uint32_t nib = SC_ROW(c, c.bitRow + (bp >> 5)) >> (bp & 31);
-        SC_ROW(c, dstRow + w) = g4(src.a(w), src.b(w), nibble_to_bytemask(nib));
+        dst[(w) << 5] = g4(src.a(w), src.b(w), nibble_to_bytemask(nib));
     }
 }
 
@@ -157,15 +176,15 @@ POLAR_DEV void sc_g_r1_short(ScCtx& c, const Src& src, int s, int pos)
 
 // ---- bit helpers (block of n = 2^s bits at absolute position pos, pos % n == 0)
 // sign bits of LLR rows [row, ..) of a block of n values, bit word j
-POLAR_DEV uint32_t sc_sign_word(const ScCtx& c, int row, int s, int j)
+POLAR_DEV uint32_t sc_sign_word(const uint32_t* src, int s, int j)
 {
-    if (s < 2) return sign_nibble(SC_ROW(c, row)) & ((1u << (1 << s)) - 1u);
+    if (s < 2) return sign_nibble(src[0]) & ((1u << (1 << s)) - 1u);
     const int words = 1 << (s - 2);
     uint32_t w = 0;
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
         const int lw = 8 * j + t;
-        if (lw < words) w |= sign_nibble(SC_ROW(c, row + lw)) << (4 * t);
+        if (lw < words) w |= sign_nibble(src[(lw) << 5]) << (4 * t);
     }
     return w;
 }
@@ -187,11 +206,11 @@ POLAR_DEV void sc_fill_bits(ScCtx& c, int s, int pos, uint32_t pattern)
     for (int j = 0; j < nbw; ++j) sc_put_bits(c, s, pos, j, pattern);
 }
 // bits = sign(LLR rows) with an optional flipped position; dup: the same bits again in [pos+n, pos+2n)
-POLAR_DEV void sc_put_signs(ScCtx& c, int row, int s, int pos, bool dup, uint32_t flipIdx, bool doFlip)
+POLAR_DEV void sc_put_signs(ScCtx& c, const uint32_t* src, int s, int pos, bool dup, uint32_t flipIdx, bool doFlip)
 {
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     for (int j = 0; j < nbw; ++j) {
-        uint32_t v = sc_sign_word(c, row, s, j);
+        uint32_t v = sc_sign_word(src, s, j);
         if (doFlip && (int)(flipIdx >> 5) == j) v ^= 1u << (flipIdx & 31u);
         sc_put_bits(c, s, pos, j, v);
         if (dup) sc_put_bits(c, s, pos + (1 << s), j, v);
@@ -201,23 +220,23 @@ POLAR_DEV void sc_put_signs(ScCtx& c, int row, int s, int pos, bool dup, uint32_
 // ---- leaves
 // acc[t] (t < 8) = byte lanes 4t..4t+3 of the reference's 32-byte accumulator:
 // acc[j] = sat(..sat(sat(0 + x[j]) + x[32+j]).. ) (fastssc_fip_char.cpp:227-232)
-POLAR_DEV void sc_rep_acc(const ScCtx& c, int row, int s, uint32_t (&acc)[8])
+POLAR_DEV void sc_rep_acc(const uint32_t* src, int s, uint32_t (&acc)[8])
 {
     const int words = s >= 2 ? 1 << (s - 2) : 1;
 #pragma unroll
     for (int t = 0; t < 8; ++t) acc[t] = 0u;
     if (s < 2) {
-        acc[0] = SC_ROW(c, row) & (s == 1 ? 0xFFFFu : 0xFFu);
+        acc[0] = src[0] & (s == 1 ? 0xFFFFu : 0xFFu);
     } else if (words < 8) {
 #pragma unroll
         for (int t = 0; t < 4; ++t)
-            if (t < words) acc[t] = SC_ROW(c, row + t); // sat(0 + x) = x
+            if (t < words) acc[t] = src[(t) << 5]; // sat(0 + x) = x
     } else {
 #pragma unroll
-        for (int t = 0; t < 8; ++t) acc[t] = SC_ROW(c, row + t);
+        for (int t = 0; t < 8; ++t) acc[t] = src[(t) << 5];
         for (int v = 8; v < words; v += 8) {
 #pragma unroll
-            for (int t = 0; t < 8; ++t) acc[t] = adds4(acc[t], SC_ROW(c, row + v + t));
+            for (int t = 0; t < 8; ++t) acc[t] = adds4(acc[t], src[(v + t) << 5]);
         }
     }
 }
@@ -225,12 +244,12 @@ POLAR_DEV void sc_rep_acc(const ScCtx& c, int row, int s, uint32_t (&acc)[8])
 // SPC decision on rows [row, ..) holding n = 2^s values (fastssc_fip_char.cpp:274-319): returns whether a
 // bit flips and which.  Long form = threshold search (start 127, strict <), short form = plain first
 // minimum with +127 pads.  The flip is an arithmetic negate, so it is void for 0 and -128.
-POLAR_DEV bool sc_spc_decide(const ScCtx& c, int row, int s, bool longForm, uint32_t& flipIdx)
+POLAR_DEV bool sc_spc_decide(const uint32_t* src, int s, bool longForm, uint32_t& flipIdx)
 {
     const int n = 1 << s, words = n >= 4 ? n >> 2 : 1;
     uint32_t px = 0, best = 0xFFFFFFFFu;
     for (int w = 0; w < words; ++w) {
-        uint32_t x = SC_ROW(c, row + w);
+        uint32_t x = src[(w) << 5];
         if (s < 2) x &= 0xFFFFu;
         px ^= x;
         const uint32_t m = uabs4(x); // |x| as unsigned, |-128| = 128
@@ -246,7 +265,7 @@ POLAR_DEV bool sc_spc_decide(const ScCtx& c, int row, int s, bool longForm, uint
     } else if (mv > 127u && n < 32) {
         flip = false; // a +127 pad wins: the negate lands outside the block
     }
-    const uint32_t wv = SC_ROW(c, row + (int)(mi >> 2));
+    const uint32_t wv = src[(int)(mi >> 2) << 5];
     const int v = (int)(int8_t)(wv >> (8 * (mi & 3u)));
     if (v == 0 || v == -128) flip = false;
     flipIdx = mi;
@@ -288,6 +307,8 @@ __global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__
     c.bitRow = p.llrRows;
     c.tileRow = p.tileRow;
     c.chanRow = p.chanRow;
+    c.smemStages = p.smemStages;
+    c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW : nullptr;
     c.lastFrame = p.nFrames - 1;
     uint32_t* tileA = c.sm + (p.tileRow << 5);
     uint32_t* tileB = tileA + 33 * 32;
@@ -320,24 +341,24 @@ __global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__
             case OP_G:      // fip_char.h:93-110
             case OP_G_0R:   // fip_char.h:112-131
             case OP_G_R1: { // fastssc_fip_char.cpp:436-474
-                const int dstRow = llr_woff(s);
+                uint32_t* dst = sc_stage(c, s);
                 if (s < 2) { // block of 2: both halves in one word (never the channel: N >= 8)
-                    const ScRows src{ c, sc_llr_row(c, s + 1), 1 };
+                    const ScRows src{ sc_stage(c, s + 1), 1 };
                     const uint32_t x = src.a(0);
-                    if (code == OP_F) SC_ROW(c, dstRow) = f4(x, x >> 16);
-                    else if (code == OP_G_0R) SC_ROW(c, dstRow) = adds4(x, x >> 16);
+                    if (code == OP_F) dst[0] = f4(x, x >> 16);
+                    else if (code == OP_G_0R) dst[0] = adds4(x, x >> 16);
                     else if (code == OP_G) {
                         const uint32_t nib = (SC_ROW(c, c.bitRow + (pos >> 5)) >> (pos & 31)) & 3u;
-                        SC_ROW(c, dstRow) = g4(x, x >> 16, nibble_to_bytemask(nib));
+                        dst[0] = g4(x, x >> 16, nibble_to_bytemask(nib));
                     } else sc_g_r1_short(c, src, s, pos);
                     break;
                 }
                 const int words = 1 << (s - 2);
                 if (!top) {
-                    const ScRows src{ c, sc_llr_row(c, s + 1), words };
-                    if (code == OP_F) sc_f_range(c, src, dstRow, 0, words);
-                    else if (code == OP_G_0R) sc_adds_range(c, src, dstRow, 0, words);
-                    else if (code == OP_G) sc_g_range(c, src, dstRow, pos, 0, words);
+                    const ScRows src{ sc_stage(c, s + 1), words };
+                    if (code == OP_F) sc_f_range(src, dst, 0, words);
+                    else if (code == OP_G_0R) sc_adds_range(src, dst, 0, words);
+                    else if (code == OP_G) sc_g_range(c, src, dst, pos, 0, words);
                     else if (s >= 5) sc_g_r1_range(c, src, s, pos, 0, words);
                     else sc_g_r1_short(c, src, s, pos);
                 } else { // words == halfW
@@ -346,9 +367,9 @@ __global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__
                         sc_load_tile(c, tileB, halfW + w0, cw);
                         __syncwarp();
                         const ScTiles src{ myA, myB, w0 };
-                        if (code == OP_F) sc_f_range(c, src, dstRow, w0, w0 + cw);
-                        else if (code == OP_G_0R) sc_adds_range(c, src, dstRow, w0, w0 + cw);
-                        else if (code == OP_G) sc_g_range(c, src, dstRow, pos, w0, w0 + cw);
+                        if (code == OP_F) sc_f_range(src, dst, w0, w0 + cw);
+                        else if (code == OP_G_0R) sc_adds_range(src, dst, w0, w0 + cw);
+                        else if (code == OP_G) sc_g_range(c, src, dst, pos, w0, w0 + cw);
                         else if (s >= 5) sc_g_r1_range(c, src, s, pos, w0, w0 + cw);
                         else sc_g_r1_short(c, src, s, pos); // halfW <= 4: a single chunk
                         __syncwarp();
@@ -382,10 +403,10 @@ __global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__
                 break;
             }
             case OP_SC_R0: sc_fill_bits(c, s, pos, 0u); break;
-            case OP_SC_R1: sc_put_signs(c, sc_llr_row(c, s), s, pos, false, 0u, false); break;
+            case OP_SC_R1: sc_put_signs(c, sc_stage(c, s), s, pos, false, 0u, false); break;
             case OP_SC_REP: { // fastssc_fip_char.cpp:225-240,265-272 + reduce_adds_epi8
                 uint32_t a[8];
-                sc_rep_acc(c, sc_llr_row(c, s), s, a);
+                sc_rep_acc(sc_stage(c, s), s, a);
 #pragma unroll
                 for (int t = 0; t < 4; ++t) a[t] = adds4(a[t], a[t + 4]);
                 a[0] = adds4(a[0], a[2]);
@@ -398,7 +419,7 @@ __global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__
             }
             case OP_SC_REP2: { // fastssc_fip_char.cpp:249-263 + half_reduce_adds_epi8 (n >= 32)
                 uint32_t a[8];
-                sc_rep_acc(c, sc_llr_row(c, s), s, a);
+                sc_rep_acc(sc_stage(c, s), s, a);
 #pragma unroll
                 for (int t = 0; t < 4; ++t) a[t] = adds4(a[t], a[t + 4]);
                 a[0] = adds4(a[0], a[2]);
@@ -410,29 +431,29 @@ __global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__
                 break;
             }
             case OP_SC_SPC: { // fastssc_fip_char.cpp:274-319
-                const int row = sc_llr_row(c, s);
+                const uint32_t* src = sc_stage(c, s);
                 uint32_t fi;
-                const bool flip = sc_spc_decide(c, row, s, longForm, fi);
-                sc_put_signs(c, row, s, pos, false, fi, flip);
+                const bool flip = sc_spc_decide(src, s, longForm, fi);
+                sc_put_signs(c, src, s, pos, false, fi, flip);
                 break;
             }
             case OP_SC_ZERO_SPC:   // fastssc_fip_char.cpp:321-388
             case OP_SC_ZERO_ONE: { // fastssc_fip_char.cpp:390-399
-                const int hs = s - 1, yRow = llr_woff(hs); // y = sat(l + r) goes to the (free) child stage
+                // y = sat(l + r) goes to the (free) child stage, or to row 0 when that stage is spilled
+                const int hs = s - 1;
+                uint32_t* y = hs < c.smemStages ? sc_stage(c, hs) : c.sm + c.lane;
+                const uint32_t* src = sc_stage(c, s);
                 if (hs >= 2) {
                     const int words = 1 << (hs - 2);
-                    if (s == c.lgN && c.chanRow < 0) { // cannot happen: one-leaf codes stage the channel
-                    }
-                    const ScRows src{ c, sc_llr_row(c, s), words };
-                    sc_adds_range(c, src, yRow, 0, words);
+                    sc_adds_range(ScRows{ src, words }, y, 0, words);
                 } else {
-                    const uint32_t x = SC_ROW(c, sc_llr_row(c, s));
-                    SC_ROW(c, yRow) = adds4(x, x >> 16) & 0xFFFFu;
+                    const uint32_t x = src[0];
+                    y[0] = adds4(x, x >> 16) & 0xFFFFu;
                 }
                 uint32_t fi = 0;
                 bool flip = false;
-                if (code == OP_SC_ZERO_SPC) flip = sc_spc_decide(c, yRow, hs, longForm, fi);
-                sc_put_signs(c, yRow, hs, pos, true, fi, flip);
+                if (code == OP_SC_ZERO_SPC) flip = sc_spc_decide(y, hs, longForm, fi);
+                sc_put_signs(c, y, hs, pos, true, fi, flip);
                 break;
             }
             default: break;
@@ -447,7 +468,24 @@ __global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__
         int curW = -1;
         uint32_t curV = 0;
         const bool wordOut = (p.kb & 3) == 0;
-        for (int k = 0; k < p.K; ++k) {
+        const bool byRuns = wordOut && !p.crcBits && p.nRuns > 0;
+        if (byRuns) { // information bits come in runs of consecutive positions: move a run at a time
+            int outBits = 0;
+            for (int r = 0; r < p.nRuns; ++r) {
+                const uint32_t run = __ldg(p.runs + r);
+                const int pos = (int)(run & 0xFFFFu), len = (int)(run >> 16);
+                if ((pos >> 5) != curW) {
+                    curW = pos >> 5;
+                    curV = SC_ROW(c, c.bitRow + curW);
+                }
+                const uint32_t rev = __brev(curV >> (pos & 31)) >> (32 - len); // first position -> highest bit
+                acc = len == 32 ? rev : ((acc << len) | rev);
+                outBits += len;
+                if ((outBits & 31) == 0)
+                    reinterpret_cast<uint32_t*>(img)[lane * (p.kb >> 2) + (outBits >> 5) - 1] = __byte_perm(acc, 0u, 0x0123u);
+            }
+        }
+        for (int k = byRuns ? p.K : 0; k < p.K; ++k) {
             const int pos = (int)__ldg(p.infoPos + k);
             if ((pos >> 5) != curW) { // uniform: positions ascend
                 curW = pos >> 5;

@@ -55,6 +55,8 @@ struct polar_code {
     DecodeParams geo{};            // geometry fields only
     int warpsPerBlock = 0, blocksPerSM = 0, numSMs = 0;
     size_t smemPerBlock = 0;
+    uint32_t* dRuns = nullptr;     // Fast-SSC: runs of consecutive information positions
+    int nRuns = 0;
     uint32_t* dSpill = nullptr;    // list decoders: L2-resident scratch for the top LLR stage
     int8_t* dQuant = nullptr;      // int8 copy of fp32 LLRs (quantiser pre-pass)
     size_t quantBytes = 0;
@@ -145,17 +147,26 @@ int setup_decoder_geometry(polar_code* c)
         if (nSpill) g.spillWarpW = 32 * ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
         c->kernel = pick_scl_kernel(L);
     } else {
-        // One frame per thread; a warp's shared memory is a stack of 32-word rows.
-        g.llrRows = llr_woff(c->lgN);
+        // One frame per thread; a warp's shared memory is a stack of 32-word rows: LLR stages below smemStages,
+        // then the packed partial sums.  The top stages live in an L2-resident scratch with the same
+        // [row][lane] layout (every access a full 128-byte line), which sets the resident warp count.
+        const bool rootLeaf = !c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN;
+        int nSpill = env_int("POLAR_CUDA_SC_SPILL", c->lgN >= 9 ? 2 : (c->lgN >= 8 ? 1 : 0));
+        nSpill = rootLeaf ? 0 : std::max(0, std::min(nSpill, c->lgN - 6));
+        g.smemStages = c->lgN - nSpill;
+        const int imgRows = (8 * c->kb + 31) / 32; // image of the warp's 32 output rows (reuses the stage rows)
+        g.llrRows = std::max(llr_woff(g.smemStages), imgRows);
         g.bitRows = std::max(1, c->N / 32);
         int rows = g.llrRows + g.bitRows;
         const int tileRows = 66; // two 32x33 transpose tiles
-        if (llr_woff(c->lgN - 1) >= tileRows) g.tileRow = 0; // the lower stages are dead at both top-level steps
+        // the shared-memory stage rows below the top-level destination are dead at both top-level steps
+        if (nSpill) { g.llrRows = std::max(g.llrRows, tileRows); g.tileRow = 0; rows = g.llrRows + g.bitRows; }
+        else if (llr_woff(c->lgN - 1) >= tileRows) g.tileRow = 0;
         else { g.tileRow = rows; rows += tileRows; }
-        const bool rootLeaf = !c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN;
         if (rootLeaf) { g.chanRow = rows; rows += c->N / 4; }
         g.outRow = 0;
         g.warpW = rows * 32;
+        if (nSpill) g.spillWarpW = 32 * (llr_woff(c->lgN) - llr_woff(g.smemStages));
         c->kernel = (DecodeKernel)fastssc_i8_kernel;
     }
     if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
@@ -164,7 +175,8 @@ int setup_decoder_geometry(polar_code* c)
         return fail(POLAR_E_UNSUPPORTED, "code does not fit in shared memory (N x listSize too large)");
     int bestWarps = 0, bestW = 1, bestB = 1;
     const int forceW = env_int("POLAR_CUDA_WARPS_PER_BLOCK", 0);
-    for (int w = 8; w >= 1; --w) {
+    // equal resident warps: blocks of 4 warps first (the lockstep barrier then spans 4 warps, one per scheduler)
+    for (int w : { 4, 6, 8, 5, 7, 3, 2, 1 }) {
         if (forceW && w != forceW) continue;
         const size_t smem = perWarp * w;
         if (smem > (size_t)prop.sharedMemPerBlockOptin) continue;
@@ -229,7 +241,7 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaSetDevice(c->device);
     cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab);
     cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
-    cudaFree(c->dSpill); cudaFree(c->dQuant);
+    cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns);
     delete c;
     return POLAR_OK;
 }
@@ -302,6 +314,24 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
             rc = fail(POLAR_E_CUDA, std::string("table upload: ") + cudaGetErrorString(e));
             break;
         }
+        if (kind == POLAR_KIND_FASTSSC_I8) {
+            // runs of consecutive information positions that stay inside one 32-bit word on both sides
+            std::vector<uint32_t> runs;
+            for (int k = 0; k < K;) {
+                int len = 1;
+                while (k + len < K && infoPos[k + len] == infoPos[k] + len && ((infoPos[k] + len) & 31) != 0 &&
+                       ((k + len) & 31) != 0)
+                    ++len;
+                runs.push_back((uint32_t)infoPos[k] | ((uint32_t)len << 16));
+                k += len;
+            }
+            c->nRuns = (int)runs.size();
+            if ((e = cudaMalloc(&c->dRuns, runs.size() * sizeof(uint32_t))) != cudaSuccess ||
+                (e = cudaMemcpy(c->dRuns, runs.data(), runs.size() * sizeof(uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
+                rc = fail(POLAR_E_CUDA, std::string("run table upload: ") + cudaGetErrorString(e));
+                break;
+            }
+        }
         if (kind != POLAR_KIND_ENC) {
             rc = setup_decoder_geometry(c);
         } else {
@@ -346,6 +376,8 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
         p.llr = llr; p.out = info_out; p.ok = okDev;
     }
     p.spill = c->dSpill;
+    p.runs = c->dRuns;
+    p.nRuns = c->nRuns;
     if (llrType == POLAR_LLR_F32) { // CharContainer::insertLlr(const float*): quantise once, decode the int8 copy
         const size_t need = nFrames * (size_t)c->N;
         if (need > c->quantBytes) {
