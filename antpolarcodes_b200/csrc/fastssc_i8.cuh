@@ -293,7 +293,7 @@ POLAR_DEV void sc_polar_transform(ScCtx& c, int N)
 }
 
 // ---------------------------------------------------------------- the kernel
-__global__ void __launch_bounds__(256) fastssc_i8_kernel(const __grid_constant__ DecodeParams p,
+__global__ void __launch_bounds__(128, 4) fastssc_i8_kernel(const __grid_constant__ DecodeParams p,
                                                          const __grid_constant__ Schedule sched)
 {
     extern __shared__ __align__(16) uint32_t smem[];

@@ -178,6 +178,7 @@ int setup_decoder_geometry(polar_code* c)
     // equal resident warps: blocks of 4 warps first (the lockstep barrier then spans 4 warps, one per scheduler)
     for (int w : { 4, 6, 8, 5, 7, 3, 2, 1 }) {
         if (forceW && w != forceW) continue;
+        if (!scl && w > 4) continue; // fastssc_i8_kernel is compiled for blocks of at most 128 threads
         const size_t smem = perWarp * w;
         if (smem > (size_t)prop.sharedMemPerBlockOptin) continue;
         CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -17,8 +17,8 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
-from polar_testlib import (KIND_FASTSSC_I8, KIND_SCL_I8, awgn_llrs, pcbench_llrs, ref_decode, ref_encode,  # noqa: E402
-                           ref_frozen_bits, stress_llrs)
+from polar_testlib import (KIND_FASTSSC_F32, KIND_FASTSSC_I8, KIND_SCL_F32, KIND_SCL_I8, ref_decode,  # noqa: E402
+                           ref_decode_fresh, ref_encode, ref_frozen_bits, workload)
 
 REF = "/root/reference"
 
@@ -48,6 +48,12 @@ DEC_CASES = [  # kind, N, K, ctype, L, crc, frames
     (KIND_SCL_I8, 256, 128, "BB", 4, 8, 32), (KIND_SCL_I8, 64, 32, "BB", 16, 0, 32),
     (KIND_FASTSSC_I8, 1024, 512, "BB", 1, 0, 32), (KIND_FASTSSC_I8, 256, 128, "BB", 1, 8, 32),
     (KIND_FASTSSC_I8, 4096, 1024, "BB", 1, 0, 8), (KIND_FASTSSC_I8, 64, 40, "BB", 1, 8, 32),
+    # fp32 decoders (BASELINE configs[1]: Fast-SSC float N=256 K=128; the fp32 variant of configs[2])
+    (KIND_FASTSSC_F32, 256, 128, "BB", 1, 0, 32), (KIND_FASTSSC_F32, 1024, 512, "BB", 1, 8, 32),
+    (KIND_FASTSSC_F32, 2048, 1024, "BB", 1, 0, 8), (KIND_FASTSSC_F32, 64, 40, "BB", 1, 8, 32),
+    (KIND_FASTSSC_F32, 512, 448, "BB", 1, 0, 16), (KIND_FASTSSC_F32, 128, 16, "BB", 1, 8, 16),
+    (KIND_SCL_F32, 1024, 512, "5G", 8, 16, 16), (KIND_SCL_F32, 256, 128, "BB", 4, 8, 32),
+    (KIND_SCL_F32, 64, 32, "BB", 16, 0, 32),
 ]
 ENC_CASES = [(1024, 512, "5G", 1, 16), (256, 128, "BB", 1, 8), (256, 128, "BB", 0, 0), (2048, 1024, "BB", 1, 32),
              (64, 24, "BB", 1, 8)]
@@ -63,12 +69,15 @@ def main():
         out["frozen_%d_%d_%g_%s" % (N, K, d, t)] = ref_frozen_bits(N, K, d, t)
     for kind, N, K, t, L, crc, n in DEC_CASES:
         fz = ref_frozen_bits(N, K, 0.0, t)
-        for wname, llr in (("awgn", awgn_llrs(N, fz, n, 2.0, crc)[0]), ("pcbench", pcbench_llrs(N, n)),
-                           ("stress", stress_llrs(N, n))):
+        for wname in ("awgn", "pcbench", "stress"):
+            llr = workload(wname, kind, N, fz, n, crc)
             for sysm in (1, 0):
                 if not sysm and N < 256:
                     continue  # the reference's non-systematic path is broken below 256
-                o, k, _ = ref_decode(kind, N, fz, llr, L, sysm, crc)
+                if kind == KIND_SCL_F32:  # a fresh object per frame: see ref_decode_fresh
+                    o, k = ref_decode_fresh(kind, N, fz, llr, L, sysm, crc)
+                else:
+                    o, k, _ = ref_decode(kind, N, fz, llr, L, sysm, crc)
                 key = "dec_%d_%d_%d_%s_%d_%d_%s_%d" % (kind, N, K, t, L, crc, wname, sysm)
                 out[key + "_out"] = o
                 out[key + "_ok"] = k

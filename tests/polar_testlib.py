@@ -112,6 +112,40 @@ def ref_decode(kind, N, frozen, llr, L=1, systematic=1, crc=0, threads=1, repeat
     return out, ok, t
 
 
+def ref_decode_fresh(kind, N, frozen, llr, L=1, systematic=1, crc=0):
+    """One NEW reference decoder object per frame.  Needed for SclAvxFloat: PathList never resets the metric
+    of path 0 (scl_avx_float.cpp:20-56,102-108), so a reused object starts every frame from the previous
+    frame's winning metric and its fp32 roundings -- hence, rarely, its decisions -- depend on history."""
+    llr = np.ascontiguousarray(llr)
+    outs, oks = [], []
+    for f in range(llr.shape[0]):
+        o, k, _ = ref_decode(kind, N, frozen, llr[f:f + 1], L, systematic, crc)
+        outs.append(o)
+        oks.append(k)
+    return np.concatenate(outs), np.concatenate(oks)
+
+
+def is_float_kind(kind):
+    return kind in (KIND_FASTSSC_F32, KIND_SCL_F32)
+
+
+def workload(name, kind, N, frozen, n, crc, seed=None):
+    """The seeded LLR sets of the parity tests, int8 or fp32 according to the decoder kind."""
+    fmt = "f32" if is_float_kind(kind) else "i8"
+    kw = {} if seed is None else {"seed": seed}
+    if name == "awgn":
+        return awgn_llrs(N, frozen, n, 2.0, crc, fmt=fmt, **kw)[0]
+    if name == "awgn0":
+        return awgn_llrs(N, frozen, n, 0.0, crc, fmt=fmt, **({"seed": 7} if seed is None else kw))[0]
+    if name == "pcbench":
+        return pcbench_llrs(N, n, fmt=fmt, **kw)
+    if name == "stress":
+        if fmt == "f32":  # small integers as floats: exact ties in |llr| and in the path metrics, and zeros
+            return np.rint(2.0 * pcbench_llrs(N, n, fmt="f32", **({"seed": 3} if seed is None else kw))).astype(np.float32)
+        return stress_llrs(N, n, **kw)
+    raise ValueError(name)
+
+
 # ---------------------------------------------------------------- oracle wrappers
 def oracle_encode(N, frozen, info, systematic=1, crc=0):
     frozen = np.ascontiguousarray(frozen, np.uint32)

@@ -7,16 +7,21 @@ import os
 import numpy as np
 import pytest
 
-from polar_testlib import (KIND_FASTSSC_I8, KIND_SCL_I8, awgn_llrs, have_ref, oracle, oracle_crc_check,
-                           oracle_crc_generate, oracle_decode, oracle_encode, oracle_quantize, oracle_tree_stats,
-                           pcbench_llrs, ref, ref_decode, ref_encode, stress_llrs, unpack_bits)
+from polar_testlib import (KIND_FASTSSC_F32, KIND_FASTSSC_I8, KIND_SCL_F32, KIND_SCL_I8, awgn_llrs, have_ref, oracle,
+                           oracle_crc_check, oracle_crc_generate, oracle_decode, oracle_encode, oracle_quantize,
+                           oracle_tree_stats, pcbench_llrs, ref, ref_decode, ref_decode_fresh, ref_encode,
+                           stress_llrs, unpack_bits, workload)
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 REFOUT = np.load(os.path.join(GOLD, "ref_outputs.npz"))
 
 
 def frozen(N, K, t, d=0.0):
-    return REFOUT["frozen_%d_%d_%g_%s" % (N, K, d, t)]
+    key = "frozen_%d_%d_%g_%s" % (N, K, d, t)
+    if key in REFOUT.files:
+        return REFOUT[key]
+    import antpolarcodes_b200 as ap  # host-side construction (pinned against the committed sets in test_host.py)
+    return ap.frozen_bits(N, K, d, t)
 
 
 def test_fg_golden_vectors():
@@ -57,6 +62,9 @@ def test_kat_n8():
     assert out[0, 0] & 0xF0 == 0xF0
     out, ok = oracle_decode(KIND_SCL_I8, 8, fz, llr, 4, 1, 0)
     assert out[0, 0] & 0xF0 == 0xF0
+    for kind, L in ((KIND_SCL_F32, 4), (KIND_FASTSSC_F32, 1)):  # the fp32 list decoder has the same KAT (:1128-1177)
+        out, ok = oracle_decode(kind, 8, fz, llr.astype(np.float32), L, 1, 0)
+        assert out[0, 0] & 0xF0 == 0xF0
 
 
 def test_encoder_kats():
@@ -147,8 +155,7 @@ def test_decoders_against_committed_reference_outputs(kind, N, K, t, L, crc, wna
     fz = frozen(N, K, t)
     key = "dec_%d_%d_%d_%s_%d_%d_%s_%d" % (kind, N, K, t, L, crc, wname, sysm)
     n = REFOUT[key + "_ok"].shape[0]
-    llr = {"awgn": lambda: awgn_llrs(N, fz, n, 2.0, crc)[0], "pcbench": lambda: pcbench_llrs(N, n),
-           "stress": lambda: stress_llrs(N, n)}[wname]()
+    llr = workload(wname, kind, N, fz, n, crc)
     out, ok = oracle_decode(kind, N, fz, llr, L, sysm, crc)
     assert np.array_equal(out, REFOUT[key + "_out"]) and np.array_equal(ok, REFOUT[key + "_ok"])
 
@@ -169,11 +176,21 @@ def test_encoder_against_committed_reference_outputs():
 @pytest.mark.parametrize("kind,N,K,t,L,crc,n", [
     (KIND_SCL_I8, 1024, 512, "5G", 8, 16, 40), (KIND_SCL_I8, 256, 128, "BB", 4, 8, 100),
     (KIND_SCL_I8, 64, 32, "BB", 16, 0, 100), (KIND_FASTSSC_I8, 1024, 512, "BB", 1, 0, 200),
-    (KIND_FASTSSC_I8, 4096, 1024, "BB", 1, 0, 20), (KIND_FASTSSC_I8, 64, 40, "BB", 1, 8, 200)])
+    (KIND_FASTSSC_I8, 4096, 1024, "BB", 1, 0, 20), (KIND_FASTSSC_I8, 64, 40, "BB", 1, 8, 200),
+    (KIND_FASTSSC_F32, 256, 128, "BB", 1, 0, 200), (KIND_FASTSSC_F32, 1024, 512, "5G", 1, 16, 50),
+    (KIND_FASTSSC_F32, 32, 11, "BB", 1, 0, 200), (KIND_FASTSSC_F32, 16, 8, "BB", 1, 0, 200),
+    (KIND_FASTSSC_F32, 8, 4, "BB", 1, 0, 200), (KIND_FASTSSC_F32, 512, 384, "BB", 1, 32, 50),
+    (KIND_SCL_F32, 256, 128, "BB", 8, 8, 40), (KIND_SCL_F32, 128, 64, "BB", 2, 8, 60),
+    (KIND_SCL_F32, 32, 16, "BB", 4, 8, 60)])
 def test_oracle_against_live_reference(kind, N, K, t, L, crc, n):
     fz = frozen(N, K, t)
-    for seed, llr in ((11, awgn_llrs(N, fz, n, 1.0, crc, seed=11)[0]), (12, pcbench_llrs(N, n, seed=12)),
-                      (13, stress_llrs(N, n, seed=13))):
+    for seed, wname in ((11, "awgn0"), (12, "pcbench"), (13, "stress")):
+        llr = workload(wname, kind, N, fz, n, crc, seed=seed)
+        if kind == KIND_SCL_F32:
+            o1, k1 = ref_decode_fresh(kind, N, fz, llr, L, 1, crc)
+            o2, k2 = oracle_decode(kind, N, fz, llr, L, 1, crc)
+            assert np.array_equal(o1, o2) and np.array_equal(k1, k2), seed
+            continue
         o1, k1, _ = ref_decode(kind, N, fz, llr, L, 1, crc)
         o2, k2 = oracle_decode(kind, N, fz, llr, L, 1, crc)
         assert np.array_equal(o1, o2) and np.array_equal(k1, k2), seed
