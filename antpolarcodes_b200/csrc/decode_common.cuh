@@ -92,4 +92,97 @@ POLAR_DEV void store_info(const DecodeParams& p, long long frame, const uint32_t
     }
 }
 
+// ---------------------------------------------------------------- one-frame-per-thread epilogue
+// (Fast-SSC kernels: the lane's packed codeword estimate sits in rows bitRow.. of the warp's [row][lane] stack)
+#define TF_ROW(w) sm[((bitRow + (w)) << 5) + lane]
+// x <- x * F^{(x)n} on the lane's packed codeword estimate (non-systematic mode:
+// fastssc_fip_char.cpp:619-622, butterfly_fip.cpp:31-63)
+POLAR_DEV void thread_polar_transform(uint32_t* sm, int lane, int bitRow, int N)
+{
+    const int W = max(N >> 5, 1);
+    for (int w = 0; w < W; ++w) {
+        uint32_t v = TF_ROW(w);
+        if (N < 32) v &= (1u << N) - 1u;
+        v ^= (v >> 1) & 0x55555555u;
+        v ^= (v >> 2) & 0x33333333u;
+        v ^= (v >> 4) & 0x0F0F0F0Fu;
+        v ^= (v >> 8) & 0x00FF00FFu;
+        v ^= (v >> 16) & 0x0000FFFFu;
+        TF_ROW(w) = v;
+    }
+    for (int d = 1; d < W; d <<= 1)
+        for (int w = 0; w < W; ++w)
+            if (!(w & d)) TF_ROW(w) ^= TF_ROW(w + d);
+}
+
+POLAR_DEV void thread_frame_epilogue(const DecodeParams& p, uint32_t* sm, int lane, int bitRow, long long frame0)
+{
+    // systematic: gather; non-systematic: re-encode first (fastssc_fip_char.cpp:616-630), then
+    // getPackedInformationBits (bitcontainer.cpp:536-564) + Detector::check, all per lane.
+    if (!p.systematic) thread_polar_transform(sm, lane, bitRow, p.N);
+    __syncwarp(); // the stage rows are dead: reuse them as the image of the warp's 32 output rows
+    uint8_t* img = reinterpret_cast<uint8_t*>(sm);
+    uint32_t syn = 0, acc = 0;
+    int curW = -1;
+    uint32_t curV = 0;
+    const bool wordOut = (p.kb & 3) == 0;
+    const bool byRuns = wordOut && !p.crcBits && p.nRuns > 0;
+    if (byRuns) { // information bits come in runs of consecutive positions: move a run at a time
+        int outBits = 0;
+        for (int r = 0; r < p.nRuns; ++r) {
+            const uint32_t run = __ldg(p.runs + r);
+            const int pos = (int)(run & 0xFFFFu), len = (int)(run >> 16);
+            if ((pos >> 5) != curW) {
+                curW = pos >> 5;
+                curV = TF_ROW(curW);
+            }
+            const uint32_t rev = __brev(curV >> (pos & 31)) >> (32 - len); // first position -> highest bit
+            acc = len == 32 ? rev : ((acc << len) | rev);
+            outBits += len;
+            if ((outBits & 31) == 0)
+                reinterpret_cast<uint32_t*>(img)[lane * (p.kb >> 2) + (outBits >> 5) - 1] = __byte_perm(acc, 0u, 0x0123u);
+        }
+    }
+    for (int k = byRuns ? p.K : 0; k < p.K; ++k) {
+        const int pos = (int)__ldg(p.infoPos + k);
+        if ((pos >> 5) != curW) { // uniform: positions ascend
+            curW = pos >> 5;
+            curV = TF_ROW(curW);
+        }
+        const uint32_t bit = (curV >> (pos & 31)) & 1u;
+        acc = (acc << 1) | bit;
+        if (p.crcBits) syn ^= __ldg(p.crcTab + k) & (0u - bit);
+        if (wordOut) {
+            if ((k & 31) == 31)
+                reinterpret_cast<uint32_t*>(img)[lane * (p.kb >> 2) + (k >> 5)] = __byte_perm(acc, 0u, 0x0123u);
+        } else if ((k & 7) == 7) {
+            img[lane * p.kb + (k >> 3)] = (uint8_t)acc;
+        }
+    }
+    if (wordOut) { // the last, partly filled unit is zero padded (MSB first)
+        if (p.K & 31)
+            reinterpret_cast<uint32_t*>(img)[lane * (p.kb >> 2) + (p.K >> 5)] =
+                __byte_perm(acc << (32 - (p.K & 31)), 0u, 0x0123u);
+    } else if (p.K & 7) {
+        img[lane * p.kb + (p.K >> 3)] = (uint8_t)(acc << (8 - (p.K & 7)));
+    }
+    const bool ok = !p.crcBits || (syn ^ p.crcInit) == 0u;
+    __syncwarp();
+    // bit rows and the image may overlap only if the image is larger than the stage rows: never
+    // (8*kb <= N words <= 32 * llrRows).  Coalesced copy of the image.
+    const long long nHere = min(32LL, p.nFrames - frame0);
+    uint8_t* dst = p.out + frame0 * p.kb;
+    const long long bytes = nHere * p.kb;
+    if (wordOut) {
+        uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
+        const uint32_t* s4 = reinterpret_cast<const uint32_t*>(img);
+        for (long long i = lane; i < (bytes >> 2); i += 32) d4[i] = s4[i];
+    } else {
+        for (long long i = lane; i < bytes; i += 32) dst[i] = img[i];
+    }
+    if (frame0 + lane < p.nFrames) p.ok[frame0 + lane] = ok ? 1 : 0;
+    __syncwarp();
+}
+#undef TF_ROW
+
 } // namespace polar

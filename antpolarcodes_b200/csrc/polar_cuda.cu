@@ -5,6 +5,7 @@
 #include "crc_host.h"
 #include "decode_params.h"
 #include "encode.cuh"
+#include "fastssc_f32.cuh"
 #include "fastssc_i8.cuh"
 #include "schedule.h"
 #include "scl_i8.cuh"
@@ -146,6 +147,26 @@ int setup_decoder_geometry(polar_code* c)
         g.warpW = ((32 / L) * g.frameW + g.scratchW + 3) & ~3;
         if (nSpill) g.spillWarpW = 32 * ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
         c->kernel = pick_scl_kernel(L);
+    } else if (c->kind == POLAR_KIND_FASTSSC_F32) {
+        // fp32 Fast-SSC: same row stack, one float per word; stage s sits at row 2^s - 1.  Stages from 7 up
+        // (128 floats and more) go to the L2-resident scratch.
+        const bool rootLeaf = !c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN;
+        int keep = env_int("POLAR_CUDA_F32_SMEM_STAGES", 7);
+        g.smemStages = rootLeaf ? c->lgN : std::max(3, std::min(keep, c->lgN));
+        const int nSpill = c->lgN - g.smemStages;
+        const int imgRows = (8 * c->kb + 31) / 32;
+        g.llrRows = std::max(f32_woff(g.smemStages), imgRows);
+        g.bitRows = std::max(1, c->N / 32);
+        const int tileRows = 66;
+        int rows;
+        if (nSpill) { g.llrRows = std::max(g.llrRows, tileRows); g.tileRow = 0; rows = g.llrRows + g.bitRows; }
+        else if (f32_woff(c->lgN - 1) >= tileRows) { g.tileRow = 0; rows = g.llrRows + g.bitRows; }
+        else { rows = g.llrRows + g.bitRows; g.tileRow = rows; rows += tileRows; }
+        if (rootLeaf) { g.chanRow = rows; rows += c->N; }
+        g.outRow = 0;
+        g.warpW = rows * 32;
+        if (nSpill) g.spillWarpW = 32 * (f32_woff(c->lgN) - f32_woff(g.smemStages));
+        c->kernel = (DecodeKernel)fastssc_f32_kernel;
     } else {
         // One frame per thread; a warp's shared memory is a stack of 32-word rows: LLR stages below smemStages,
         // then the packed partial sums.  The top stages live in an L2-resident scratch with the same
@@ -261,8 +282,7 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
         return fail(POLAR_E_ARG, "with a CRC, K must be a multiple of 8 and at least the CRC size");
     if (crcBits == 32 && K / 8 < 4) return fail(POLAR_E_ARG, "CRC32 needs at least 4 info bytes");
     if (K < 1) return fail(POLAR_E_ARG, "no information bits");
-    if (kind == POLAR_KIND_FASTSSC_F32 || kind == POLAR_KIND_SCL_F32)
-        return fail(POLAR_E_UNSUPPORTED, "fp32 decoders are not built yet");
+    if (kind == POLAR_KIND_SCL_F32) return fail(POLAR_E_UNSUPPORTED, "the fp32 list decoder is not built yet");
     if (cudaSetDevice(device) != cudaSuccess) {
         cudaGetLastError();
         return fail(POLAR_E_CUDA, "cudaSetDevice failed (no CUDA device?)");
@@ -277,7 +297,7 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
     do {
         const char* err = nullptr;
         if (kind != POLAR_KIND_ENC) {
-            TreeKind tk = (kind == POLAR_KIND_SCL_I8) ? TREE_SCL_I8 : TREE_FASTSSC_I8;
+            TreeKind tk = kind == POLAR_KIND_SCL_I8 ? TREE_SCL_I8 : kind == POLAR_KIND_FASTSSC_F32 ? TREE_FASTSSC_F32 : TREE_FASTSSC_I8;
             if (!compile_schedule(tk, N, c->frozen, c->L, c->ops, c->stats, &err)) { rc = fail(POLAR_E_ARG, err); break; }
             memset(&c->sched, 0, sizeof(c->sched));
             memcpy(c->sched.ops, c->ops.data(), c->ops.size() * sizeof(uint32_t));
@@ -315,7 +335,7 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
             rc = fail(POLAR_E_CUDA, std::string("table upload: ") + cudaGetErrorString(e));
             break;
         }
-        if (kind == POLAR_KIND_FASTSSC_I8) {
+        if (kind == POLAR_KIND_FASTSSC_I8 || kind == POLAR_KIND_FASTSSC_F32) {
             // runs of consecutive information positions that stay inside one 32-bit word on both sides
             std::vector<uint32_t> runs;
             for (int k = 0; k < K;) {
@@ -354,6 +374,8 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     if (nFrames == 0) return POLAR_OK;
     if (!llr || !info_out) return fail(POLAR_E_ARG, "null buffer");
     if (llrType != POLAR_LLR_I8 && llrType != POLAR_LLR_F32) return fail(POLAR_E_ARG, "bad llr type");
+    if ((c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32) && llrType != POLAR_LLR_F32)
+        return fail(POLAR_E_ARG, "an fp32 decoder takes float LLRs");
     CUDA_TRY(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const int eb = llrType == POLAR_LLR_F32 ? 4 : 1;
@@ -379,7 +401,8 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     p.spill = c->dSpill;
     p.runs = c->dRuns;
     p.nRuns = c->nRuns;
-    if (llrType == POLAR_LLR_F32) { // CharContainer::insertLlr(const float*): quantise once, decode the int8 copy
+    const bool f32Kind = (c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32);
+    if (llrType == POLAR_LLR_F32 && !f32Kind) { // CharContainer::insertLlr(const float*): quantise once, decode the int8 copy
         const size_t need = nFrames * (size_t)c->N;
         if (need > c->quantBytes) {
             cudaFree(c->dQuant);
@@ -478,7 +501,9 @@ int polar_cuda_code_info(polar_code_t c, struct polar_code_info* info)
     info->warpsPerBlock = c->warpsPerBlock; info->blocksPerSM = c->blocksPerSM;
     info->smemPerWarp = c->geo.warpW * 4; info->gridBlocks = c->blocksPerSM * c->numSMs;
     info->laneOpsPerFrame = c->stats.laneOps;
-    info->bytesPerFrame = c->kind == POLAR_KIND_ENC ? (double)(c->kb + std::max(1, c->N / 8)) : (double)(c->N + c->kb + 1);
+    const bool f32 = (c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32);
+    info->bytesPerFrame = c->kind == POLAR_KIND_ENC ? (double)(c->kb + std::max(1, c->N / 8))
+                                                    : (double)((f32 ? 4 : 1) * c->N + c->kb + 1);
     for (int i = 0; i < 32 && i < (int)OP_COUNT; ++i) { info->opCount[i] = c->stats.count[i]; info->opSize[i] = c->stats.size[i]; }
     return POLAR_OK;
 }

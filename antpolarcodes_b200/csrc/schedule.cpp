@@ -28,7 +28,8 @@ struct Compiler {
         st->count[code]++;
         st->size[code] += 1L << stage;
         const double paths = (double)(1 << lgP);
-        st->laneOps += elemOps * paths / 4.0;
+        const bool f32 = (kind == TREE_FASTSSC_F32 || kind == TREE_SCL_F32);
+        st->laneOps += elemOps * paths / (f32 ? 1.0 : 4.0); // 4 int8 or 1 fp32 per lane-op
         if (code == OP_F || code == OP_G || code == OP_COMBINE) st->pathElems += (double)(1L << stage) * paths;
     }
 
@@ -107,6 +108,62 @@ struct Compiler {
         fastssc(pos + h, cs);
         emit(OP_COMBINE, cs, 0, pos, h / 8.0);
     }
+
+    // ---- fp32 Fast-SSC (fastssc_avx_float.cpp:797-896): more leaf kinds, no 32-byte vector rules
+    int lastFrozen(int pos, int n, int k) const // k-th frozen index from the end of the block, relative
+    {
+        for (int i = n - 1; i >= 0; --i)
+            if (frozenIn(pos + i, 1) && --k == 0) return i;
+        return -1;
+    }
+    void fastsscF32(int pos, int stage)
+    {
+        const int n = 1 << stage, fc = frozenIn(pos, n);
+        if (fc == n) { emit(OP_SC_R0, stage, 0, pos, 0); return; }
+        if (fc == 0) { emit(OP_SC_R1, stage, 0, pos, 0); return; }
+        if (fc == n - 1) { emit(OP_SC_REP, stage, 0, pos, 1.0 * n); return; }
+        if (fc == 1) { emit(OP_SC_SPC, stage, 0, pos, 3.0 * n); return; }
+        if (fc == n - 2) {
+            // DoubleRepetitionDecoder: the reference throws unless the frozen bits are the first n-2 (:816-823)
+            if (frozenIn(pos, n - 2) != n - 2) { err = "fp32 Fast-SSC: double-repetition pattern with scattered frozen bits"; return; }
+            emit(OP_SC_REP2, stage, 0, pos, 1.0 * n);
+            return;
+        }
+        if (fc == 2 && frozenIn(pos, 2) == 2) { emit(n == 8 ? OP_F32_SPC2_8 : OP_F32_SPC2, stage, 0, pos, 3.0 * n); return; }
+        if (fc == n - 3 && n > 8 && lastFrozen(pos, n, 1) == n - 4) { emit(OP_F32_REP3, stage, 0, pos, 1.0 * n); return; }
+        if (fc == n - 4 && lastFrozen(pos, n, 1) == n - 4 && lastFrozen(pos, n, 2) == n - 6) {
+            emit(OP_F32_TYPE5, stage, 0, pos, 1.0 * n);
+            return;
+        }
+        if (n == 8 && fc == 3 && frozenIn(pos, 3) == 3) { emit(OP_F32_REPR1_8, stage, 0, pos, 2.0 * n); return; }
+        if (n == 8 && fc == 5 && lastFrozen(pos, n, 1) == 4 && lastFrozen(pos, n, 2) == 3) {
+            emit(OP_F32_ZSPC_8, stage, 0, pos, 2.0 * n);
+            return;
+        }
+        if (stage == 0) { err = "unexpected length-1 inner node"; return; }
+        const int h = n / 2, cs = stage - 1;
+        const int lf = frozenIn(pos, h), rf = frozenIn(pos + h, h);
+        if (n > 8) {
+            if (lf == h && rf == 1) { emit(OP_SC_ZERO_SPC, stage, 0, pos, 2.0 * n); return; }
+            if (rf == 0) {
+                emit(OP_F, cs, 0, pos, 5.0 * h);
+                fastsscF32(pos, cs);
+                emit(OP_G_R1, cs, 0, pos, 2.0 * h);
+                return;
+            }
+            if (lf == h) {
+                emit(OP_G_0R, cs, 0, pos, 1.0 * h);
+                fastsscF32(pos + h, cs);
+                emit(OP_COMBINE_0R, cs, 0, pos, 0);
+                return;
+            }
+        }
+        emit(OP_F, cs, 0, pos, 5.0 * h);
+        fastsscF32(pos, cs);
+        emit(OP_G, cs, 0, pos, 2.0 * h);
+        fastsscF32(pos + h, cs);
+        emit(OP_COMBINE, cs, 0, pos, h / 32.0);
+    }
 };
 
 } // namespace
@@ -144,6 +201,7 @@ bool compile_schedule(TreeKind kind, int N, const std::vector<uint32_t>& frozen,
     case TREE_SCL_I8:
     case TREE_SCL_F32: c.scl(0, c.lgN, false); break;
     case TREE_FASTSSC_I8: c.fastssc(0, c.lgN); break;
+    case TREE_FASTSSC_F32: c.fastsscF32(0, c.lgN); break;
     default: *err = e_kind; return false;
     }
     if (c.err) { *err = c.err; return false; }

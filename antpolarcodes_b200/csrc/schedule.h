@@ -21,6 +21,13 @@ enum OpCode : uint32_t {
     OP_SC_R0, OP_SC_R1, OP_SC_REP, OP_SC_REP2, OP_SC_SPC, OP_SC_ZERO_SPC, OP_SC_ZERO_ONE,
     // list-decoder leaves
     OP_SCL_R0, OP_SCL_R1, OP_SCL_REP, OP_SCL_SPC,
+    // extra leaves of the fp32 Fast-SSC tree (fastssc_avx_float.cpp:797-896)
+    OP_F32_SPC2,      // DoubleSpcDecoder (n >= 16)
+    OP_F32_SPC2_8,    // DoubleSpcDecoderShort8
+    OP_F32_REP3,      // TripleRepetitionDecoder
+    OP_F32_TYPE5,     // TypeFiveDecoder
+    OP_F32_REPR1_8,   // RepetitionRateOneDecoderShort8
+    OP_F32_ZSPC_8,    // ZeroSpcDecoderShort8
     OP_COUNT
 };
 

@@ -30,6 +30,8 @@ WORKLOADS = {
                  label="SCL L=8 + CRC16, N=1024 K=512, 5G frozen set, int8 LLR, Eb/N0=2dB"),
     "fastssc": dict(N=1024, K=512, ctype="BB", L=1, crc=0, frames=1 << 20, e2e_frames=1 << 19,
                     label="Fast-SSC int8, N=1024 K=512, BB frozen set, Eb/N0=2dB"),
+    "fastssc_f32": dict(N=256, K=128, ctype="BB", L=1, crc=0, frames=1 << 20, e2e_frames=1 << 19, fmt="f32",
+                        label="Fast-SSC fp32, N=256 K=128, BB frozen set, Eb/N0=2dB"),
     "scl32": dict(N=2048, K=1024, ctype="BB", L=32, crc=32, frames=1 << 16, e2e_frames=1 << 16,
                   label="SCL L=32 + CRC32, N=2048 K=1024, BB frozen set, int8 LLR, Eb/N0=2dB"),
 }
@@ -93,7 +95,8 @@ def make_llrs_on_device(torch, ap, wl, frozen, frames, seed, device):
     enc = ap.PolarEncoder(N, frozen, device=device.index)
     enc.setSystematic(True)
     enc.setErrorDetection(crc)
-    llr = torch.empty((frames, N), dtype=torch.int8, device=device)
+    f32 = wl.get("fmt") == "f32"
+    llr = torch.empty((frames, N), dtype=torch.float32 if f32 else torch.int8, device=device)
     info_all = torch.empty((frames, K // 8), dtype=torch.uint8, device=device)
     sigma = 1.0 / np.sqrt(2.0 * (K / N) * 10.0 ** (EBN0_DB / 10.0))
     shifts = torch.arange(7, -1, -1, device=device, dtype=torch.uint8)
@@ -105,7 +108,10 @@ def make_llrs_on_device(torch, ap, wl, frozen, frames, seed, device):
         torch.cuda.synchronize(device)
         bits = ((code.unsqueeze(-1) >> shifts) & 1).reshape(n, N).to(torch.float32)
         y = (1.0 - 2.0 * bits) + sigma * torch.randn((n, N), device=device, generator=g)
-        llr[lo:lo + n] = torch.clamp(torch.round(10.0 * y), -128, 127).to(torch.int8)
+        if f32:
+            llr[lo:lo + n] = (2.0 / (sigma * sigma)) * y
+        else:
+            llr[lo:lo + n] = torch.clamp(torch.round(10.0 * y), -128, 127).to(torch.int8)
         info_all[lo:lo + n] = info
     return llr, info_all
 
@@ -116,8 +122,11 @@ def ref_threads():
 
 def time_reference(wl, frozen, llr_host, seconds_target, threads):
     """The unmodified reference decoders (oracle/_ref) on the host cores, one decoder object per thread."""
-    from polar_testlib import KIND_FASTSSC_I8, KIND_SCL_I8, ref_decode
-    kind = KIND_SCL_I8 if wl["L"] > 1 else KIND_FASTSSC_I8
+    from polar_testlib import KIND_FASTSSC_F32, KIND_FASTSSC_I8, KIND_SCL_F32, KIND_SCL_I8, ref_decode
+    if wl.get("fmt") == "f32":
+        kind = KIND_SCL_F32 if wl["L"] > 1 else KIND_FASTSSC_F32
+    else:
+        kind = KIND_SCL_I8 if wl["L"] > 1 else KIND_FASTSSC_I8
     n = llr_host.shape[0]
     _, _, t1 = ref_decode(kind, wl["N"], frozen, llr_host, wl["L"], 1, wl["crc"], threads, 1)
     rep = max(1, int(seconds_target / max(t1, 1e-6)))
@@ -134,7 +143,7 @@ def run_reference_arm(args, wl):
     frozen = ap.frozen_bits(wl["N"], wl["K"], 0.0, wl["ctype"])
     threads = ref_threads()
     sample = max(4 * threads, 1024)
-    llr, _ = awgn_llrs(wl["N"], frozen, sample, EBN0_DB, wl["crc"])
+    llr, _ = awgn_llrs(wl["N"], frozen, sample, EBN0_DB, wl["crc"], fmt=wl.get("fmt", "i8"))
     if not have_ref():
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libpolar_ref.so not present"}))
         return
@@ -176,7 +185,8 @@ def run_ours(args, wl):
     frames = args.frames or wl["frames"]
     e2e_frames = min(args.e2e_frames or wl["e2e_frames"], frames)
     frozen = ap.frozen_bits(N, K, 0.0, wl["ctype"])
-    dec = ap.PolarDecoder(N, L, frozen, "char", device=local)
+    f32 = wl.get("fmt") == "f32"
+    dec = ap.PolarDecoder(N, L, frozen, "float" if f32 else "char", device=local)
     dec.setErrorDetection(crc)
     dec.setSystematic(True)
     info = dec.info()
@@ -222,7 +232,7 @@ def run_ours(args, wl):
     ok_count = int(ok.sum().item())
 
     # e2e: pinned host LLRs -> C ABI with HOST pointers (H2D + kernel + D2H inside the timed region)
-    h_llr = torch.empty((e2e_frames, N), dtype=torch.int8).pin_memory()
+    h_llr = torch.empty((e2e_frames, N), dtype=llr.dtype).pin_memory()
     h_llr.copy_(llr[:e2e_frames])
     h_out = torch.empty((e2e_frames, K // 8), dtype=torch.uint8).pin_memory()
     h_ok = torch.empty((e2e_frames,), dtype=torch.uint8).pin_memory()
@@ -280,12 +290,12 @@ def run_ours(args, wl):
             cpu = {"value": None, "unit": "Gbit/s", "cores": 0, "kind": "reference", "sample": "failed: %r" % (e,)}
         line = {"metric": METRIC if args.workload == "scl8" else wl["label"], "value": value, "unit": "Gbit/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32" if f32 else "int8", "data": "synthetic",
                 "config": {"workload": wl["label"], "frames_per_step_per_gpu": frames, "e2e_frames_per_step_per_gpu": e2e_frames,
-                           "list_size": L, "crc_bits": crc, "cache": "inputs larger than L2 (%d MiB of LLRs per step)" % (frames * N >> 20),
+                           "list_size": L, "crc_bits": crc, "cache": "inputs larger than L2 (%d MiB of LLRs per step)" % (frames * N * (4 if f32 else 1) >> 20),
                            "warps_per_block": info.warpsPerBlock, "blocks_per_sm": info.blocksPerSM,
                            "smem_per_warp": info.smemPerWarp, "schedule_ops": info.nOps, "parallelism": "frames sharded x%d" % world},
-                "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": e2e_frames * N,
+                "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": e2e_frames * N * (4 if f32 else 1),
                         "d2h_bytes_per_step": e2e_frames * (K // 8 + 1), "matches_device_run": e2e_match},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
                 "check": {"frames": int(errs[2].item()), "frame_errors_vs_sent": int(errs[0].item()),

@@ -4,8 +4,9 @@ import numpy as np
 import pytest
 
 import antpolarcodes_b200 as ap
-from polar_testlib import (KIND_FASTSSC_I8, KIND_SCL_I8, awgn_llrs, have_ref, oracle_decode, oracle_encode,
-                           pcbench_llrs, ref_decode, ref_encode, stress_llrs)
+from polar_testlib import (KIND_FASTSSC_F32, KIND_FASTSSC_I8, KIND_SCL_F32, KIND_SCL_I8, awgn_llrs, have_ref,
+                           oracle_decode, oracle_encode, pcbench_llrs, ref_decode, ref_decode_fresh, ref_encode,
+                           stress_llrs, workload)
 
 pytestmark = pytest.mark.gpu
 
@@ -23,7 +24,11 @@ def _compare(dec, kind, N, frozen, L, sysm, crc, llr, tag):
     bad = np.where((out != eo).any(axis=1) | (ok != ek))[0]
     assert len(bad) == 0, "%s: %d/%d frames differ from the oracle, first %s" % (tag, len(bad), len(llr), bad[:5])
     if have_ref() and (sysm or N >= 256):
-        ro, rk, _ = ref_decode(kind, N, frozen, llr, L, sysm, crc)
+        if kind == KIND_SCL_F32:  # the reference's fp32 list decoder depends on its history: fresh object per frame
+            ro, rk = ref_decode_fresh(kind, N, frozen, llr[:16], L, sysm, crc)
+            out, ok = out[:16], ok[:16]
+        else:
+            ro, rk, _ = ref_decode(kind, N, frozen, llr, L, sysm, crc)
         bad = np.where((out != ro).any(axis=1) | (ok != rk))[0]
         assert len(bad) == 0, "%s: %d frames differ from the reference, first %s" % (tag, len(bad), bad[:5])
 
@@ -74,6 +79,30 @@ def test_fastssc_i8_parity(gpu, N, K, ctype, crc, n, sysm):
     dec.setSystematic(bool(sysm))
     for name, llr in _workloads(N, frozen, n, crc):
         _compare(dec, KIND_FASTSSC_I8, N, frozen, 1, sysm, crc, llr, "fastssc N=%d %s sys=%d" % (N, name, sysm))
+
+
+FASTSSC_F32_CASES = [
+    (256, 128, "BB", 0, 256), (1024, 512, "BB", 8, 128), (1024, 512, "5G", 16, 64), (2048, 1024, "BB", 0, 64),
+    (4096, 1024, "BB", 0, 32), (512, 448, "BB", 0, 128), (128, 16, "BB", 8, 128), (64, 40, "BB", 8, 256),
+    (32, 11, "BB", 0, 256), (16, 8, "BB", 0, 256), (8, 4, "BB", 0, 256), (1024, 768, "BE", 16, 64),
+    (1024, 64, "5G", 0, 64), (256, 192, "BB", 32, 100), (128, 64, "BE", 8, 100),
+]
+
+
+def _float_workloads(kind, N, frozen, n, crc):
+    return [(w, workload(w, kind, N, frozen, n, crc)) for w in ("awgn", "awgn0", "pcbench", "stress")]
+
+
+@pytest.mark.parametrize("N,K,ctype,crc,n", FASTSSC_F32_CASES)
+@pytest.mark.parametrize("sysm", [1, 0])
+def test_fastssc_f32_parity(gpu, N, K, ctype, crc, n, sysm):
+    """FastSscAvxFloat: bit-exact (every sum in the reference's evaluation order)."""
+    frozen = ap.frozen_bits(N, K, 0.0, ctype)
+    dec = ap.PolarDecoder(N, 1, frozen, "float")
+    dec.setErrorDetection(crc)
+    dec.setSystematic(bool(sysm))
+    for name, llr in _float_workloads(KIND_FASTSSC_F32, N, frozen, n, crc):
+        _compare(dec, KIND_FASTSSC_F32, N, frozen, 1, sysm, crc, llr, "fastssc f32 N=%d %s sys=%d" % (N, name, sysm))
 
 
 def test_float_llr_into_int8_decoder(gpu):

@@ -10,7 +10,7 @@ timeout 900 python -m pytest tests -m gpu -q --timeout 300 -p no:cacheprovider -
 RC=$?
 tail -5 $OUT/${TAG}_pytest.log
 echo "pytest rc=$RC"
-for WL in scl8 fastssc; do
+for WL in ${BENCH_WLS:-scl8 fastssc fastssc_f32}; do
   timeout 300 python bench.py --workload $WL --steps 5 --warmup 3 > $OUT/${TAG}_bench_$WL.json 2> $OUT/${TAG}_bench_$WL.err
   echo "bench $WL rc=$?"; cat $OUT/${TAG}_bench_$WL.json | cut -c1-600
 done
@@ -22,7 +22,7 @@ for V in ${VARIANTS:-}; do
 done
 if [ $RC -eq 0 ] && [ "${NCU:-1}" = "1" ]; then
   for WL in ${NCU_WLS:-scl8 fastssc}; do
-    if [ $WL = scl8 ]; then KRN=scl_i8_kernel; FR=131072; else KRN=fastssc_i8_kernel; FR=262144; fi
+    if [ $WL = scl8 ]; then KRN=scl_i8_kernel; FR=131072; elif [ $WL = fastssc_f32 ]; then KRN=fastssc_f32_kernel; FR=262144; else KRN=fastssc_i8_kernel; FR=262144; fi
     CMD="python bench.py --workload $WL --steps 2 --warmup 1 --frames $FR --e2e-frames 8192"
     $CMD > $OUT/${TAG}_ncu_plain_$WL.log 2>&1 &&
     ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches_$WL.csv $CMD > $OUT/${TAG}_ncu_list_$WL.log 2>&1
