@@ -273,7 +273,10 @@ POLAR_DEV bool sc_spc_decide(const uint32_t* src, int s, bool longForm, uint32_t
 }
 
 // ---------------------------------------------------------------- the kernel
-__global__ void __launch_bounds__(128, 4) fastssc_i8_kernel(const __grid_constant__ DecodeParams p,
+// WIDE: blocks of up to 16 warps at 128 registers (the lockstep barrier then spans every resident warp of the
+// SM); otherwise blocks of up to 8 warps with the full register budget.
+template <bool WIDE>
+__global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const __grid_constant__ DecodeParams p,
                                                          const __grid_constant__ Schedule sched)
 {
     extern __shared__ __align__(16) uint32_t smem[];
@@ -298,7 +301,11 @@ __global__ void __launch_bounds__(128, 4) fastssc_i8_kernel(const __grid_constan
 
     const long long totalWarps = (long long)gridDim.x * warpsPerBlock;
     const long long nGroups = (p.nFrames + 31) >> 5;
-    for (long long grp = (long long)blockIdx.x * warpsPerBlock + warp; grp < nGroups; grp += totalWarps) {
+    // block-uniform trip count: with p.lockstep the warps of a block meet at a barrier before every schedule
+    // step, so they fetch the same instruction lines together (see scl_i8_kernel)
+    for (long long g0 = (long long)blockIdx.x * warpsPerBlock; g0 < nGroups; g0 += totalWarps) {
+        const bool live = g0 + warp < nGroups; // a spare warp redoes the last group and drops it
+        const long long grp = live ? g0 + warp : nGroups - 1;
         c.frame0 = grp << 5;
         if (c.chanRow >= 0) { // one-leaf codes: stage the channel rows (transposed) once
             for (int w0 = 0; w0 < c.nw; w0 += 32) {
@@ -313,6 +320,7 @@ __global__ void __launch_bounds__(128, 4) fastssc_i8_kernel(const __grid_constan
             const uint32_t op = sched.ops[pc];
             const uint32_t code = POLAR_OP_CODE(op);
             if (code == OP_END) break;
+            if (p.lockstep) __syncthreads();
             const int s = (int)POLAR_OP_STAGE(op), pos = (int)POLAR_OP_POS(op);
             const bool longForm = (POLAR_OP_FLAGS(op) & OPF_LONG) != 0;
             const bool top = (s + 1 == c.lgN) && c.chanRow < 0; // parent block = channel row in global memory
@@ -439,7 +447,7 @@ __global__ void __launch_bounds__(128, 4) fastssc_i8_kernel(const __grid_constan
             default: break;
             }
         }
-        thread_frame_epilogue(p, c.sm, lane, c.bitRow, c.frame0);
+        if (live) thread_frame_epilogue(p, c.sm, lane, c.bitRow, c.frame0);
     }
 }
 

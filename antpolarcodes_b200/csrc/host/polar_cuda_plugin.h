@@ -1,0 +1,244 @@
+// Drop-in subclasses of the reference's Decoder / Encoder interfaces on top of the libpolar_cuda C ABI.
+//
+// This header is the code a maintainer of david13pod/antPolarCodes adds to the reference tree (see
+// INTEGRATION.md): it is compiled against the reference's OWN headers (include/polarcode/...) and calls nothing
+// but include/polar_cuda.h.  Nothing here restates an algorithm; the classes only adapt the call conventions:
+//
+//   PolarCode::Decoding::FastSscCudaChar   next to FastSscFipChar   (fastssc_fip_char.h:298)
+//   PolarCode::Decoding::FastSscCudaFloat  next to FastSscAvxFloat  (fastssc_avx_float.h:283)
+//   PolarCode::Decoding::SclCudaChar       next to SclFipChar       (scl_fip_char.h:391)
+//   PolarCode::Decoding::SclCudaFloat      next to SclAvxFloat      (scl_avx_float.h:407)
+//   PolarCode::Decoding::makeCudaDecoder   like makeDecoder         (decoder.cpp:50-87)
+//   PolarCode::Encoding::ButterflyCudaPacked next to ButterflyFipPacked (butterfly_fip_packed.h:25)
+//
+// The one-frame virtual API (decode_vector / decode / encode_vector / encode) is served by a batch of one --
+// correct, and as slow as a kernel launch; throughput comes from decode_batch / encode_batch, the entry points
+// this header adds.  The base-class setters (setSystematic, setErrorDetection) stay usable at any time: the
+// device-side code handle is rebuilt lazily when the configuration it was compiled for has changed.
+#pragma once
+#include <polar_cuda.h>
+#include <polarcode/bitcontainer.h>
+#include <polarcode/decoding/decoder.h>
+#include <polarcode/encoding/encoder.h>
+#include <polarcode/errordetection/crc8.h>
+#include <polarcode/errordetection/errordetector.h>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace PolarCode {
+namespace CudaDetail {
+
+inline void check(int rc)
+{
+    if (rc == POLAR_OK) return;
+    const std::string msg = polar_cuda_last_error();
+    if (rc == POLAR_E_ARG) throw std::invalid_argument(msg); // the reference's convention for bad parameters
+    throw std::runtime_error(msg);
+}
+
+// CRC width the kernels fuse for this detector: Dummy -> 0, CRC8/16/32 -> 8/16/32.  Anything else (CMAC) has no
+// device implementation.
+inline int fusedCrcBits(ErrorDetection::Detector* d)
+{
+    const std::string type = d->getType();
+    const unsigned bits = d->getCheckBitCount();
+    if (bits == 0) return 0;
+    if (type == "CRC" && (bits == 8 || bits == 16 || bits == 32)) return (int)bits;
+    throw std::runtime_error("polar_cuda: error detector " + type + "-" + std::to_string(bits) + " is not fused on the GPU");
+}
+
+// A compiled code handle plus the configuration it was compiled for.
+struct Handle {
+    polar_code_t code = nullptr;
+    int sys = -1, crc = -1;
+    ~Handle() { if (code) polar_cuda_code_destroy(code); }
+    polar_code_t get(int device, int kind, size_t N, const std::vector<unsigned>& frozen, size_t L, bool systematic,
+                     ErrorDetection::Detector* det)
+    {
+        const int crcBits = fusedCrcBits(det);
+        if (code && sys == (int)systematic && crc == crcBits) return code;
+        if (code) { polar_cuda_code_destroy(code); code = nullptr; }
+        check(polar_cuda_code_create(device, kind, (int)N, frozen.data(), (int)frozen.size(), (int)L, systematic ? 1 : 0,
+                                     crcBits, &code));
+        sys = (int)systematic;
+        crc = crcBits;
+        return code;
+    }
+};
+
+} // namespace CudaDetail
+
+namespace Decoding {
+
+// Common part of the four decoders.  FLOAT selects the arithmetic (and with it the input container type, so
+// that the inherited setSignal() overloads convert exactly like the CPU decoder of the same type does:
+// CharContainer::insertLlr quantises floats, FloatContainer::insertLlr widens chars).
+template <bool FLOAT>
+class CudaDecoder : public Decoder
+{
+    CudaDetail::Handle mHandle;
+    size_t mListSize;
+    int mDevice;
+
+    int kind() const
+    {
+        if (mListSize > 1) return FLOAT ? POLAR_KIND_SCL_F32 : POLAR_KIND_SCL_I8;
+        return FLOAT ? POLAR_KIND_FASTSSC_F32 : POLAR_KIND_FASTSSC_I8;
+    }
+    polar_code_t code()
+    {
+        return mHandle.get(mDevice, kind(), mBlockLength, mFrozenBits, mListSize, mSystematic, mErrorDetector);
+    }
+
+public:
+    CudaDecoder(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int device = 0)
+        : mListSize(listSize), mDevice(device)
+    {
+        initialize(blockLength, frozenBits);
+    }
+    ~CudaDecoder() override {} // the base class deletes the containers
+
+    void initialize(size_t blockLength, const std::vector<unsigned>& frozenBits) override
+    {
+        Decoder::initialize(blockLength, frozenBits);
+        delete mLlrContainer;
+        delete mBitContainer;
+        delete[] mOutputContainer;
+        if (FLOAT) {
+            mLlrContainer = new FloatContainer(blockLength);
+            mBitContainer = new FloatContainer(blockLength, frozenBits);
+        } else {
+            mLlrContainer = new CharContainer(blockLength);
+            mBitContainer = new CharContainer(blockLength, frozenBits);
+        }
+        mOutputContainer = new unsigned char[(blockLength - frozenBits.size() + 7) / 8];
+        mHandle.sys = -1; // force a rebuild
+    }
+
+    size_t getListSize() override { return mListSize; }
+
+    // Decoder::decode(): the frame setSignal() left in mLlrContainer, a batch of one.
+    bool decode() override
+    {
+        uint8_t ok = 0;
+        const void* llr = FLOAT ? static_cast<const void*>(static_cast<FloatContainer*>(mLlrContainer)->data())
+                                : static_cast<const void*>(static_cast<CharContainer*>(mLlrContainer)->data());
+        CudaDetail::check(polar_cuda_decode_batch(code(), llr, FLOAT ? POLAR_LLR_F32 : POLAR_LLR_I8, POLAR_MEM_HOST, 1,
+                                                  mOutputContainer, &ok, nullptr));
+        return ok != 0;
+    }
+
+    // nFrames x blockLength() LLRs in, nFrames x ceil(infoLength()/8) bytes and nFrames verdicts out.
+    // Host buffers: returns when the results are in place.  Device buffers: asynchronous on `stream`.
+    void decode_batch(const char* llr, size_t nFrames, unsigned char* info, unsigned char* ok, bool deviceBuffers = false,
+                      void* stream = nullptr)
+    {
+        if (FLOAT) throw std::invalid_argument("a float decoder takes float LLRs");
+        CudaDetail::check(polar_cuda_decode_batch(code(), llr, POLAR_LLR_I8, deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
+                                                  nFrames, info, ok, stream));
+    }
+    // float LLRs into a char decoder are quantised on the device like CharContainer::insertLlr(const float*)
+    void decode_batch(const float* llr, size_t nFrames, unsigned char* info, unsigned char* ok, bool deviceBuffers = false,
+                      void* stream = nullptr)
+    {
+        CudaDetail::check(polar_cuda_decode_batch(code(), llr, POLAR_LLR_F32, deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
+                                                  nFrames, info, ok, stream));
+    }
+};
+
+class FastSscCudaChar : public CudaDecoder<false>
+{
+public:
+    FastSscCudaChar(size_t blockLength, const std::vector<unsigned>& frozenBits, int device = 0)
+        : CudaDecoder<false>(blockLength, 1, frozenBits, device) {}
+};
+class FastSscCudaFloat : public CudaDecoder<true>
+{
+public:
+    FastSscCudaFloat(size_t blockLength, const std::vector<unsigned>& frozenBits, int device = 0)
+        : CudaDecoder<true>(blockLength, 1, frozenBits, device) {}
+};
+class SclCudaChar : public CudaDecoder<false>
+{
+public:
+    SclCudaChar(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int device = 0)
+        : CudaDecoder<false>(blockLength, listSize, frozenBits, device) {}
+};
+class SclCudaFloat : public CudaDecoder<true>
+{
+public:
+    SclCudaFloat(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int device = 0)
+        : CudaDecoder<true>(blockLength, listSize, frozenBits, device) {}
+};
+
+// makeDecoder (decoder.cpp:50-87) for the GPU types: decoder_impl 0 = char, 1 = float; like the CPU factory a
+// fresh decoder checks CRC8.
+inline Decoder* makeCudaDecoder(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits,
+                                int decoder_impl = 0, int device = 0)
+{
+    Decoder* dec;
+    if (listSize == 1) {
+        if (decoder_impl == 1) dec = new FastSscCudaFloat(blockLength, frozenBits, device);
+        else dec = new FastSscCudaChar(blockLength, frozenBits, device);
+    } else {
+        if (decoder_impl == 1) dec = new SclCudaFloat(blockLength, listSize, frozenBits, device);
+        else dec = new SclCudaChar(blockLength, listSize, frozenBits, device);
+    }
+    dec->setErrorDetection(new ErrorDetection::CRC8());
+    return dec;
+}
+
+} // namespace Decoding
+
+namespace Encoding {
+
+class ButterflyCudaPacked : public Encoder
+{
+    CudaDetail::Handle mHandle;
+    int mDevice;
+
+    polar_code_t code()
+    {
+        return mHandle.get(mDevice, POLAR_KIND_ENC, mBlockLength, mFrozenBits, 1, mSystematic, mErrorDetector);
+    }
+
+public:
+    ButterflyCudaPacked(size_t blockLength, const std::vector<unsigned>& frozenBits, int device = 0) : mDevice(device)
+    {
+        initialize(blockLength, frozenBits);
+    }
+    ~ButterflyCudaPacked() override {}
+
+    void initialize(size_t blockLength, const std::vector<unsigned>& frozenBits) override
+    {
+        mBlockLength = blockLength;
+        mFrozenBits.assign(frozenBits.begin(), frozenBits.end());
+        delete mBitContainer;
+        mBitContainer = new PackedContainer(mBlockLength, mFrozenBits); // getEncodedData() reads the codeword from here
+        mHandle.sys = -1;
+    }
+
+    // ButterflyFipPacked::encode (butterfly_fip_packed.cpp:45-59): checksum into the caller's info block, then
+    // the codeword into mBitContainer.  setCodeword()-style pre-loaded containers are outside the hot path.
+    void encode() override
+    {
+        if (mCodewordReady) throw std::runtime_error("ButterflyCudaPacked: encode from a pre-loaded codeword is not supported");
+        std::vector<unsigned char> cw(mBlockLength / 8);
+        CudaDetail::check(polar_cuda_encode_batch(code(), xmInputData, POLAR_MEM_HOST, 1, cw.data(), nullptr));
+        mBitContainer->insertPackedBits(cw.data());
+    }
+
+    // nFrames x infoLength()/8 bytes in (the checksum bytes of every block are overwritten in place, like
+    // Detector::generate does), nFrames x blockLength()/8 bytes out.
+    void encode_batch(unsigned char* info, size_t nFrames, unsigned char* codewords, bool deviceBuffers = false,
+                      void* stream = nullptr)
+    {
+        CudaDetail::check(polar_cuda_encode_batch(code(), info, deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST, nFrames,
+                                                  codewords, stream));
+    }
+};
+
+} // namespace Encoding
+} // namespace PolarCode

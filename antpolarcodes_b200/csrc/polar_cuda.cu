@@ -8,6 +8,7 @@
 #include "fastssc_f32.cuh"
 #include "fastssc_i8.cuh"
 #include "schedule.h"
+#include "scl_f32.cuh"
 #include "scl_i8.cuh"
 
 #include <cstdio>
@@ -89,6 +90,19 @@ DecodeKernel pick_scl_kernel(int L)
     return nullptr;
 }
 
+DecodeKernel pick_sclf_kernel(int L)
+{
+    switch (L) {
+    case 1: return scl_f32_kernel<1>;
+    case 2: return scl_f32_kernel<2>;
+    case 4: return scl_f32_kernel<4>;
+    case 8: return scl_f32_kernel<8>;
+    case 16: return scl_f32_kernel<16>;
+    case 32: return scl_f32_kernel<32>;
+    }
+    return nullptr;
+}
+
 int env_int(const char* name, int dflt)
 {
     const char* v = getenv(name);
@@ -111,8 +125,10 @@ int setup_decoder_geometry(polar_code* c)
     g.bitB1 = 0;
     g.spillWarpW = 0;
     g.chanRow = -1;
-    const bool scl = (c->kind == POLAR_KIND_SCL_I8);
+    const bool scl = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32);
+    const bool sclF32 = (c->kind == POLAR_KIND_SCL_F32);
     const int L = scl ? c->L : 1;
+    bool wide = false; // Fast-SSC kernels: 16-warp blocks at 128 registers
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, c->device));
     c->numSMs = prop.multiProcessorCount;
@@ -124,10 +140,13 @@ int setup_decoder_geometry(polar_code* c)
         // The top LLR stages live in an L2-resident scratch instead (coalesced [word][lane] layout), which is
         // what sets the resident warp count; region A of the bit slots holds stages 0..lgN-1 (the root is
         // assembled by the epilogue), region B is a ping-pong pair.
+        // (fp32 lists: one float per word, stage s at word 2^s - 1 of the slot)
         int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 9 ? 2 : (c->lgN >= 7 ? 1 : 0));
         nSpill = std::max(0, std::min(nSpill, c->lgN - 5));
+        if (sclF32) // keep a warp's footprint within reach of a few resident warps per SM
+            while (nSpill < c->lgN - 5 && (size_t)32 * f32_woff(c->lgN - nSpill) * 4 > 96 * 1024) ++nSpill;
         g.smemStages = c->lgN - nSpill;
-        int slot = llr_woff(g.smemStages);
+        int slot = sclF32 ? f32_woff(g.smemStages) : llr_woff(g.smemStages);
         while (slot % L != 1 % L) ++slot;
         g.slotW = slot;
         g.rootLeaf = (!c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN) ? 1 : 0;
@@ -145,8 +164,10 @@ int setup_decoder_geometry(polar_code* c)
         g.frameW = frame;
         g.scratchW = 2 * ((c->K + 31) / 32) + nW + 4;
         g.warpW = ((32 / L) * g.frameW + g.scratchW + 3) & ~3;
-        if (nSpill) g.spillWarpW = 32 * ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
-        c->kernel = pick_scl_kernel(L);
+        if (nSpill)
+            g.spillWarpW = sclF32 ? 32 * ((1 << c->lgN) - (1 << g.smemStages))
+                                  : 32 * ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
+        c->kernel = sclF32 ? pick_sclf_kernel(L) : pick_scl_kernel(L);
     } else if (c->kind == POLAR_KIND_FASTSSC_F32) {
         // fp32 Fast-SSC: same row stack, one float per word; stage s sits at row 2^s - 1.  Stages from 7 up
         // (128 floats and more) go to the L2-resident scratch.
@@ -166,7 +187,8 @@ int setup_decoder_geometry(polar_code* c)
         g.outRow = 0;
         g.warpW = rows * 32;
         if (nSpill) g.spillWarpW = 32 * (f32_woff(c->lgN) - f32_woff(g.smemStages));
-        c->kernel = (DecodeKernel)fastssc_f32_kernel;
+        wide = env_int("POLAR_CUDA_SC_WIDE", 1) != 0;
+        c->kernel = wide ? (DecodeKernel)fastssc_f32_kernel<true> : (DecodeKernel)fastssc_f32_kernel<false>;
     } else {
         // One frame per thread; a warp's shared memory is a stack of 32-word rows: LLR stages below smemStages,
         // then the packed partial sums.  The top stages live in an L2-resident scratch with the same
@@ -188,7 +210,8 @@ int setup_decoder_geometry(polar_code* c)
         g.outRow = 0;
         g.warpW = rows * 32;
         if (nSpill) g.spillWarpW = 32 * (llr_woff(c->lgN) - llr_woff(g.smemStages));
-        c->kernel = (DecodeKernel)fastssc_i8_kernel;
+        wide = env_int("POLAR_CUDA_SC_WIDE", 1) != 0;
+        c->kernel = wide ? (DecodeKernel)fastssc_i8_kernel<true> : (DecodeKernel)fastssc_i8_kernel<false>;
     }
     if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
     const size_t perWarp = (size_t)g.warpW * 4;
@@ -197,9 +220,13 @@ int setup_decoder_geometry(polar_code* c)
     int bestWarps = 0, bestW = 1, bestB = 1;
     const int forceW = env_int("POLAR_CUDA_WARPS_PER_BLOCK", 0);
     // equal resident warps: blocks of 4 warps first (the lockstep barrier then spans 4 warps, one per scheduler)
-    for (int w : { 4, 6, 8, 5, 7, 3, 2, 1 }) {
+    // (the Fast-SSC kernels take the widest block instead: one barrier domain per SM)
+    static const int sclOrder[] = { 4, 6, 8, 5, 7, 3, 2, 1 };
+    static const int scOrder[] = { 16, 12, 8, 6, 4, 3, 2, 1 };
+    for (int i = 0; i < 8; ++i) {
+        const int w = scl ? sclOrder[i] : scOrder[i];
         if (forceW && w != forceW) continue;
-        if (!scl && w > 4) continue; // fastssc_i8_kernel is compiled for blocks of at most 128 threads
+        if (!scl && w > (wide ? 16 : 8)) continue; // launch bounds of the Fast-SSC kernels
         const size_t smem = perWarp * w;
         if (smem > (size_t)prop.sharedMemPerBlockOptin) continue;
         CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -282,14 +309,13 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
         return fail(POLAR_E_ARG, "with a CRC, K must be a multiple of 8 and at least the CRC size");
     if (crcBits == 32 && K / 8 < 4) return fail(POLAR_E_ARG, "CRC32 needs at least 4 info bytes");
     if (K < 1) return fail(POLAR_E_ARG, "no information bits");
-    if (kind == POLAR_KIND_SCL_F32) return fail(POLAR_E_UNSUPPORTED, "the fp32 list decoder is not built yet");
     if (cudaSetDevice(device) != cudaSuccess) {
         cudaGetLastError();
         return fail(POLAR_E_CUDA, "cudaSetDevice failed (no CUDA device?)");
     }
     polar_code* c = new polar_code;
     c->device = device; c->kind = kind; c->N = N; c->K = K; c->kb = (K + 7) / 8;
-    c->L = (kind == POLAR_KIND_SCL_I8) ? listSize : 1;
+    c->L = (kind == POLAR_KIND_SCL_I8 || kind == POLAR_KIND_SCL_F32) ? listSize : 1;
     c->systematic = systematic ? 1 : 0; c->crcBits = crcBits;
     while ((1 << c->lgN) < N) ++c->lgN;
     c->frozen.assign(frozen, frozen + nFrozen);
@@ -297,7 +323,8 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
     do {
         const char* err = nullptr;
         if (kind != POLAR_KIND_ENC) {
-            TreeKind tk = kind == POLAR_KIND_SCL_I8 ? TREE_SCL_I8 : kind == POLAR_KIND_FASTSSC_F32 ? TREE_FASTSSC_F32 : TREE_FASTSSC_I8;
+            TreeKind tk = kind == POLAR_KIND_SCL_I8 ? TREE_SCL_I8 : kind == POLAR_KIND_SCL_F32 ? TREE_SCL_F32
+                          : kind == POLAR_KIND_FASTSSC_F32 ? TREE_FASTSSC_F32 : TREE_FASTSSC_I8;
             if (!compile_schedule(tk, N, c->frozen, c->L, c->ops, c->stats, &err)) { rc = fail(POLAR_E_ARG, err); break; }
             memset(&c->sched, 0, sizeof(c->sched));
             memcpy(c->sched.ops, c->ops.data(), c->ops.size() * sizeof(uint32_t));
@@ -419,7 +446,7 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
         CUDA_TRY(cudaGetLastError());
         p.llr = c->dQuant;
     }
-    const int framesPerWarp = c->kind == POLAR_KIND_SCL_I8 ? 32 / c->L : 32;
+    const int framesPerWarp = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32) ? 32 / c->L : 32;
     const long long warpsNeeded = ((long long)nFrames + framesPerWarp - 1) / framesPerWarp;
     const long long blocksNeeded = (warpsNeeded + c->warpsPerBlock - 1) / c->warpsPerBlock;
     const int grid = (int)std::min<long long>(blocksNeeded, (long long)c->blocksPerSM * c->numSMs);

@@ -171,3 +171,241 @@ POLAR_DEV void sclf_weak_search(const FWords& src, int n, float (&val)[4], int (
         }
     }
 }
+
+// simplePartialSortDescending on float metrics (see scl_select in scl_i8.cuh): 64-bit keys
+// (ordered metric << 8 | 255 - position); unused registers hold key 0, below every real key.
+template <int L, int FMAX>
+POLAR_DEV void sclf_select(const SclCtx& c, const float (&cand)[FMAX], int lgF, int lgP, int nOut, float& outMet, int& outIdx)
+{
+    const int gl = c.gl, F = 1 << lgF;
+    unsigned long long key[FMAX];
+    int orig[FMAX];
+#pragma unroll
+    for (int k = 0; k < FMAX; ++k) {
+        const int pos = (gl << lgF) + k;
+        const uint32_t o = f32_ordered(__fadd_rn(cand[k], 0.0f)); // -0.0 -> +0.0: equal floats, equal keys
+        key[k] = (gl < (1 << lgP) && k < F) ? (((unsigned long long)o << 8) | (unsigned)(255 - pos)) : 0ull;
+        orig[k] = pos;
+    }
+    outMet = 0.0f;
+    outIdx = 0;
+#pragma unroll 1
+    for (int i = 0; i < nOut; ++i) {
+        unsigned long long m = key[0];
+#pragma unroll
+        for (int k = 1; k < FMAX; ++k) m = key[k] > m ? key[k] : m;
+        const unsigned long long best = list_max64<L>(m);
+        const int pos = 255 - (int)(best & 255u), wl = pos >> lgF, wk = pos & (F - 1);
+        const int il = i >> lgF, ik = i & (F - 1);
+        int wo = orig[0], io = orig[0];
+        unsigned long long ikl = key[0];
+#pragma unroll
+        for (int k = 1; k < FMAX; ++k) {
+            if (k == wk) wo = orig[k];
+            if (k == ik) { io = orig[k]; ikl = key[k]; }
+        }
+        const int widx = __shfl_sync(FULL_MASK, wo, c.fb + wl);
+        const unsigned long long ikey = shfl64(ikl, c.fb + il); // the element now at position i
+        const int iidx = __shfl_sync(FULL_MASK, io, c.fb + il);
+        const unsigned long long moved = (ikey & ~255ull) | (unsigned)(255 - pos);
+#pragma unroll
+        for (int k = 0; k < FMAX; ++k) {
+            if (gl == wl && k == wk) { key[k] = moved; orig[k] = iidx; }
+            if (gl == il && k == ik) key[k] = 0ull;
+        }
+        if (gl == i) {
+            outMet = f32_unordered((uint32_t)(best >> 8));
+            outIdx = widx;
+        }
+    }
+}
+
+POLAR_DEV float sclf_metric(const SclCtx& c) { return __int_as_float(c.metric); }
+
+// sign bits of 32 consecutive LLRs (or the whole block when shorter), LSB first
+POLAR_DEV uint32_t sclf_sign_word(const FWords& src, int n, int bw)
+{
+    uint32_t w = 0;
+    const int cnt = min(32, n);
+    for (int t = 0; t < cnt; ++t) w |= (fbits(src(32 * bw + t)) >> 31) << t;
+    return w;
+}
+
+// ---------------------------------------------------------------- leaves
+// RateZero: scl_avx_float.cpp:320-340
+template <int L>
+POLAR_DEV void sclf_leaf_r0(SclCtx& c, int s, int lgP, bool isRight)
+{
+    const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
+    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    float pun = 0.0f;
+    if (g == 0) pun = sclf_lane_reduce(src, n, [](float x) { return x < 0.0f ? x : 0.0f; });
+    pun = __shfl_sync(FULL_MASK, pun, c.fb + ((c.gl << lgG) & (L - 1)));
+    if (c.gl < (1 << lgP)) c.metric = __float_as_int(__fadd_rn(sclf_metric(c), pun));
+    uint32_t* out = scl_bits_out(c, q, s, isRight);
+    const int nbw = s >= 5 ? 1 << (s - 5) : 1;
+    for (int j = g; j < nbw; j += G) out[j] = 0u;
+    scl_finish_leaf(c, s, isRight);
+}
+
+// Repetition (blocks of 2 and 4 only): scl_avx_float.cpp:432-481
+template <int L>
+POLAR_DEV void sclf_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
+{
+    constexpr int lgL = Log2<L>::v;
+    const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
+    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    float z = 0.0f, o = 0.0f;
+    if (g == 0) {
+        z = sclf_lane_reduce(src, n, [](float x) { return x < 0.0f ? x : 0.0f; });
+        o = sclf_lane_reduce(src, n, [](float x) { return x > 0.0f ? x : 0.0f; });
+    }
+    const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
+    z = __shfl_sync(FULL_MASK, z, srcLane);
+    o = __shfl_sync(FULL_MASK, o, srcLane);
+    const float m = sclf_metric(c);
+    const float cand[2] = { __fadd_rn(m, z), __fadd_rn(m, -o) };
+    const int lgPo = min(lgL, lgP + 1);
+    float outMet;
+    int outIdx;
+    sclf_select<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
+    scl_adopt(c, __float_as_int(outMet), (outIdx >> 1) & (L - 1));
+    const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
+    const int kq = __shfl_sync(FULL_MASK, outIdx & 1, c.fb + qo);
+    uint32_t* out = scl_bits_out(c, qo, s, isRight);
+    if (go == 0) out[0] = kq ? (1u << n) - 1u : 0u;
+    scl_finish_leaf(c, s, isRight);
+}
+
+// RateOne (scl_avx_float.cpp:356-419) and SPC (:498-617)
+template <int L>
+POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSpc)
+{
+    constexpr int lgL = Log2<L>::v;
+    const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
+    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    float a[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
+    int idx[4] = { 0, 0, 0, 0 };
+    int par = 0;
+    if (g == 0) {
+        if (isSpc) {
+            uint32_t px = 0;
+            for (int i = 0; i < n; ++i) px ^= fbits(src(i));
+            par = (int)(px >> 31);
+        }
+        sclf_weak_search(src, n, a, idx);
+    }
+    const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
+#pragma unroll
+    for (int t = 0; t < 4; ++t) a[t] = __shfl_sync(FULL_MASK, a[t], srcLane);
+    const uint32_t pk01 = __shfl_sync(FULL_MASK, (uint32_t)idx[0] | ((uint32_t)idx[1] << 16), srcLane);
+    const uint32_t pk23 = __shfl_sync(FULL_MASK, (uint32_t)idx[2] | ((uint32_t)idx[3] << 16), srcLane);
+    par = __shfl_sync(FULL_MASK, par, srcLane);
+    float m = sclf_metric(c);
+    float cand[8];
+    auto sub = [](float x, float y) { return __fadd_rn(x, -y); };
+    if (isSpc) {
+        const float inv = par ? 0.0f : 1.0f;
+        if (par) m = sub(m, a[0]);
+        const float mw = sub(m, __fmul_rn(inv, a[0]));
+        cand[0] = m;
+        cand[1] = sub(mw, a[1]);
+        cand[2] = sub(mw, a[2]);
+        cand[3] = sub(mw, a[3]);
+        cand[4] = sub(sub(m, a[1]), a[2]);
+        cand[5] = sub(sub(m, a[1]), a[3]);
+        cand[6] = sub(sub(m, a[2]), a[3]);
+        cand[7] = sub(sub(sub(mw, a[1]), a[2]), a[3]);
+    } else {
+        cand[0] = m;
+        cand[1] = sub(m, a[0]);
+        cand[2] = sub(m, a[1]);
+        cand[3] = sub(sub(m, a[0]), a[1]);
+        cand[4] = cand[5] = cand[6] = cand[7] = 0.0f;
+    }
+    const int lgF = isSpc ? 3 : 2;
+    const int lgPo = min(lgL, lgP + lgF);
+    float outMet;
+    int outIdx;
+    sclf_select<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
+    const int srcPath = (outIdx >> lgF) & (L - 1), kind = outIdx & ((1 << lgF) - 1);
+    const uint32_t s01 = __shfl_sync(FULL_MASK, pk01, c.fb + srcPath), s23 = __shfl_sync(FULL_MASK, pk23, c.fb + srcPath);
+    const int sp = __shfl_sync(FULL_MASK, par, c.fb + srcPath);
+    const uint32_t table = isSpc ? (sp ? 0xEDB78421u : 0xFCA69530u) : 0x3210u;
+    const uint32_t fmask = (table >> (4 * kind)) & 15u;
+    scl_adopt(c, __float_as_int(outMet), srcPath);
+    // the new path's bits: sign(llr) with the chosen flips (an index past a short block flips nothing)
+    const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
+    const uint32_t fm = __shfl_sync(FULL_MASK, fmask, c.fb + qo);
+    const uint32_t p01 = __shfl_sync(FULL_MASK, s01, c.fb + qo), p23 = __shfl_sync(FULL_MASK, s23, c.fb + qo);
+    const FWords srcn = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo));
+    uint32_t* out = scl_bits_out(c, qo, s, isRight);
+    const int nbw = s >= 5 ? 1 << (s - 5) : 1;
+    const uint32_t f[4] = { p01 & 0xFFFFu, p01 >> 16, p23 & 0xFFFFu, p23 >> 16 };
+    for (int j = go; j < nbw; j += Go) {
+        uint32_t w = sclf_sign_word(srcn, n, j);
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (((fm >> t) & 1u) && (int)f[t] < n && (int)(f[t] >> 5) == j) w ^= 1u << (f[t] & 31u);
+        out[j] = w;
+    }
+    scl_finish_leaf(c, s, isRight);
+}
+
+// ---------------------------------------------------------------- the kernel
+template <int L>
+__global__ void __launch_bounds__(256) scl_f32_kernel(const __grid_constant__ DecodeParams p,
+                                                      const __grid_constant__ Schedule sched)
+{
+    constexpr int lgL = Log2<L>::v, FPW = 32 / L;
+    extern __shared__ __align__(16) uint32_t smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpsPerBlock = blockDim.x >> 5;
+    uint32_t* base = smem + warp * p.warpW;
+    uint32_t* scr = base + FPW * p.frameW;
+    SclCtx c;
+    c.gl = lane & (L - 1);
+    c.fb = lane & ~(L - 1);
+    const int fi = lane >> lgL;
+    c.llr = base + fi * p.frameW;
+    c.bits = c.llr + L * p.slotW;
+    c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + c.fb : nullptr;
+    c.slotW = p.slotW;
+    c.bitBW = p.bitBW;
+    c.bitB1 = p.bitB1;
+    c.bitSlotW = p.bitSlotW;
+    c.lgN = p.lgN;
+    c.smemStages = p.smemStages;
+
+    const long long nQuads = (p.nFrames + FPW - 1) / FPW;
+    for (long long qb = blockIdx.x; qb * warpsPerBlock < nQuads; qb += gridDim.x) {
+        const bool live = qb * warpsPerBlock + warp < nQuads;
+        const long long quad = live ? qb * warpsPerBlock + warp : nQuads - 1;
+        const long long myFrame = min(quad * FPW + fi, p.nFrames - 1);
+        c.chan = reinterpret_cast<const uint32_t*>(static_cast<const float*>(p.llr) + myFrame * p.N);
+        c.metric = __float_as_int(0.0f); // every frame starts a fresh list (see the header)
+        c.llrPtr = 0ull;
+        c.lbPtr = 0ull;
+        int lgPfinal = 0;
+        for (int pc = 0;; ++pc) {
+            const uint32_t op = sched.ops[pc];
+            const uint32_t code = POLAR_OP_CODE(op);
+            if (code == OP_END) break;
+            const int s = (int)POLAR_OP_STAGE(op), lgP = (int)POLAR_OP_LGP(op);
+            const bool isRight = (POLAR_OP_FLAGS(op) & OPF_RIGHT) != 0;
+            if (p.lockstep) __syncthreads();
+            switch (code) {
+            case OP_F: sclf_op_fg<L, false>(c, s, lgP); break;
+            case OP_G: sclf_op_fg<L, true>(c, s, lgP); break;
+            case OP_COMBINE: scl_op_combine<L>(c, s, lgP, isRight); break;
+            case OP_SCL_R0: sclf_leaf_r0<L>(c, s, lgP, isRight); lgPfinal = lgP; break;
+            case OP_SCL_REP: sclf_leaf_rep<L>(c, s, lgP, isRight); lgPfinal = min(lgL, lgP + 1); break;
+            case OP_SCL_R1: sclf_leaf_flip<L>(c, s, lgP, isRight, false); lgPfinal = min(lgL, lgP + 2); break;
+            case OP_SCL_SPC: sclf_leaf_flip<L>(c, s, lgP, isRight, true); lgPfinal = min(lgL, lgP + 3); break;
+            default: break;
+            }
+        }
+        scl_extract_best_path<L>(p, c, base, scr, lane, live, quad, lgPfinal);
+    }
+}
+
+} // namespace polar

@@ -533,6 +533,59 @@ POLAR_DEV void scl_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSpc
     scl_write_flipped<L>(c, s, lgPo, isRight, fm, s01, s23);
 }
 
+// extractBestPath (scl_fip_char.cpp:816-855, scl_avx_float.cpp:711-750): first path in list order that passes
+// the detector, else the most likely one.  The whole warp works on one frame of the quad at a time.
+template <int L>
+POLAR_DEV void scl_extract_best_path(const DecodeParams& p, const SclCtx& c, uint32_t* base, uint32_t* scr, int lane,
+                                     bool live, long long quad, int lgPfinal)
+{
+    constexpr int FPW = 32 / L;
+    const int P = 1 << lgPfinal;
+    uint32_t* outw = scr;
+    uint32_t* cw = scr + ((p.K + 31) >> 5);
+    const int top = p.lgN - 1, nW = max(p.N >> 5, 1);
+    const uint32_t slotA = (uint32_t)(c.lbPtr >> (5 * top)) & 31u; // where this lane's path keeps its left half
+    for (int f = 0; f < FPW && live; ++f) {
+        const long long frame = quad * FPW + f;
+        if (frame >= p.nFrames) break;
+        const uint32_t* fbits = base + f * p.frameW + L * p.slotW;
+        bool okFlag = false;
+        for (int path = 0; path < P; ++path) {
+            // codeword estimate of this path: the root leaf's bits, or [left ^ right | right] of the two halves
+            const uint32_t sa = __shfl_sync(FULL_MASK, slotA, f * L + path);
+            if (p.rootLeaf) {
+                const uint32_t* root = fbits + path * p.bitSlotW + bit_woff(p.lgN);
+                for (int w = lane; w < nW; w += 32) cw[w] = root[w];
+            } else {
+                const uint32_t* left = fbits + sa * p.bitSlotW + bit_woff(top);
+                const uint32_t* right = fbits + path * p.bitSlotW + p.bitBW + ((top & 1) ? p.bitB1 : 0);
+                if (top >= 5) {
+                    const int hw = 1 << (top - 5);
+                    for (int w = lane; w < nW; w += 32) cw[w] = w < hw ? (left[w] ^ right[w]) : right[w - hw];
+                } else if (lane == 0) {
+                    cw[0] = (left[0] ^ right[0]) | (right[0] << (1 << top));
+                }
+            }
+            __syncwarp();
+            if (!p.systematic) warp_polar_transform(cw, p.N, lane);
+            const uint32_t syn = gather_info_and_syndrome(p, cw, outw, lane);
+            if (syn == 0u) { okFlag = true; break; }
+            if (!p.crcBits || (path == 0 && P == 1)) break;
+            // remember path 0's decision in case nobody passes (scl_fip_char.cpp:848-853)
+            if (path == 0)
+                for (int w = lane; w < ((p.K + 31) >> 5); w += 32) cw[nW + w] = outw[w];
+            __syncwarp();
+        }
+        if (!okFlag && P > 1 && p.crcBits) { // fall back to the most likely path
+            for (int w = lane; w < ((p.K + 31) >> 5); w += 32) outw[w] = cw[nW + w];
+            __syncwarp();
+        }
+        store_info(p, frame, outw, lane);
+        if (lane == 0) p.ok[frame] = okFlag ? 1 : 0;
+        __syncwarp();
+    }
+}
+
 // ---------------------------------------------------------------- the kernel
 template <int L>
 __global__ void __launch_bounds__(256) scl_i8_kernel(const __grid_constant__ DecodeParams p,
@@ -589,52 +642,7 @@ __global__ void __launch_bounds__(256) scl_i8_kernel(const __grid_constant__ Dec
             default: break;
             }
         }
-        // extractBestPath (scl_fip_char.cpp:816-855): first path in list order that passes the detector.
-        // The whole warp works on one frame of the quad at a time.
-        const int P = 1 << lgPfinal;
-        uint32_t* outw = scr;
-        uint32_t* cw = scr + ((p.K + 31) >> 5);
-        const int top = p.lgN - 1, nW = max(p.N >> 5, 1);
-        const uint32_t slotA = (uint32_t)(c.lbPtr >> (5 * top)) & 31u; // where this lane's path keeps its left half
-        for (int f = 0; f < FPW && live; ++f) {
-            const long long frame = quad * FPW + f;
-            if (frame >= p.nFrames) break;
-            const uint32_t* fbits = base + f * p.frameW + L * p.slotW;
-            bool okFlag = false;
-            for (int path = 0; path < P; ++path) {
-                // codeword estimate of this path: the root leaf's bits, or [left ^ right | right] of the two halves
-                const uint32_t sa = __shfl_sync(FULL_MASK, slotA, f * L + path);
-                if (p.rootLeaf) {
-                    const uint32_t* root = fbits + path * p.bitSlotW + bit_woff(p.lgN);
-                    for (int w = lane; w < nW; w += 32) cw[w] = root[w];
-                } else {
-                    const uint32_t* left = fbits + sa * p.bitSlotW + bit_woff(top);
-                    const uint32_t* right = fbits + path * p.bitSlotW + p.bitBW + ((top & 1) ? p.bitB1 : 0);
-                    if (top >= 5) {
-                        const int hw = 1 << (top - 5);
-                        for (int w = lane; w < nW; w += 32) cw[w] = w < hw ? (left[w] ^ right[w]) : right[w - hw];
-                    } else if (lane == 0) {
-                        cw[0] = (left[0] ^ right[0]) | (right[0] << (1 << top));
-                    }
-                }
-                __syncwarp();
-                if (!p.systematic) warp_polar_transform(cw, p.N, lane);
-                const uint32_t syn = gather_info_and_syndrome(p, cw, outw, lane);
-                if (syn == 0u) { okFlag = true; break; }
-                if (!p.crcBits || (path == 0 && P == 1)) break;
-                // remember path 0's decision in case nobody passes (scl_fip_char.cpp:848-853)
-                if (path == 0)
-                    for (int w = lane; w < ((p.K + 31) >> 5); w += 32) cw[nW + w] = outw[w];
-                __syncwarp();
-            }
-            if (!okFlag && P > 1 && p.crcBits) { // fall back to the most likely path
-                for (int w = lane; w < ((p.K + 31) >> 5); w += 32) outw[w] = cw[nW + w];
-                __syncwarp();
-            }
-            store_info(p, frame, outw, lane);
-            if (lane == 0) p.ok[frame] = okFlag ? 1 : 0;
-            __syncwarp();
-        }
+        scl_extract_best_path<L>(p, c, base, scr, lane, live, quad, lgPfinal);
     }
 }
 

@@ -32,6 +32,8 @@ WORKLOADS = {
                     label="Fast-SSC int8, N=1024 K=512, BB frozen set, Eb/N0=2dB"),
     "fastssc_f32": dict(N=256, K=128, ctype="BB", L=1, crc=0, frames=1 << 20, e2e_frames=1 << 19, fmt="f32",
                         label="Fast-SSC fp32, N=256 K=128, BB frozen set, Eb/N0=2dB"),
+    "scl8_f32": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 17, e2e_frames=1 << 17, fmt="f32",
+                     label="SCL fp32 L=8 + CRC16, N=1024 K=512, 5G frozen set, Eb/N0=2dB"),
     "scl32": dict(N=2048, K=1024, ctype="BB", L=32, crc=32, frames=1 << 16, e2e_frames=1 << 16,
                   label="SCL L=32 + CRC32, N=2048 K=1024, BB frozen set, int8 LLR, Eb/N0=2dB"),
 }

@@ -105,6 +105,29 @@ def test_fastssc_f32_parity(gpu, N, K, ctype, crc, n, sysm):
         _compare(dec, KIND_FASTSSC_F32, N, frozen, 1, sysm, crc, llr, "fastssc f32 N=%d %s sys=%d" % (N, name, sysm))
 
 
+SCL_F32_CASES = [
+    # N, K, construction, L, crc, frames
+    (1024, 512, "5G", 8, 16, 48), (1024, 512, "BB", 4, 0, 32), (256, 128, "BB", 8, 8, 64), (128, 64, "BB", 2, 8, 64),
+    (64, 32, "BB", 16, 0, 64), (512, 384, "BB", 8, 32, 32), (32, 16, "BB", 8, 8, 64), (8, 4, "BB", 4, 0, 64),
+    (2048, 1024, "BB", 32, 32, 8), (4096, 2048, "BB", 4, 16, 8), (1024, 512, "BE", 1, 16, 32), (16, 8, "BB", 32, 0, 64),
+]
+
+
+@pytest.mark.parametrize("N,K,ctype,L,crc,n", SCL_F32_CASES)
+@pytest.mark.parametrize("sysm", [1, 0])
+def test_scl_f32_parity(gpu, N, K, ctype, L, crc, n, sysm):
+    """SclAvxFloat with every frame decoded by a fresh list (the reference object carries path 0's metric over
+    from frame to frame, scl_avx_float.cpp:46-56,102-108, so only a fresh object per frame is a function of
+    the frame): float sums in the reference's order, ties through its selection sort."""
+    frozen = ap.frozen_bits(N, K, 0.0, ctype)
+    dec = ap.PolarDecoder(N, L, frozen, "float")
+    dec._kind = ap.KIND_SCL_F32
+    dec.setErrorDetection(crc)
+    dec.setSystematic(bool(sysm))
+    for name, llr in _float_workloads(KIND_SCL_F32, N, frozen, n, crc):
+        _compare(dec, KIND_SCL_F32, N, frozen, L, sysm, crc, llr, "scl f32 N=%d L=%d %s sys=%d" % (N, L, name, sysm))
+
+
 def test_float_llr_into_int8_decoder(gpu):
     """decode_vector(const float*) on a char decoder quantises like CharContainer::insertLlr."""
     N, K = 1024, 512
