@@ -108,10 +108,10 @@ public:
         delete[] mOutputContainer;
         if (FLOAT) {
             mLlrContainer = new FloatContainer(blockLength);
-            mBitContainer = new FloatContainer(blockLength, frozenBits);
+            mBitContainer = new FloatContainer(blockLength, mFrozenBits);
         } else {
             mLlrContainer = new CharContainer(blockLength);
-            mBitContainer = new CharContainer(blockLength, frozenBits);
+            mBitContainer = new CharContainer(blockLength, mFrozenBits);
         }
         mOutputContainer = new unsigned char[(blockLength - frozenBits.size() + 7) / 8];
         mHandle.sys = -1; // force a rebuild
