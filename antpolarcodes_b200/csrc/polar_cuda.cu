@@ -141,7 +141,7 @@ int setup_decoder_geometry(polar_code* c)
         // what sets the resident warp count; region A of the bit slots holds stages 0..lgN-1 (the root is
         // assembled by the epilogue), region B is a ping-pong pair.
         // (fp32 lists: one float per word, stage s at word 2^s - 1 of the slot)
-        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 9 ? 2 : (c->lgN >= 7 ? 1 : 0));
+        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 9 ? (sclF32 ? 3 : 2) : (c->lgN >= 7 ? 1 : 0));
         nSpill = std::max(0, std::min(nSpill, c->lgN - 5));
         if (sclF32) // keep a warp's footprint within reach of a few resident warps per SM
             while (nSpill < c->lgN - 5 && (size_t)32 * f32_woff(c->lgN - nSpill) * 4 > 96 * 1024) ++nSpill;
@@ -169,10 +169,10 @@ int setup_decoder_geometry(polar_code* c)
                                   : 32 * ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
         c->kernel = sclF32 ? pick_sclf_kernel(L) : pick_scl_kernel(L);
     } else if (c->kind == POLAR_KIND_FASTSSC_F32) {
-        // fp32 Fast-SSC: same row stack, one float per word; stage s sits at row 2^s - 1.  Stages from 7 up
-        // (128 floats and more) go to the L2-resident scratch.
+        // fp32 Fast-SSC: same row stack, one float per word; stage s sits at row 2^s - 1.  Stages from 6 up
+        // (64 floats and more) go to the L2-resident scratch.
         const bool rootLeaf = !c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN;
-        int keep = env_int("POLAR_CUDA_F32_SMEM_STAGES", 7);
+        int keep = env_int("POLAR_CUDA_F32_SMEM_STAGES", 6);
         g.smemStages = rootLeaf ? c->lgN : std::max(3, std::min(keep, c->lgN));
         const int nSpill = c->lgN - g.smemStages;
         const int imgRows = (8 * c->kb + 31) / 32;
@@ -221,9 +221,9 @@ int setup_decoder_geometry(polar_code* c)
     const int forceW = env_int("POLAR_CUDA_WARPS_PER_BLOCK", 0);
     // equal resident warps: blocks of 4 warps first (the lockstep barrier then spans 4 warps, one per scheduler)
     // (the Fast-SSC kernels take the widest block instead: one barrier domain per SM)
-    static const int sclOrder[] = { 4, 6, 8, 5, 7, 3, 2, 1 };
-    static const int scOrder[] = { 16, 12, 8, 6, 4, 3, 2, 1 };
-    for (int i = 0; i < 8; ++i) {
+    static const int sclOrder[] = { 4, 6, 8, 5, 7, 3, 2, 1, 12, 16, 10, 9 };
+    static const int scOrder[] = { 16, 12, 8, 6, 4, 3, 2, 1, 14, 10, 7, 5 };
+    for (int i = 0; i < 12; ++i) {
         const int w = scl ? sclOrder[i] : scOrder[i];
         if (forceW && w != forceW) continue;
         if (!scl && w > (wide ? 16 : 8)) continue; // launch bounds of the Fast-SSC kernels

@@ -588,7 +588,7 @@ POLAR_DEV void scl_extract_best_path(const DecodeParams& p, const SclCtx& c, uin
 
 // ---------------------------------------------------------------- the kernel
 template <int L>
-__global__ void __launch_bounds__(256) scl_i8_kernel(const __grid_constant__ DecodeParams p,
+__global__ void __launch_bounds__(512) scl_i8_kernel(const __grid_constant__ DecodeParams p,
                                                      const __grid_constant__ Schedule sched)
 {
     constexpr int lgL = Log2<L>::v, FPW = 32 / L;
