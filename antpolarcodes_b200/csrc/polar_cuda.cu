@@ -159,7 +159,7 @@ int setup_decoder_geometry(polar_code* c)
         int bslot = bitA + stageWords(topEven) + stageWords(std::max(topOdd, 1));
         while (bslot % L != 1 % L) ++bslot;
         g.bitSlotW = bslot;
-        int frame = L * g.slotW + L * g.bitSlotW;
+        int frame = L * g.slotW + L * g.bitSlotW + 9 * L; // + select scratch (candidate keys, swap history)
         while (frame % 32 != L % 32) ++frame;
         g.frameW = frame;
         g.scratchW = 2 * ((c->K + 31) / 32) + nW + 4;

@@ -368,6 +368,7 @@ __global__ void __launch_bounds__(512) scl_f32_kernel(const __grid_constant__ De
     const int fi = lane >> lgL;
     c.llr = base + fi * p.frameW;
     c.bits = c.llr + L * p.slotW;
+    c.sel = c.bits + L * p.bitSlotW;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + c.fb : nullptr;
     c.slotW = p.slotW;
     c.bitBW = p.bitBW;

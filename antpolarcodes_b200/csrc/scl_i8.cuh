@@ -52,6 +52,7 @@ struct SclCtx {
     uint32_t* llr;    // this lane's frame: LLR slots (shared memory)
     uint32_t* bits;   // this lane's frame: bit slots (shared memory)
     uint32_t* spill;  // this lane's frame: first column of the frame in the warp's spill scratch
+    uint32_t* sel;    // this lane's frame: select scratch (9 L words: candidate keys, swap history)
     int gl, fb;       // lane within the frame's group, first lane of the group
     int slotW, bitBW, bitB1, bitSlotW, lgN, smemStages;
     int metric;
@@ -163,6 +164,19 @@ POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_
         const int words = 1 << (s - 2);
         const uint32_t* srcb = src + words * ss;
         int w = g;
+        if (G == 1) { // a lane owns the path: the four words of a batch share one word of left bits
+            for (; w + 3 < words; w += 4) {
+                uint32_t a[4], b[4];
+                const uint32_t lw = lb[w >> 3] >> ((w & 4) * 4);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    a[t] = scl_ld<SG>(src + (w + t) * ss, chan);
+                    b[t] = scl_ld<SG>(srcb + (w + t) * ss, chan);
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t) scl_st<DG>(dst + (w + t) * ds, g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t))));
+            }
+        }
         for (; w + 3 * G < words; w += 4 * G) {
             uint32_t a[4], b[4], n[4];
 #pragma unroll
@@ -254,10 +268,11 @@ POLAR_DEV void scl_weak_search(const Words& src, int s, int lgG, int g, int (&va
         const int words = 1 << (s - 2);
         for (int w = g; w < words; w += G) {
             if (w == 0) continue;
-            const uint32_t x = src(w);
+            uint32_t m = uabs4(src(w));
+            m -= (m >> 7) & 0x01010101u; // |max(x,-127)| per byte
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                uint32_t key = ((uint32_t)abs127_byte(x, e) << 16) | (uint32_t)(4 * w + e);
+                uint32_t key = prmt(m, (uint32_t)(4 * w + e), 0x7054u | (e << 8)); // (|x_e| << 16) | position
 #pragma unroll
                 for (int r = 0; r < K; ++r) {
                     const uint32_t lo = min(T[r], key);
@@ -279,12 +294,13 @@ POLAR_DEV void scl_weak_search(const Words& src, int s, int lgG, int g, int (&va
         }
     }
     // head: elements 0..3 can be displaced by the swaps; simulate the selection sort on them
-    const uint32_t w0 = src(0);
+    uint32_t m0 = uabs4(src(0));
+    m0 -= (m0 >> 7) & 0x01010101u;
     int ha[4], cur[4];
     bool alive[4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-        ha[e] = abs127_byte(w0, e);
+        ha[e] = (int)((m0 >> (8 * e)) & 0xFFu);
         cur[e] = e;
         alive[e] = e < n;
     }
@@ -325,52 +341,65 @@ POLAR_DEV void scl_weak_search(const Words& src, int s, int lgG, int g, int (&va
 
 // Keep the nOut best of M = P*F candidates in the reference's order (simplePartialSortDescending,
 // arrayfuncs.h:161-183: selection sort that SWAPS the displaced element to the winner's place, strict >,
-// so ties go to the lower current position).  Lane q < P of the group holds the candidates at list
-// positions q*F .. q*F+F-1, F = 2^lgF <= FMAX (unused registers hold key 0).  Out (lane j < nOut of the
-// group): metric and original candidate index of list entry j.
+// so ties go to the lower current position).  Lane q < P of the group contributes the candidates at list
+// positions q*F .. q*F+F-1, F = 2^lgF <= FMAX.  Out (lane j < nOut of the group): metric and original
+// candidate index of list entry j.
+// The keys (metric, 255 - current position) live in the frame's select scratch (position p at word
+// (p % F) * L + p / F: conflict free for the owner lanes); every lane only carries the maximum of its own F
+// keys.  Step i: group maximum -> winner position w; the element at position i moves to w (key rewritten with
+// its new position), position i is final; the two owner lanes refresh their maxima.  The swap history
+// w_0 .. w_i then tells every output lane which original candidate it received.
 template <int L, int FMAX>
 POLAR_DEV void scl_select(const SclCtx& c, const int (&cand)[FMAX], int lgF, int lgP, int nOut, int& outMet, int& outIdx)
 {
     const int gl = c.gl, F = 1 << lgF;
-    uint32_t key[FMAX];
-    int orig[FMAX];
+    uint32_t* ks = c.sel;          // L * 8 key words
+    uint32_t* hs = c.sel + 8 * L;  // L history words
+    const bool act = gl < (1 << lgP);
+    uint32_t lmax = 0u;
 #pragma unroll
     for (int k = 0; k < FMAX; ++k) {
-        const int pos = (gl << lgF) + k;
-        key[k] = (gl < (1 << lgP) && k < F) ? (((uint32_t)(cand[k] + SCL_METRIC_BIAS) << 8) | (uint32_t)(255 - pos)) : 0u;
-        orig[k] = pos;
+        if (k < F) {
+            const int pos = (gl << lgF) + k;
+            const uint32_t key = act ? (((uint32_t)(cand[k] + SCL_METRIC_BIAS) << 8) | (uint32_t)(255 - pos)) : 0u;
+            ks[k * L + gl] = key;
+            lmax = max(lmax, key);
+        }
     }
+    __syncwarp();
     outMet = 0;
-    outIdx = 0;
+    int myW = 0;
 #pragma unroll 1
     for (int i = 0; i < nOut; ++i) {
-        uint32_t m = key[0];
-#pragma unroll
-        for (int k = 1; k < FMAX; ++k) m = max(m, key[k]);
-        const uint32_t best = list_max<L>(m);
-        const int pos = 255 - (int)(best & 255u), wl = pos >> lgF, wk = pos & (F - 1);
-        const int il = i >> lgF, ik = i & (F - 1);
-        int wo = orig[0], io = orig[0];
-        uint32_t ikl = key[0];
-#pragma unroll
-        for (int k = 1; k < FMAX; ++k) {
-            if (k == wk) wo = orig[k];
-            if (k == ik) { io = orig[k]; ikl = key[k]; }
-        }
-        const int widx = __shfl_sync(FULL_MASK, wo, c.fb + wl);
-        const uint32_t ikey = __shfl_sync(FULL_MASK, ikl, c.fb + il); // the element now at position i
-        const int iidx = __shfl_sync(FULL_MASK, io, c.fb + il);
-        const uint32_t moved = (ikey & ~255u) | (uint32_t)(255 - pos);
-#pragma unroll
-        for (int k = 0; k < FMAX; ++k) {
-            if (gl == wl && k == wk) { key[k] = moved; orig[k] = iidx; } // it moves to the winner's place ...
-            if (gl == il && k == ik) key[k] = 0u;                        // ... and position i is final
-        }
+        const uint32_t best = list_max<L>(lmax);
+        const int pos = 255 - (int)(best & 255u), wl = pos >> lgF, il = i >> lgF;
+        const int wa = (pos & (F - 1)) * L + wl, ia = (i & (F - 1)) * L + il;
         if (gl == i) {
             outMet = (int)(best >> 8) - SCL_METRIC_BIAS;
-            outIdx = widx;
+            myW = pos;
+        }
+        const uint32_t ikey = ks[ia]; // the element now at position i
+        __syncwarp();
+        if (gl == wl) ks[wa] = (ikey & ~255u) | (uint32_t)(255 - pos); // ... moves to the winner's place
+        if (gl == il) ks[ia] = 0u;                                     // position i is final
+        if (gl == 0) hs[i] = (uint32_t)pos;
+        __syncwarp();
+        if (gl == wl || gl == il) {
+            lmax = 0u;
+#pragma unroll
+            for (int k = 0; k < FMAX; ++k)
+                if (k < F) lmax = max(lmax, ks[k * L + gl]);
         }
     }
+    // which original candidate sits at position gl: follow the swaps backwards (the element found at w_t at step
+    // t came from position t' if an earlier step t' displaced its element to w_t)
+    int p = myW;
+    for (int t = nOut - 2; t >= 0; --t) {
+        const int wt = (int)hs[t];
+        if (t < gl && wt == p) p = t;
+    }
+    outIdx = p;
+    __syncwarp();
 }
 
 // After a fork: adopt the parent's lazy-copy vectors and metric.
@@ -602,6 +631,7 @@ __global__ void __launch_bounds__(512) scl_i8_kernel(const __grid_constant__ Dec
     const int fi = lane >> lgL;
     c.llr = base + fi * p.frameW;
     c.bits = c.llr + L * p.slotW;
+    c.sel = c.bits + L * p.bitSlotW;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + c.fb : nullptr;
     c.slotW = p.slotW;
     c.bitBW = p.bitBW;
