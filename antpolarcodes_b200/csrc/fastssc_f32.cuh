@@ -26,6 +26,8 @@ struct ScfCtx {
     uint32_t* spill;
     int lane, lgN, nw;    // nw = N
     int bitRow, chanRow, smemStages;
+    uint32_t* smLane;     // sm + lane
+    uint32_t* spillLane;  // spill + lane, rebased so that row f32_woff(s) is the row of spilled stage s
 };
 
 #define SCF_ROW(c, row) (c).sm[((row) << 5) + (c).lane]
@@ -34,11 +36,9 @@ __host__ __device__ inline int f32_woff(int s) { return (1 << s) - 1; } // row o
 
 POLAR_DEV float* scf_stage(const ScfCtx& c, int s)
 {
-    uint32_t* p;
-    if (s == c.lgN) p = c.sm + (c.chanRow << 5) + c.lane;
-    else if (s >= c.smemStages) p = c.spill + ((f32_woff(s) - f32_woff(c.smemStages)) << 5) + c.lane;
-    else p = c.sm + (f32_woff(s) << 5) + c.lane;
-    return reinterpret_cast<float*>(p);
+    if (s == c.lgN) return reinterpret_cast<float*>(c.sm + (c.chanRow << 5) + c.lane);
+    uint32_t* base = s >= c.smemStages ? c.spillLane : c.smLane; // both already offset to the lane's column
+    return reinterpret_cast<float*>(base + (f32_woff(s) << 5));
 }
 
 POLAR_DEV uint32_t fbits(float x) { return __float_as_uint(x); }
@@ -300,6 +300,8 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_f32_kernel(const 
     c.smemStages = p.smemStages;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW : nullptr;
     c.lastFrame = p.nFrames - 1;
+    c.smLane = c.sm + lane;
+    c.spillLane = c.spill ? c.spill - (f32_woff(p.smemStages) << 5) + lane : c.smLane;
     uint32_t* tileA = c.sm + (p.tileRow << 5);
     uint32_t* tileB = tileA + 33 * 32;
     const float* myA = reinterpret_cast<const float*>(tileA + lane * 33);
@@ -327,7 +329,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_f32_kernel(const 
             const uint32_t op = sched.ops[pc];
             const uint32_t code = POLAR_OP_CODE(op);
             if (code == OP_END) break;
-            if (p.lockstep) __syncthreads();
+            if (p.lockstep && (pc & (p.lockstep - 1)) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
             const int s = (int)POLAR_OP_STAGE(op), pos = (int)POLAR_OP_POS(op), n = 1 << s;
             const bool top = (s + 1 == c.lgN) && c.chanRow < 0; // parent block = channel row in global memory
             switch (code) {

@@ -27,6 +27,8 @@ struct ScCtx {
     uint32_t* spill;       // this warp's rows of the L2-resident scratch (stages >= smemStages), or null
     int lane, lgN, nw;     // nw = N/4
     int bitRow, tileRow, chanRow, smemStages;
+    uint32_t* smLane;      // sm + lane
+    uint32_t* spillLane;   // spill + lane, rebased so that row llr_woff(s) is the row of spilled stage s
 };
 
 #define SC_ROW(c, row) (c).sm[((row) << 5) + (c).lane]
@@ -37,8 +39,8 @@ struct ScCtx {
 POLAR_DEV uint32_t* sc_stage(const ScCtx& c, int s)
 {
     if (s == c.lgN) return c.sm + (c.chanRow << 5) + c.lane;
-    if (s >= c.smemStages) return c.spill + ((llr_woff(s) - llr_woff(c.smemStages)) << 5) + c.lane;
-    return c.sm + (llr_woff(s) << 5) + c.lane;
+    uint32_t* base = s >= c.smemStages ? c.spillLane : c.smLane; // both already offset to the lane's column
+    return base + (llr_woff(s) << 5);
 }
 
 // Source views of a parent block split in halves a = [0, words), b = [words, 2*words)
@@ -293,6 +295,8 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
     c.smemStages = p.smemStages;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW : nullptr;
     c.lastFrame = p.nFrames - 1;
+    c.smLane = c.sm + lane;
+    c.spillLane = c.spill ? c.spill - (llr_woff(p.smemStages) << 5) + lane : c.smLane;
     uint32_t* tileA = c.sm + (p.tileRow << 5);
     uint32_t* tileB = tileA + 33 * 32;
     const uint32_t* myA = tileA + lane * 33;
@@ -320,7 +324,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
             const uint32_t op = sched.ops[pc];
             const uint32_t code = POLAR_OP_CODE(op);
             if (code == OP_END) break;
-            if (p.lockstep) __syncthreads();
+            if (p.lockstep && (pc & (p.lockstep - 1)) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
             const int s = (int)POLAR_OP_STAGE(op), pos = (int)POLAR_OP_POS(op);
             const bool longForm = (POLAR_OP_FLAGS(op) & OPF_LONG) != 0;
             const bool top = (s + 1 == c.lgN) && c.chanRow < 0; // parent block = channel row in global memory

@@ -69,6 +69,8 @@ struct polar_code {
     uint8_t* dInfo = nullptr;
     size_t stageFrames = 0;
     int stageLlrBytes = 0;
+    cudaStream_t pipe[2] = { nullptr, nullptr }; // HOST-buffer calls: double-buffered copy / compute pipeline
+    cudaEvent_t pipeDone[2] = { nullptr, nullptr };
     long launches = 0;
 };
 
@@ -141,7 +143,7 @@ int setup_decoder_geometry(polar_code* c)
         // what sets the resident warp count; region A of the bit slots holds stages 0..lgN-1 (the root is
         // assembled by the epilogue), region B is a ping-pong pair.
         // (fp32 lists: one float per word, stage s at word 2^s - 1 of the slot)
-        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 9 ? (sclF32 ? 3 : 2) : (c->lgN >= 7 ? 1 : 0));
+        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 10 ? (sclF32 ? 4 : 3) : c->lgN >= 9 ? (sclF32 ? 3 : 2) : (c->lgN >= 7 ? 1 : 0));
         nSpill = std::max(0, std::min(nSpill, c->lgN - 5));
         if (sclF32) // keep a warp's footprint within reach of a few resident warps per SM
             while (nSpill < c->lgN - 5 && (size_t)32 * f32_woff(c->lgN - nSpill) * 4 > 96 * 1024) ++nSpill;
@@ -219,9 +221,9 @@ int setup_decoder_geometry(polar_code* c)
         return fail(POLAR_E_UNSUPPORTED, "code does not fit in shared memory (N x listSize too large)");
     int bestWarps = 0, bestW = 1, bestB = 1;
     const int forceW = env_int("POLAR_CUDA_WARPS_PER_BLOCK", 0);
-    // equal resident warps: blocks of 4 warps first (the lockstep barrier then spans 4 warps, one per scheduler)
+    // equal resident warps: wide blocks first (one or two lockstep domains per SM keep the instruction fetch shared)
     // (the Fast-SSC kernels take the widest block instead: one barrier domain per SM)
-    static const int sclOrder[] = { 4, 6, 8, 5, 7, 3, 2, 1, 12, 16, 10, 9 };
+    static const int sclOrder[] = { 8, 16, 12, 6, 4, 10, 5, 7, 3, 2, 1, 9 };
     static const int scOrder[] = { 16, 12, 8, 6, 4, 3, 2, 1, 14, 10, 7, 5 };
     for (int i = 0; i < 12; ++i) {
         const int w = scl ? sclOrder[i] : scOrder[i];
@@ -291,6 +293,10 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab);
     cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
     cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns);
+    for (int i = 0; i < 2; ++i) {
+        if (c->pipe[i]) cudaStreamDestroy(c->pipe[i]);
+        if (c->pipeDone[i]) cudaEventDestroy(c->pipeDone[i]);
+    }
     delete c;
     return POLAR_OK;
 }
@@ -393,38 +399,16 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
     return POLAR_OK;
 }
 
-int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int mem, size_t nFrames,
-                            uint8_t* info_out, uint8_t* ok_out, void* stream)
+// One batch with DEVICE buffers on stream st: optional quantiser pre-pass + the decoder kernel.
+static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t nFrames, uint8_t* out, uint8_t* ok,
+                            cudaStream_t st)
 {
-    if (!c) return fail(POLAR_E_ARG, "null code handle");
-    if (c->kind == POLAR_KIND_ENC) return fail(POLAR_E_ARG, "handle is an encoder");
-    if (nFrames == 0) return POLAR_OK;
-    if (!llr || !info_out) return fail(POLAR_E_ARG, "null buffer");
-    if (llrType != POLAR_LLR_I8 && llrType != POLAR_LLR_F32) return fail(POLAR_E_ARG, "bad llr type");
-    if ((c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32) && llrType != POLAR_LLR_F32)
-        return fail(POLAR_E_ARG, "an fp32 decoder takes float LLRs");
-    CUDA_TRY(cudaSetDevice(c->device));
-    cudaStream_t st = (cudaStream_t)stream;
-    const int eb = llrType == POLAR_LLR_F32 ? 4 : 1;
     DecodeParams p = c->geo;
     p.infoPos = c->dInfoPos;
     p.crcTab = c->dSynTab;
     p.crcInit = c->synInit;
     p.nFrames = (long long)nFrames;
-    uint8_t* okDev = ok_out;
-    if (mem == POLAR_MEM_HOST) {
-        int rc = ensure_staging(c, nFrames, eb);
-        if (rc) return rc;
-        CUDA_TRY(cudaMemcpyAsync(c->dLlr, llr, nFrames * c->N * (size_t)eb, cudaMemcpyHostToDevice, st));
-        p.llr = c->dLlr; p.out = c->dOut; p.ok = c->dOk;
-    } else {
-        if (!okDev) { // the kernels always write the verdict
-            int rc = ensure_staging(c, nFrames, 0);
-            if (rc) return rc;
-            okDev = c->dOk;
-        }
-        p.llr = llr; p.out = info_out; p.ok = okDev;
-    }
+    p.llr = llr; p.out = out; p.ok = ok;
     p.spill = c->dSpill;
     p.runs = c->dRuns;
     p.nRuns = c->nRuns;
@@ -453,9 +437,70 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     c->kernel<<<grid, c->warpsPerBlock * 32, c->smemPerBlock, st>>>(p, c->sched);
     c->launches++;
     CUDA_TRY(cudaGetLastError());
-    if (mem == POLAR_MEM_HOST) {
-        CUDA_TRY(cudaMemcpyAsync(info_out, c->dOut, nFrames * (size_t)c->kb, cudaMemcpyDeviceToHost, st));
-        if (ok_out) CUDA_TRY(cudaMemcpyAsync(ok_out, c->dOk, nFrames, cudaMemcpyDeviceToHost, st));
+    return POLAR_OK;
+}
+
+int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int mem, size_t nFrames,
+                            uint8_t* info_out, uint8_t* ok_out, void* stream)
+{
+    if (!c) return fail(POLAR_E_ARG, "null code handle");
+    if (c->kind == POLAR_KIND_ENC) return fail(POLAR_E_ARG, "handle is an encoder");
+    if (nFrames == 0) return POLAR_OK;
+    if (!llr || !info_out) return fail(POLAR_E_ARG, "null buffer");
+    if (llrType != POLAR_LLR_I8 && llrType != POLAR_LLR_F32) return fail(POLAR_E_ARG, "bad llr type");
+    if ((c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32) && llrType != POLAR_LLR_F32)
+        return fail(POLAR_E_ARG, "an fp32 decoder takes float LLRs");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int eb = llrType == POLAR_LLR_F32 ? 4 : 1;
+    if (mem == POLAR_MEM_DEVICE) {
+        uint8_t* okDev = ok_out;
+        if (!okDev) { // the kernels always write the verdict
+            int rc = ensure_staging(c, nFrames, 0);
+            if (rc) return rc;
+            okDev = c->dOk;
+        }
+        return decode_on_device(c, llr, llrType, nFrames, info_out, okDev, st);
+    }
+    // HOST buffers: chunks of whole grid waves, double buffered over two internal streams, so that the H2D copy
+    // of chunk k+1 and the D2H copy of chunk k-1 run under the kernel of chunk k.  The kernels themselves are
+    // chained by events (they share the spill / quantiser scratch of the handle).
+    const int framesPerWarp = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32) ? 32 / c->L : 32;
+    const size_t wave = (size_t)framesPerWarp * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
+    const size_t targetBytes = (size_t)env_int("POLAR_CUDA_CHUNK_MB", 32) << 20;
+    size_t chunk = std::max<size_t>(1, targetBytes / ((size_t)c->N * eb) / wave) * wave;
+    if (chunk * 2 > nFrames || !env_int("POLAR_CUDA_PIPELINE", 1)) chunk = nFrames; // too small to split
+    const size_t nChunks = (nFrames + chunk - 1) / chunk;
+    const int depth = nChunks > 1 ? 2 : 1;
+    int rc = ensure_staging(c, chunk * depth, eb);
+    if (rc) return rc;
+    if (depth == 2 && !c->pipe[0]) {
+        for (int i = 0; i < 2; ++i) {
+            CUDA_TRY(cudaStreamCreateWithFlags(&c->pipe[i], cudaStreamNonBlocking));
+            CUDA_TRY(cudaEventCreateWithFlags(&c->pipeDone[i], cudaEventDisableTiming));
+        }
+    }
+    CUDA_TRY(cudaStreamSynchronize(st)); // work queued before this call on the caller's stream comes first
+    const uint8_t* src = static_cast<const uint8_t*>(llr);
+    for (size_t k = 0; k < nChunks; ++k) {
+        const size_t f0 = k * chunk, n = std::min(chunk, nFrames - f0);
+        const int h = depth == 2 ? (int)(k & 1) : 0;
+        cudaStream_t s = depth == 2 ? c->pipe[h] : st;
+        uint8_t* dL = static_cast<uint8_t*>(c->dLlr) + (size_t)h * chunk * c->N * eb;
+        uint8_t* dO = c->dOut + (size_t)h * chunk * c->kb;
+        uint8_t* dK = c->dOk + (size_t)h * chunk;
+        CUDA_TRY(cudaMemcpyAsync(dL, src + f0 * c->N * eb, n * c->N * (size_t)eb, cudaMemcpyHostToDevice, s));
+        if (depth == 2 && k > 0) CUDA_TRY(cudaStreamWaitEvent(s, c->pipeDone[h ^ 1], 0)); // kernel k-1 has finished
+        rc = decode_on_device(c, dL, llrType, n, dO, dK, s);
+        if (rc) return rc;
+        if (depth == 2) CUDA_TRY(cudaEventRecord(c->pipeDone[h], s));
+        CUDA_TRY(cudaMemcpyAsync(info_out + f0 * c->kb, dO, n * (size_t)c->kb, cudaMemcpyDeviceToHost, s));
+        if (ok_out) CUDA_TRY(cudaMemcpyAsync(ok_out + f0, dK, n, cudaMemcpyDeviceToHost, s));
+    }
+    if (depth == 2) {
+        CUDA_TRY(cudaStreamSynchronize(c->pipe[0]));
+        CUDA_TRY(cudaStreamSynchronize(c->pipe[1]));
+    } else {
         CUDA_TRY(cudaStreamSynchronize(st));
     }
     return POLAR_OK;

@@ -660,7 +660,7 @@ __global__ void __launch_bounds__(512) scl_i8_kernel(const __grid_constant__ Dec
             if (code == OP_END) break;
             const int s = (int)POLAR_OP_STAGE(op), lgP = (int)POLAR_OP_LGP(op);
             const bool isRight = (POLAR_OP_FLAGS(op) & OPF_RIGHT) != 0;
-            if (p.lockstep) __syncthreads();
+            if (p.lockstep && (pc & (p.lockstep - 1)) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
             switch (code) {
             case OP_F: scl_op_fg<L, false>(c, s, lgP); break;
             case OP_G: scl_op_fg<L, true>(c, s, lgP); break;

@@ -269,15 +269,23 @@ def run_ours(args, wl):
         alu = fps * info.laneOpsPerFrame / 1e12
         hbm = fps * info.bytesPerFrame / 1e9
         alu_bound = (info.laneOpsPerFrame / (alu_peak_max * 1e12)) > (info.bytesPerFrame / (hbm_peak * 1e9))
+        traffic, traffic_src = None, None
+        try:  # DRAM bytes per launch from the committed ncu capture of this kernel (profiles/traffic.json)
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+            if tj:
+                traffic, traffic_src = tj["dram_bytes"] / tj["frames"] * frames, tj["source"]
+        except Exception:
+            pass
         roof = {"bound": "alu_issue" if alu_bound else "hbm",
                 "achieved": alu if alu_bound else hbm, "peak": alu_peak_max if alu_bound else hbm_peak,
                 "unit": "Tlane-op/s" if alu_bound else "GB/s",
-                "frac": (alu / alu_peak_max) if alu_bound else hbm / hbm_peak, "traffic": None,
+                "frac": (alu / alu_peak_max) if alu_bound else hbm / hbm_peak, "traffic": traffic,
                 "peak_source": which + (" sm_max_mhz x 148 SM x 128 lanes" if alu_bound else " hbm copy"),
                 "frac_at_run_clock": alu / alu_peak_run,
                 "alu": {"lane_ops_per_frame": info.laneOpsPerFrame, "achieved_T": alu, "peak_T": alu_peak_max},
                 "hbm": {"bytes_per_frame": info.bytesPerFrame, "achieved_GBs": hbm, "peak_GBs": hbm_peak,
                         "frac": hbm / hbm_peak},
+                "traffic_source": traffic_src, "algorithmic_bytes": info.bytesPerFrame * frames,
                 "kernel_ms": k_ms, "frames_per_launch": frames}
         cpu = None
         try:

@@ -128,6 +128,31 @@ def test_scl_f32_parity(gpu, N, K, ctype, L, crc, n, sysm):
         _compare(dec, KIND_SCL_F32, N, frozen, L, sysm, crc, llr, "scl f32 N=%d L=%d %s sys=%d" % (N, L, name, sysm))
 
 
+@pytest.mark.parametrize("N,K,L,n", [(64, 32, 1, 200_000), (128, 64, 4, 90_000)])
+def test_host_buffer_pipeline(gpu, monkeypatch, N, K, L, n):
+    """HOST-buffer calls are split into grid-wave chunks and double buffered (copy under compute): the result must
+    not depend on the chunking, including a ragged last chunk."""
+    frozen = ap.frozen_bits(N, K, 0.0, "BB")
+    dec = ap.PolarDecoder(N, L, frozen, "char")
+    dec.setErrorDetection(8)
+    kind = KIND_SCL_I8 if L > 1 else KIND_FASTSSC_I8
+    rng = np.random.default_rng(5)
+    base, _ = awgn_llrs(N, frozen, 4096, 1.0, 8)
+    llr = base[rng.integers(0, len(base), n)]
+    llr[::7] = np.clip(llr[::7].astype(np.int16) + rng.integers(-20, 21, (len(llr[::7]), N)), -128, 127).astype(np.int8)
+    monkeypatch.setenv("POLAR_CUDA_PIPELINE", "0")
+    o0, k0 = dec.decode_batch(llr)
+    monkeypatch.setenv("POLAR_CUDA_PIPELINE", "1")
+    monkeypatch.setenv("POLAR_CUDA_CHUNK_MB", "1")
+    launches = dec._get().launches()
+    o1, k1 = dec.decode_batch(llr)
+    assert dec._get().launches() - launches >= 2, "the batch was not split"
+    assert np.array_equal(o0, o1) and np.array_equal(k0, k1)
+    for sl in (slice(0, 256), slice(n - 256, n)):
+        eo, ek = oracle_decode(kind, N, frozen, llr[sl], L, 1, 8)
+        assert np.array_equal(o1[sl], eo) and np.array_equal(k1[sl], ek)
+
+
 def test_float_llr_into_int8_decoder(gpu):
     """decode_vector(const float*) on a char decoder quantises like CharContainer::insertLlr."""
     N, K = 1024, 512
