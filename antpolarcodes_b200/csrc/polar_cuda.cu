@@ -224,9 +224,10 @@ int setup_decoder_geometry(polar_code* c)
     // equal resident warps: wide blocks first (one or two lockstep domains per SM keep the instruction fetch shared)
     // (the Fast-SSC kernels take the widest block instead: one barrier domain per SM)
     static const int sclOrder[] = { 8, 16, 12, 6, 4, 10, 5, 7, 3, 2, 1, 9 };
+    static const int sclF32Order[] = { 4, 6, 8, 5, 7, 3, 2, 1, 12, 16, 10, 9 }; // measured: small blocks win here
     static const int scOrder[] = { 16, 12, 8, 6, 4, 3, 2, 1, 14, 10, 7, 5 };
     for (int i = 0; i < 12; ++i) {
-        const int w = scl ? sclOrder[i] : scOrder[i];
+        const int w = sclF32 ? sclF32Order[i] : scl ? sclOrder[i] : scOrder[i];
         if (forceW && w != forceW) continue;
         if (!scl && w > (wide ? 16 : 8)) continue; // launch bounds of the Fast-SSC kernels
         const size_t smem = perWarp * w;

@@ -34,6 +34,8 @@ WORKLOADS = {
                         label="Fast-SSC fp32, N=256 K=128, BB frozen set, Eb/N0=2dB"),
     "scl8_f32": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 17, e2e_frames=1 << 17, fmt="f32",
                      label="SCL fp32 L=8 + CRC16, N=1024 K=512, 5G frozen set, Eb/N0=2dB"),
+    "encode": dict(N=256, K=128, ctype="BB", L=1, crc=0, frames=1 << 22, e2e_frames=1 << 21, encoder=True,
+                   label="packed butterfly encoder, systematic, N=256 K=128, BB frozen set"),
     "scl32": dict(N=2048, K=1024, ctype="BB", L=32, crc=32, frames=1 << 16, e2e_frames=1 << 16,
                   label="SCL L=32 + CRC32, N=2048 K=1024, BB frozen set, int8 LLR, Eb/N0=2dB"),
 }
@@ -151,20 +153,153 @@ def run_reference_arm(args, wl):
         return
     per_step = 20.0 / max(args.steps + args.warmup, 1)
     vals, ms = [], []
+    enc_info = None
+    if wl.get("encoder"):
+        enc_info = np.random.default_rng(1).integers(0, 256, (1 << 18, wl["K"] // 8), dtype=np.uint8)
     for s in range(args.warmup + args.steps):
-        v, nfr, t = time_reference(wl, frozen, llr, min(per_step, 4.0), threads)
+        if enc_info is not None:
+            v, nfr, t = time_reference_encoder(wl, frozen, enc_info, min(per_step, 4.0), threads)
+        else:
+            v, nfr, t = time_reference(wl, frozen, llr, min(per_step, 4.0), threads)
         if s >= args.warmup:
             vals.append(v)
             ms.append(t * 1e3)
     v = float(np.mean(vals))
     line = {"metric": METRIC if args.workload == "scl8" else wl["label"], "value": v, "unit": "Gbit/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(ms)), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic", "impl": "reference",
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8" if wl.get("encoder") else ("f32" if wl.get("fmt") == "f32" else "int8"), "data": "synthetic", "impl": "reference",
             "config": {"workload": wl["label"], "frames_per_step": "bounded sample (%d frames x repeats)" % sample},
             "cpu_baseline": {"value": v, "unit": "Gbit/s", "cores": threads, "kind": "reference",
                              "sample": "%d AWGN frames cycled for ~%.1f s per step, one SclFipChar/FastSscFipChar object per thread" % (sample, min(per_step, 4.0))},
             "e2e": {"value": v, "unit": "Gbit/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def time_reference_encoder(wl, frozen, info_host, seconds_target, threads):
+    """ButterflyFipPacked (oracle/_ref) on the host cores: one encoder object per thread, each on its own slice."""
+    from concurrent.futures import ThreadPoolExecutor
+    from polar_testlib import ref_encode
+    parts = np.array_split(info_host, threads)
+
+    def work(a):
+        ref_encode(wl["N"], frozen, a, 1, wl["crc"])
+    with ThreadPoolExecutor(threads) as ex:
+        t0 = time.perf_counter()
+        list(ex.map(work, parts))
+        t1 = time.perf_counter() - t0
+        rep = max(1, int(seconds_target / max(t1, 1e-6)))
+        t0 = time.perf_counter()
+        for _ in range(rep):
+            list(ex.map(work, parts))
+        t = time.perf_counter() - t0
+    n = info_host.shape[0]
+    return n * rep * wl["K"] / t / 1e9, n * rep, t
+
+
+def run_encoder(args, wl):
+    """Encoder::encode_vector over a batch (configs[1]): info bytes -> codeword bytes, CRC fused when configured."""
+    import torch
+    import torch.distributed as dist
+    import antpolarcodes_b200 as ap
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    N, K, crc = wl["N"], wl["K"], wl["crc"]
+    frames = args.frames or wl["frames"]
+    e2e_frames = min(args.e2e_frames or wl["e2e_frames"], frames)
+    frozen = ap.frozen_bits(N, K, 0.0, wl["ctype"])
+    enc = ap.PolarEncoder(N, frozen, device=local)
+    enc.setSystematic(True)
+    enc.setErrorDetection(crc)
+    g = torch.Generator(device=device)
+    g.manual_seed(0xE0C + rank)
+    info = torch.randint(0, 256, (frames, K // 8), dtype=torch.uint8, device=device, generator=g)
+    code = torch.empty((frames, N // 8), dtype=torch.uint8, device=device)
+    stream = torch.cuda.current_stream(device)
+    sp = stream.cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+    for _ in range(args.warmup):
+        enc.encode_batch(info, code, stream=sp)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    l0 = enc._get().launches()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    barrier()
+    ev[0].record(stream)
+    for s_ in range(args.steps):
+        enc.encode_batch(info, code, stream=sp)
+        ev[s_ + 1].record(stream)
+    barrier()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    k_ms = float(np.mean([ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]))
+    launches = enc._get().launches() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    # e2e through host buffers
+    h_info = torch.empty((e2e_frames, K // 8), dtype=torch.uint8).pin_memory()
+    h_info.copy_(info[:e2e_frames])
+    h_code = torch.empty((e2e_frames, N // 8), dtype=torch.uint8).pin_memory()
+    for _ in range(2):
+        enc.encode_batch(h_info, h_code, stream=sp)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        enc.encode_batch(h_info, h_code, stream=sp)
+    e1.record(stream)
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    e2e_match = bool((h_code == code[:e2e_frames].cpu()).all().item())
+    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(t[0].item()), float(t[1].item())
+    if rank == 0:
+        hbm_peak, sm_max, which = peaks()
+        value = world * frames * args.steps * K / (total_ms * 1e-3) / 1e9
+        e2e_val = world * e2e_frames * args.steps * K / (e2e_ms * 1e-3) / 1e9
+        bpf = K // 8 + N // 8
+        hbm = frames * bpf / (k_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": hbm, "peak": hbm_peak, "unit": "GB/s", "frac": hbm / hbm_peak, "traffic": None,
+                "peak_source": which + " hbm copy", "algorithmic_bytes": bpf * frames, "kernel_ms": k_ms,
+                "frames_per_launch": frames}
+        cpu = None
+        try:
+            from polar_testlib import have_ref
+            if have_ref():
+                th = ref_threads()
+                sample = np.ascontiguousarray(h_info[:1 << 18].numpy())
+                v, nfr, tt = time_reference_encoder(wl, frozen, sample, 8.0, th)
+                cpu = {"value": v, "unit": "Gbit/s", "cores": th, "kind": "reference",
+                       "sample": "%d frames encoded %d times in %.1f s by %d threads (one ButterflyFipPacked each)" % (len(sample), nfr // len(sample), tt, th)}
+        except Exception as e:
+            cpu = {"value": None, "unit": "Gbit/s", "cores": 0, "kind": "reference", "sample": "failed: %r" % (e,)}
+        line = {"metric": wl["label"], "value": value, "unit": "Gbit/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u8", "data": "synthetic",
+                "config": {"workload": wl["label"], "frames_per_step_per_gpu": frames, "e2e_frames_per_step_per_gpu": e2e_frames,
+                           "crc_bits": crc, "cache": "inputs larger than L2 (%d MiB in+out per step)" % (frames * bpf >> 20),
+                           "parallelism": "frames sharded x%d" % world},
+                "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": e2e_frames * (K // 8),
+                        "d2h_bytes_per_step": e2e_frames * (N // 8), "matches_device_run": e2e_match},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def run_ours(args, wl):
@@ -328,6 +463,8 @@ def main():
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference_arm(args, wl)
+    elif wl.get("encoder"):
+        run_encoder(args, wl)
     else:
         run_ours(args, wl)
 
