@@ -344,27 +344,37 @@ POLAR_DEV void scl_weak_search(const Words& src, int s, int lgG, int g, int (&va
 // so ties go to the lower current position).  Lane q < P of the group contributes the candidates at list
 // positions q*F .. q*F+F-1, F = 2^lgF <= FMAX.  Out (lane j < nOut of the group): metric and original
 // candidate index of list entry j.
-// The keys (metric, 255 - current position) live in the frame's select scratch (position p at word
-// (p % F) * L + p / F: conflict free for the owner lanes); every lane only carries the maximum of its own F
-// keys.  Step i: group maximum -> winner position w; the element at position i moves to w (key rewritten with
+// The keys (metric, 255 - current position) live in the frame's select scratch, indexed by position (a lane's F
+// keys are one or two 16-byte rows); every lane only carries the maximum of its own F keys.  Step i: group maximum -> winner position w; the element at position i moves to w (key rewritten with
 // its new position), position i is final; the two owner lanes refresh their maxima.  The swap history
 // w_0 .. w_i then tells every output lane which original candidate it received.
 template <int L, int FMAX>
 POLAR_DEV void scl_select(const SclCtx& c, const int (&cand)[FMAX], int lgF, int lgP, int nOut, int& outMet, int& outIdx)
 {
     const int gl = c.gl, F = 1 << lgF;
-    uint32_t* ks = c.sel;          // L * 8 key words
+    uint32_t* ks = c.sel;          // L * 8 key words, ks[position]
     uint32_t* hs = c.sel + 8 * L;  // L history words
+    uint32_t* mine = ks + (gl << lgF);
+    constexpr bool V4 = (FMAX >= 4 && L >= 4), V2 = (FMAX == 2 && L >= 2); // the lane's row is 16 / 8 byte aligned
     const bool act = gl < (1 << lgP);
+    uint32_t key[FMAX];
     uint32_t lmax = 0u;
 #pragma unroll
     for (int k = 0; k < FMAX; ++k) {
-        if (k < F) {
-            const int pos = (gl << lgF) + k;
-            const uint32_t key = act ? (((uint32_t)(cand[k] + SCL_METRIC_BIAS) << 8) | (uint32_t)(255 - pos)) : 0u;
-            ks[k * L + gl] = key;
-            lmax = max(lmax, key);
-        }
+        const int pos = (gl << lgF) + k;
+        key[k] = (act && k < F) ? (((uint32_t)(cand[k] + SCL_METRIC_BIAS) << 8) | (uint32_t)(255 - pos)) : 0u;
+        lmax = max(lmax, key[k]);
+    }
+    if (V4) {
+#pragma unroll
+        for (int k = 0; k < FMAX; k += 4)
+            if (k < F) *reinterpret_cast<uint4*>(mine + k) = make_uint4(key[k], key[k + 1], key[k + 2], key[k + 3]);
+    } else if (V2) {
+        *reinterpret_cast<uint2*>(mine) = make_uint2(key[0], key[1]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < FMAX; ++k)
+            if (k < F) mine[k] = key[k];
     }
     __syncwarp();
     outMet = 0;
@@ -373,22 +383,34 @@ POLAR_DEV void scl_select(const SclCtx& c, const int (&cand)[FMAX], int lgF, int
     for (int i = 0; i < nOut; ++i) {
         const uint32_t best = list_max<L>(lmax);
         const int pos = 255 - (int)(best & 255u), wl = pos >> lgF, il = i >> lgF;
-        const int wa = (pos & (F - 1)) * L + wl, ia = (i & (F - 1)) * L + il;
         if (gl == i) {
             outMet = (int)(best >> 8) - SCL_METRIC_BIAS;
             myW = pos;
         }
-        const uint32_t ikey = ks[ia]; // the element now at position i
+        const uint32_t ikey = ks[i]; // the element now at position i
         __syncwarp();
-        if (gl == wl) ks[wa] = (ikey & ~255u) | (uint32_t)(255 - pos); // ... moves to the winner's place
-        if (gl == il) ks[ia] = 0u;                                     // position i is final
+        if (gl == wl) ks[pos] = (ikey & ~255u) | (uint32_t)(255 - pos); // ... moves to the winner's place
+        if (gl == il) ks[i] = 0u;                                       // position i is final
         if (gl == 0) hs[i] = (uint32_t)pos;
         __syncwarp();
         if (gl == wl || gl == il) {
             lmax = 0u;
+            if (V4) {
 #pragma unroll
-            for (int k = 0; k < FMAX; ++k)
-                if (k < F) lmax = max(lmax, ks[k * L + gl]);
+                for (int k = 0; k < FMAX; k += 4) {
+                    if (k < F) {
+                        const uint4 v = *reinterpret_cast<const uint4*>(mine + k);
+                        lmax = max(max(lmax, v.x), max(max(v.y, v.z), v.w));
+                    }
+                }
+            } else if (V2) {
+                const uint2 v = *reinterpret_cast<const uint2*>(mine);
+                lmax = max(v.x, v.y);
+            } else {
+#pragma unroll
+                for (int k = 0; k < FMAX; ++k)
+                    if (k < F) lmax = max(lmax, mine[k]);
+            }
         }
     }
     // which original candidate sits at position gl: follow the swaps backwards (the element found at w_t at step
