@@ -36,7 +36,7 @@ POLAR_DEV uint32_t inword_transform(uint32_t v)
 template <int WPL>
 __global__ void __launch_bounds__(256) encode_kernel(const __grid_constant__ EncodeParams p)
 {
-    __shared__ __align__(16) uint8_t sinfo[8][512];
+    __shared__ __align__(16) uint8_t sinfo[8][512 + 8]; // + slack for the 5-byte window reads of the scatter
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpsPerBlock = blockDim.x >> 5;
     const int W = p.N >= 32 ? p.N >> 5 : 1;          // words per frame
     const int lpf = W < 32 ? W : 32;                  // lanes per frame
@@ -87,11 +87,18 @@ __global__ void __launch_bounds__(256) encode_kernel(const __grid_constant__ Enc
             mask[j] = t.x;
             uint32_t m = t.x, v = 0;
             int k = (int)t.y;
-            while (m) {
+            while (m) { // one run of consecutive info positions at a time (a polar info set has few runs per word)
                 const int b = __ffs(m) - 1;
-                m &= m - 1;
-                v |= (uint32_t)((myInfo[k >> 3] >> (7 - (k & 7))) & 1) << b;
-                ++k;
+                const uint32_t rest = ~(m >> b);
+                const int len = rest ? __ffs(rest) - 1 : 32;
+                // stream bits k .. k+len-1 (MSB first inside the bytes) -> bits b .. b+len-1 of the word
+                const uint8_t* q = myInfo + (k >> 3);
+                const uint32_t hi = ((uint32_t)q[0] << 24) | ((uint32_t)q[1] << 16) | ((uint32_t)q[2] << 8) | q[3];
+                const uint32_t x = __funnelshift_l((uint32_t)q[4] << 24, hi, k & 7); // len + (k & 7) <= 39 bits needed
+                const uint32_t field = __brev(x) & (len == 32 ? 0xFFFFFFFFu : (1u << len) - 1u);
+                v |= field << b;
+                m = len + b >= 32 ? 0u : m & (0xFFFFFFFFu << (b + len));
+                k += len;
             }
             word[j] = live ? v : 0u;
         }
