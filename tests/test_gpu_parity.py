@@ -47,6 +47,8 @@ SCL_CASES = [
     (8, 4, "BB", 4, 0, 128),
     (4096, 2048, "BB", 4, 16, 8),
     (1024, 512, "BE", 1, 16, 32),
+    (4096, 3072, "BB", 32, 32, 4),   # the largest code and list the library accepts
+    (4096, 256, "5G", 32, 8, 4),
 ]
 
 
@@ -110,6 +112,7 @@ SCL_F32_CASES = [
     (1024, 512, "5G", 8, 16, 48), (1024, 512, "BB", 4, 0, 32), (256, 128, "BB", 8, 8, 64), (128, 64, "BB", 2, 8, 64),
     (64, 32, "BB", 16, 0, 64), (512, 384, "BB", 8, 32, 32), (32, 16, "BB", 8, 8, 64), (8, 4, "BB", 4, 0, 64),
     (2048, 1024, "BB", 32, 32, 8), (4096, 2048, "BB", 4, 16, 8), (1024, 512, "BE", 1, 16, 32), (16, 8, "BB", 32, 0, 64),
+    (4096, 3072, "BB", 32, 32, 3),
 ]
 
 
