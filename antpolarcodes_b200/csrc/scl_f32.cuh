@@ -65,8 +65,8 @@ template <int L, bool ISG>
 POLAR_DEV void sclf_op_fg(SclCtx& c, int s, int lgP)
 {
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
-    const FWords src = sclf_llr_block(c, s + 1, scl_slot_of(c, c.llrPtr, s + 1, q));
-    const uint32_t* lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q), s);
+    const FWords src = sclf_llr_block(c, s + 1, scl_slot_of(c, c.llrPtr, s + 1, q, lgG));
+    const uint32_t* lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
     int i = g;
     for (; i + 3 * G < n; i += 4 * G) {
         float a[4], b[4], r[4];
@@ -237,7 +237,7 @@ template <int L>
 POLAR_DEV void sclf_leaf_r0(SclCtx& c, int s, int lgP, bool isRight)
 {
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
-    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
     float pun = 0.0f;
     if (g == 0) pun = sclf_lane_reduce(src, n, [](float x) { return x < 0.0f ? x : 0.0f; });
     pun = __shfl_sync(FULL_MASK, pun, c.fb + ((c.gl << lgG) & (L - 1)));
@@ -254,7 +254,7 @@ POLAR_DEV void sclf_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
 {
     constexpr int lgL = Log2<L>::v;
     const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
-    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
     float z = 0.0f, o = 0.0f;
     if (g == 0) {
         z = sclf_lane_reduce(src, n, [](float x) { return x < 0.0f ? x : 0.0f; });
@@ -283,7 +283,7 @@ POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSp
 {
     constexpr int lgL = Log2<L>::v;
     const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
-    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    const FWords src = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
     float a[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
     int idx[4] = { 0, 0, 0, 0 };
     int par = 0;
@@ -338,7 +338,7 @@ POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSp
     const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
     const uint32_t fm = __shfl_sync(FULL_MASK, fmask, c.fb + qo);
     const uint32_t p01 = __shfl_sync(FULL_MASK, s01, c.fb + qo), p23 = __shfl_sync(FULL_MASK, s23, c.fb + qo);
-    const FWords srcn = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo));
+    const FWords srcn = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo, lgGo));
     uint32_t* out = scl_bits_out(c, qo, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     const uint32_t f[4] = { p01 & 0xFFFFu, p01 >> 16, p23 & 0xFFFFu, p23 >> 16 };

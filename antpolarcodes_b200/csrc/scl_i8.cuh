@@ -70,9 +70,12 @@ POLAR_DEV unsigned long long shfl64(unsigned long long v, int src)
     return ((unsigned long long)hi << 32) | lo;
 }
 // physical slot of `path`'s block at `stage` (path state lives in lane fb + path)
-POLAR_DEV uint32_t scl_slot_of(const SclCtx& c, unsigned long long vec, int stage, int path)
+// lgG = log2 of the lanes per path: with a full list (lgG == 0, warp uniform) the path is the lane's own
+POLAR_DEV uint32_t scl_slot_of(const SclCtx& c, unsigned long long vec, int stage, int path, int lgG)
 {
-    return __shfl_sync(FULL_MASK, (uint32_t)(vec >> (5 * stage)) & 31u, c.fb + path);
+    const uint32_t mine = (uint32_t)(vec >> (5 * stage)) & 31u;
+    if (lgG == 0) return mine;
+    return __shfl_sync(FULL_MASK, mine, c.fb + path);
 }
 // word offset of a spilled stage inside the warp's scratch ([word][lane] layout, 32 columns)
 POLAR_DEV int scl_spill_woff(const SclCtx& c, int stage) { return ((1 << (stage - 2)) - (1 << (c.smemStages - 2))) << 5; }
@@ -204,9 +207,9 @@ template <int L, bool ISG>
 POLAR_DEV void scl_op_fg(SclCtx& c, int s, int lgP)
 {
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const uint32_t slot = scl_slot_of(c, c.llrPtr, s + 1, q);
+    const uint32_t slot = scl_slot_of(c, c.llrPtr, s + 1, q, lgG);
     const uint32_t* lb = nullptr;
-    if (ISG) lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q), s);
+    if (ISG) lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
     if (s + 1 < c.smemStages) { // shared -> shared: the bulk of the steps
         const uint32_t* src = c.llr + slot * c.slotW + llr_woff(s + 1);
         uint32_t* dst = c.llr + q * c.slotW + llr_woff(s);
@@ -235,7 +238,7 @@ POLAR_DEV void scl_op_combine(SclCtx& c, int s, int lgP, bool isRight)
 {
     if (s + 1 == c.lgN) return; // the root is assembled by the epilogue, straight from its two halves
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const uint32_t* left = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q), s);
+    const uint32_t* left = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
     const uint32_t* right = scl_bits_b(c, q, s);
     uint32_t* out = scl_bits_out(c, q, s + 1, isRight);
     if (s >= 5) {
@@ -458,7 +461,7 @@ template <int L>
 POLAR_DEV void scl_leaf_r0(SclCtx& c, int s, int lgP, bool isRight)
 {
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
     int acc = 0;
     if (s >= 2) {
         const int words = 1 << (s - 2);
@@ -467,7 +470,7 @@ POLAR_DEV void scl_leaf_r0(SclCtx& c, int s, int lgP, bool isRight)
         acc = sum_neg4(src(0) & (s == 1 ? 0xFFFFu : 0xFFu), 0);
     }
     acc = group_add(acc, lgG);
-    const int pun = __shfl_sync(FULL_MASK, acc, c.fb + ((c.gl << lgG) & (L - 1)));
+    const int pun = lgG ? __shfl_sync(FULL_MASK, acc, c.fb + ((c.gl << lgG) & (L - 1))) : acc;
     if (c.gl < (1 << lgP)) c.metric += pun;
     uint32_t* out = scl_bits_out(c, q, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
@@ -482,7 +485,7 @@ POLAR_DEV void scl_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
 {
     constexpr int lgL = Log2<L>::v;
     const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
     int neg = 0, pos = 0;
     if (s >= 2) {
         const int words = 1 << (s - 2);
@@ -498,16 +501,18 @@ POLAR_DEV void scl_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
     }
     neg = group_add(neg, lgG);
     pos = group_add(pos, lgG);
-    const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
-    neg = __shfl_sync(FULL_MASK, neg, srcLane);
-    pos = __shfl_sync(FULL_MASK, pos, srcLane);
+    if (lgG) { // lane q (the path's state) fetches what the path's lane group computed
+        const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
+        neg = __shfl_sync(FULL_MASK, neg, srcLane);
+        pos = __shfl_sync(FULL_MASK, pos, srcLane);
+    }
     const int cand[2] = { c.metric + neg, c.metric - pos };
     const int lgPo = min(lgL, lgP + 1);
     int outMet, outIdx;
     scl_select<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
     scl_adopt(c, outMet, (outIdx >> 1) & (L - 1));
     const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
-    const int kq = __shfl_sync(FULL_MASK, outIdx & 1, c.fb + qo);
+    const int kq = lgGo ? __shfl_sync(FULL_MASK, outIdx & 1, c.fb + qo) : (outIdx & 1);
     uint32_t* out = scl_bits_out(c, qo, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     const uint32_t full = s >= 5 ? 0xFFFFFFFFu : (1u << (1 << s)) - 1u;
@@ -521,9 +526,13 @@ POLAR_DEV void scl_write_flipped(SclCtx& c, int s, int lgPo, bool isRight, uint3
                                  uint32_t pk23)
 {
     const int lgGo = Log2<L>::v - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
-    const uint32_t fm = __shfl_sync(FULL_MASK, flipMask, c.fb + qo);
-    const uint32_t p01 = __shfl_sync(FULL_MASK, pk01, c.fb + qo), p23 = __shfl_sync(FULL_MASK, pk23, c.fb + qo);
-    const Words srcn = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo)); // through the adopted vector
+    uint32_t fm = flipMask, p01 = pk01, p23 = pk23;
+    if (lgGo) { // the path's lane group fetches the decision from lane qo
+        fm = __shfl_sync(FULL_MASK, fm, c.fb + qo);
+        p01 = __shfl_sync(FULL_MASK, p01, c.fb + qo);
+        p23 = __shfl_sync(FULL_MASK, p23, c.fb + qo);
+    }
+    const Words srcn = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo, lgGo)); // through the adopted vector
     uint32_t* out = scl_bits_out(c, qo, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     const uint32_t f[4] = { p01 & 0xFFFFu, p01 >> 16, p23 & 0xFFFFu, p23 >> 16 };
@@ -544,7 +553,7 @@ POLAR_DEV void scl_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSpc
 {
     constexpr int lgL = Log2<L>::v;
     const int lgG = lgL - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q));
+    const Words src = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, q, lgG));
     uint32_t px = 0;
     if (isSpc) {
         const int words = 1 << (s - 2); // an SPC leaf has at least 4 elements
@@ -554,12 +563,18 @@ POLAR_DEV void scl_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSpc
     int par = __popc(px & 0x80808080u) & 1;
     int val[4], idx[4];
     scl_weak_search<4>(src, s, lgG, g, val, idx); // a rate-1 leaf only uses the two weakest
-    const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
-    const int a0 = __shfl_sync(FULL_MASK, val[0], srcLane), a1 = __shfl_sync(FULL_MASK, val[1], srcLane);
-    const int a2 = __shfl_sync(FULL_MASK, val[2], srcLane), a3 = __shfl_sync(FULL_MASK, val[3], srcLane);
-    const uint32_t pk01 = __shfl_sync(FULL_MASK, (uint32_t)idx[0] | ((uint32_t)idx[1] << 16), srcLane);
-    const uint32_t pk23 = __shfl_sync(FULL_MASK, (uint32_t)idx[2] | ((uint32_t)idx[3] << 16), srcLane);
-    par = __shfl_sync(FULL_MASK, par, srcLane);
+    int a0 = val[0], a1 = val[1], a2 = val[2], a3 = val[3];
+    uint32_t pk01 = (uint32_t)idx[0] | ((uint32_t)idx[1] << 16), pk23 = (uint32_t)idx[2] | ((uint32_t)idx[3] << 16);
+    if (lgG) { // lane q (the path's state) fetches what the path's lane group computed
+        const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
+        a0 = __shfl_sync(FULL_MASK, a0, srcLane);
+        a1 = __shfl_sync(FULL_MASK, a1, srcLane);
+        a2 = __shfl_sync(FULL_MASK, a2, srcLane);
+        a3 = __shfl_sync(FULL_MASK, a3, srcLane);
+        pk01 = __shfl_sync(FULL_MASK, pk01, srcLane);
+        pk23 = __shfl_sync(FULL_MASK, pk23, srcLane);
+        par = __shfl_sync(FULL_MASK, par, srcLane);
+    }
     int m = c.metric, w = 0;
     int cand[8];
     if (isSpc) {
@@ -672,6 +687,7 @@ __global__ void __launch_bounds__(512) scl_i8_kernel(const __grid_constant__ Dec
         const long long quad = live ? qb * warpsPerBlock + warp : nQuads - 1;
         const long long myFrame = min(quad * FPW + fi, p.nFrames - 1); // tail lanes redo the last frame
         c.chan = reinterpret_cast<const uint32_t*>(static_cast<const int8_t*>(p.llr) + myFrame * p.N);
+        }
         c.metric = 0;
         c.llrPtr = 0ull;
         c.lbPtr = 0ull;

@@ -48,7 +48,7 @@ SCL_CASES = [
     (4096, 2048, "BB", 4, 16, 8),
     (1024, 512, "BE", 1, 16, 32),
     (4096, 3072, "BB", 32, 32, 4),   # the largest code and list the library accepts
-    (4096, 256, "5G", 32, 8, 4),
+    (4096, 256, "BE", 32, 8, 4),
 ]
 
 
