@@ -687,7 +687,6 @@ __global__ void __launch_bounds__(512) scl_i8_kernel(const __grid_constant__ Dec
         const long long quad = live ? qb * warpsPerBlock + warp : nQuads - 1;
         const long long myFrame = min(quad * FPW + fi, p.nFrames - 1); // tail lanes redo the last frame
         c.chan = reinterpret_cast<const uint32_t*>(static_cast<const int8_t*>(p.llr) + myFrame * p.N);
-        }
         c.metric = 0;
         c.llrPtr = 0ull;
         c.lbPtr = 0ull;
