@@ -143,7 +143,7 @@ int setup_decoder_geometry(polar_code* c)
         // what sets the resident warp count; region A of the bit slots holds stages 0..lgN-1 (the root is
         // assembled by the epilogue), region B is a ping-pong pair.
         // (fp32 lists: one float per word, stage s at word 2^s - 1 of the slot)
-        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 10 ? (sclF32 ? 4 : 3) : c->lgN >= 9 ? (sclF32 ? 3 : 2) : (c->lgN >= 7 ? 1 : 0));
+        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 10 ? (sclF32 ? 5 : 3) : c->lgN >= 9 ? (sclF32 ? 3 : 2) : (c->lgN >= 7 ? 1 : 0));
         nSpill = std::max(0, std::min(nSpill, c->lgN - 5));
         if (sclF32) // keep a warp's footprint within reach of a few resident warps per SM
             while (nSpill < c->lgN - 5 && (size_t)32 * f32_woff(c->lgN - nSpill) * 4 > 96 * 1024) ++nSpill;
@@ -161,7 +161,7 @@ int setup_decoder_geometry(polar_code* c)
         int bslot = bitA + stageWords(topEven) + stageWords(std::max(topOdd, 1));
         while (bslot % L != 1 % L) ++bslot;
         g.bitSlotW = bslot;
-        int frame = L * g.slotW + L * g.bitSlotW + 9 * L; // + select scratch (candidate keys, swap history)
+        int frame = L * g.slotW + L * g.bitSlotW + (sclF32 ? 17 : 9) * L; // + select scratch (candidate keys, swap history)
         while (frame % 32 != L % 32) ++frame;
         g.frameW = frame;
         g.scratchW = 2 * ((c->K + 31) / 32) + nW + 4;

@@ -173,51 +173,69 @@ POLAR_DEV void sclf_weak_search(const FWords& src, int n, float (&val)[4], int (
 }
 
 // simplePartialSortDescending on float metrics (see scl_select in scl_i8.cuh): 64-bit keys
-// (ordered metric << 8 | 255 - position); unused registers hold key 0, below every real key.
+// (ordered metric << 8 | 255 - current position) in the frame's select scratch (low words, high words, swap
+// history), every lane carries the maximum of its own F keys; key 0 marks a final / unused position.
 template <int L, int FMAX>
 POLAR_DEV void sclf_select(const SclCtx& c, const float (&cand)[FMAX], int lgF, int lgP, int nOut, float& outMet, int& outIdx)
 {
     const int gl = c.gl, F = 1 << lgF;
-    unsigned long long key[FMAX];
-    int orig[FMAX];
+    uint32_t* klo = c.sel;
+    uint32_t* khi = c.sel + 8 * L;
+    uint32_t* hs = c.sel + 16 * L;
+    const int row = gl << lgF;
+    const bool act = gl < (1 << lgP);
+    unsigned long long lmax = 0ull;
 #pragma unroll
     for (int k = 0; k < FMAX; ++k) {
-        const int pos = (gl << lgF) + k;
-        const uint32_t o = f32_ordered(__fadd_rn(cand[k], 0.0f)); // -0.0 -> +0.0: equal floats, equal keys
-        key[k] = (gl < (1 << lgP) && k < F) ? (((unsigned long long)o << 8) | (unsigned)(255 - pos)) : 0ull;
-        orig[k] = pos;
+        if (k < F) {
+            const uint32_t o = f32_ordered(__fadd_rn(cand[k], 0.0f)); // -0.0 -> +0.0: equal floats, equal keys
+            const unsigned long long key = act ? (((unsigned long long)o << 8) | (unsigned)(255 - (row + k))) : 0ull;
+            klo[row + k] = (uint32_t)key;
+            khi[row + k] = (uint32_t)(key >> 32);
+            lmax = key > lmax ? key : lmax;
+        }
     }
+    __syncwarp();
     outMet = 0.0f;
-    outIdx = 0;
+    int myW = 0;
 #pragma unroll 1
     for (int i = 0; i < nOut; ++i) {
-        unsigned long long m = key[0];
-#pragma unroll
-        for (int k = 1; k < FMAX; ++k) m = key[k] > m ? key[k] : m;
-        const unsigned long long best = list_max64<L>(m);
-        const int pos = 255 - (int)(best & 255u), wl = pos >> lgF, wk = pos & (F - 1);
-        const int il = i >> lgF, ik = i & (F - 1);
-        int wo = orig[0], io = orig[0];
-        unsigned long long ikl = key[0];
-#pragma unroll
-        for (int k = 1; k < FMAX; ++k) {
-            if (k == wk) wo = orig[k];
-            if (k == ik) { io = orig[k]; ikl = key[k]; }
-        }
-        const int widx = __shfl_sync(FULL_MASK, wo, c.fb + wl);
-        const unsigned long long ikey = shfl64(ikl, c.fb + il); // the element now at position i
-        const int iidx = __shfl_sync(FULL_MASK, io, c.fb + il);
-        const unsigned long long moved = (ikey & ~255ull) | (unsigned)(255 - pos);
-#pragma unroll
-        for (int k = 0; k < FMAX; ++k) {
-            if (gl == wl && k == wk) { key[k] = moved; orig[k] = iidx; }
-            if (gl == il && k == ik) key[k] = 0ull;
-        }
+        const unsigned long long best = list_max64<L>(lmax);
+        const int pos = 255 - (int)(best & 255u), wl = pos >> lgF, il = i >> lgF;
         if (gl == i) {
             outMet = f32_unordered((uint32_t)(best >> 8));
-            outIdx = widx;
+            myW = pos;
+        }
+        const uint32_t ilo = klo[i], ihi = khi[i]; // the element now at position i
+        __syncwarp();
+        if (gl == wl) { // ... moves to the winner's place
+            klo[pos] = (ilo & ~255u) | (uint32_t)(255 - pos);
+            khi[pos] = ihi;
+        }
+        if (gl == il) { // position i is final
+            klo[i] = 0u;
+            khi[i] = 0u;
+        }
+        if (gl == 0) hs[i] = (uint32_t)pos;
+        __syncwarp();
+        if (gl == wl || gl == il) {
+            lmax = 0ull;
+#pragma unroll
+            for (int k = 0; k < FMAX; ++k) {
+                if (k < F) {
+                    const unsigned long long key = ((unsigned long long)khi[row + k] << 32) | klo[row + k];
+                    lmax = key > lmax ? key : lmax;
+                }
+            }
         }
     }
+    int p = myW; // follow the swaps backwards to the original candidate (see scl_select)
+    for (int t = nOut - 2; t >= 0; --t) {
+        const int wt = (int)hs[t];
+        if (t < gl && wt == p) p = t;
+    }
+    outIdx = p;
+    __syncwarp();
 }
 
 POLAR_DEV float sclf_metric(const SclCtx& c) { return __int_as_float(c.metric); }
