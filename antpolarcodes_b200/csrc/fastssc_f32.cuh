@@ -103,13 +103,12 @@ template <class Src>
 POLAR_DEV void scf_f_range(const Src& src, float* dst, int ib, int ie)
 {
     int i = ib;
-    for (; i + 3 < ie; i += 4) {
-        const float a0 = src.a(i), a1 = src.a(i + 1), a2 = src.a(i + 2), a3 = src.a(i + 3);
-        const float b0 = src.b(i), b1 = src.b(i + 1), b2 = src.b(i + 2), b3 = src.b(i + 3);
-        dst[i << 5] = f_f32(a0, b0);
-        dst[(i + 1) << 5] = f_f32(a1, b1);
-        dst[(i + 2) << 5] = f_f32(a2, b2);
-        dst[(i + 3) << 5] = f_f32(a3, b3);
+    for (; i + 7 < ie; i += 8) { // 16 loads in flight: the parent block may sit in the L2 scratch
+        float a[8], b[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) { a[t] = src.a(i + t); b[t] = src.b(i + t); }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) dst[(i + t) << 5] = f_f32(a[t], b[t]);
     }
     for (; i < ie; ++i) dst[i << 5] = f_f32(src.a(i), src.b(i));
 }
@@ -117,13 +116,12 @@ template <class Src>
 POLAR_DEV void scf_add_range(const Src& src, float* dst, int ib, int ie) // G_function_0R (avx_float.h:164-173)
 {
     int i = ib;
-    for (; i + 3 < ie; i += 4) {
-        const float a0 = src.a(i), a1 = src.a(i + 1), a2 = src.a(i + 2), a3 = src.a(i + 3);
-        const float b0 = src.b(i), b1 = src.b(i + 1), b2 = src.b(i + 2), b3 = src.b(i + 3);
-        dst[i << 5] = __fadd_rn(a0, b0);
-        dst[(i + 1) << 5] = __fadd_rn(a1, b1);
-        dst[(i + 2) << 5] = __fadd_rn(a2, b2);
-        dst[(i + 3) << 5] = __fadd_rn(a3, b3);
+    for (; i + 7 < ie; i += 8) {
+        float a[8], b[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) { a[t] = src.a(i + t); b[t] = src.b(i + t); }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) dst[(i + t) << 5] = __fadd_rn(a[t], b[t]);
     }
     for (; i < ie; ++i) dst[i << 5] = __fadd_rn(src.a(i), src.b(i));
 }
@@ -134,8 +132,14 @@ POLAR_DEV void scf_g_range(ScfCtx& c, const Src& src, float* dst, int pos, int i
     if (((ie - ib) & 31) == 0 && (pos & 31) == 0) { // whole bit words
         for (; i < ie; i += 32) {
             const uint32_t lw = SCF_ROW(c, c.bitRow + ((pos + i) >> 5));
-#pragma unroll 4
-            for (int t = 0; t < 32; ++t) dst[(i + t) << 5] = g_f32(src.a(i + t), src.b(i + t), (lw >> t) << 31);
+#pragma unroll 1
+            for (int t0 = 0; t0 < 32; t0 += 8) {
+                float a[8], b[8];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) { a[t] = src.a(i + t0 + t); b[t] = src.b(i + t0 + t); }
+#pragma unroll
+                for (int t = 0; t < 8; ++t) dst[(i + t0 + t) << 5] = g_f32(a[t], b[t], (lw >> (t0 + t)) << 31);
+            }
         }
         return;
     }
@@ -152,8 +156,14 @@ POLAR_DEV void scf_g_r1_range(ScfCtx& c, const Src& src, int s, int pos, int ib,
             const int wl = c.bitRow + ((pos + i) >> 5), wr = c.bitRow + ((pos + h + i) >> 5);
             const uint32_t lw = SCF_ROW(c, wl);
             uint32_t rw = 0;
-#pragma unroll 4
-            for (int t = 0; t < 32; ++t) rw |= (fbits(g_f32(src.a(i + t), src.b(i + t), (lw >> t) << 31)) >> 31) << t;
+#pragma unroll 1
+            for (int t0 = 0; t0 < 32; t0 += 8) {
+                float a[8], b[8];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) { a[t] = src.a(i + t0 + t); b[t] = src.b(i + t0 + t); }
+#pragma unroll
+                for (int t = 0; t < 8; ++t) rw |= (fbits(g_f32(a[t], b[t], (lw >> (t0 + t)) << 31)) >> 31) << (t0 + t);
+            }
             SCF_ROW(c, wr) = rw;
             SCF_ROW(c, wl) = lw ^ rw;
         }

@@ -86,13 +86,17 @@ template <class Src>
 POLAR_DEV void sc_f_range(const Src& src, uint32_t* dst, int wb, int we)
 {
     int w = wb;
-    for (; w + 3 < we; w += 4) {
-        const uint32_t a0 = src.a(w), a1 = src.a(w + 1), a2 = src.a(w + 2), a3 = src.a(w + 3);
-        const uint32_t b0 = src.b(w), b1 = src.b(w + 1), b2 = src.b(w + 2), b3 = src.b(w + 3);
+    for (; w + 7 < we; w += 8) { // 16 loads in flight: the parent block may sit in the L2 scratch
+        uint32_t a[8], b[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) dst[(w + t) << 5] = f4(a[t], b[t]);
+    }
+    for (; w + 1 < we; w += 2) {
+        const uint32_t a0 = src.a(w), a1 = src.a(w + 1), b0 = src.b(w), b1 = src.b(w + 1);
         dst[(w) << 5] = f4(a0, b0);
         dst[(w + 1) << 5] = f4(a1, b1);
-        dst[(w + 2) << 5] = f4(a2, b2);
-        dst[(w + 3) << 5] = f4(a3, b3);
     }
     for (; w < we; ++w) dst[(w) << 5] = f4(src.a(w), src.b(w));
 }
@@ -101,13 +105,12 @@ template <class Src>
 POLAR_DEV void sc_adds_range(const Src& src, uint32_t* dst, int wb, int we)
 {
     int w = wb;
-    for (; w + 3 < we; w += 4) {
-        const uint32_t a0 = src.a(w), a1 = src.a(w + 1), a2 = src.a(w + 2), a3 = src.a(w + 3);
-        const uint32_t b0 = src.b(w), b1 = src.b(w + 1), b2 = src.b(w + 2), b3 = src.b(w + 3);
-        dst[(w) << 5] = adds4(a0, b0);
-        dst[(w + 1) << 5] = adds4(a1, b1);
-        dst[(w + 2) << 5] = adds4(a2, b2);
-        dst[(w + 3) << 5] = adds4(a3, b3);
+    for (; w + 7 < we; w += 8) {
+        uint32_t a[8], b[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) dst[(w + t) << 5] = adds4(a[t], b[t]);
     }
     for (; w < we; ++w) dst[(w) << 5] = adds4(src.a(w), src.b(w));
 }
