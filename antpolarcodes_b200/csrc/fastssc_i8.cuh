@@ -61,21 +61,17 @@ struct ScTiles { // a chunk [w0, w0+cw) of both halves in the transpose tiles
 // tile[r*33 + i] = channel word (w0 + i) of frame (frame0 + r), i < cw <= 32
 POLAR_DEV void sc_load_tile(const ScCtx& c, uint32_t* tile, int w0, int cw)
 {
+    // asynchronous 4-byte copies straight into the padded tile: all 32 rows of the lane's column in flight at
+    // once; the caller waits (cp_async_wait_all) before the __syncwarp that publishes the tile
     if (c.lane < cw) {
-        const uint32_t* src = c.chan + c.frame0 * c.nw + w0 + c.lane;
-        if (c.frame0 + 31 <= c.lastFrame) { // 16 row loads in flight before the first store
-#pragma unroll 1
-            for (int r0 = 0; r0 < 32; r0 += 16) {
-                uint32_t v[16];
-#pragma unroll
-                for (int r = 0; r < 16; ++r) v[r] = __ldg(src + (long long)(r0 + r) * c.nw);
-#pragma unroll
-                for (int r = 0; r < 16; ++r) tile[(r0 + r) * 33 + c.lane] = v[r];
-            }
+        if (c.frame0 + 31 <= c.lastFrame) {
+            const uint32_t* src = c.chan + c.frame0 * c.nw + w0 + c.lane;
+#pragma unroll 8
+            for (int r = 0; r < 32; ++r) cp_async4(tile + r * 33 + c.lane, src + (long long)r * c.nw);
         } else {
             for (int r = 0; r < 32; ++r) {
                 const long long f = min(c.frame0 + r, c.lastFrame);
-                tile[r * 33 + c.lane] = __ldg(c.chan + f * c.nw + w0 + c.lane);
+                cp_async4(tile + r * 33 + c.lane, c.chan + f * c.nw + w0 + c.lane);
             }
         }
     }
@@ -318,6 +314,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
             for (int w0 = 0; w0 < c.nw; w0 += 32) {
                 const int n = min(32, c.nw - w0);
                 sc_load_tile(c, tileA, w0, n);
+                cp_async_wait_all();
                 __syncwarp();
                 for (int i = 0; i < n; ++i) SC_ROW(c, c.chanRow + w0 + i) = myA[i];
                 __syncwarp();
@@ -360,6 +357,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
                     for (int w0 = 0; w0 < halfW; w0 += cw) {
                         sc_load_tile(c, tileA, w0, cw);
                         sc_load_tile(c, tileB, halfW + w0, cw);
+                        cp_async_wait_all();
                         __syncwarp();
                         const ScTiles src{ myA, myB, w0 };
                         if (code == OP_F) sc_f_range(src, dst, w0, w0 + cw);

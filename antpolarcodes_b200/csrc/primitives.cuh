@@ -101,6 +101,14 @@ POLAR_DEV int abs127_byte(uint32_t w, int k)
     return abs(v);
 }
 
+// 4-byte asynchronous global -> shared copy (LDGSTS): no register staging, any number in flight
+POLAR_DEV void cp_async4(uint32_t* smemDst, const uint32_t* globalSrc)
+{
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(globalSrc) : "memory");
+}
+POLAR_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 POLAR_DEV int sat8i(int v) { return min(max(v, -128), 127); }
 
 } // namespace polar
