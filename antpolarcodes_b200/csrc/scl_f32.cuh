@@ -68,6 +68,20 @@ POLAR_DEV void sclf_op_fg(SclCtx& c, int s, int lgP)
     const FWords src = sclf_llr_block(c, s + 1, scl_slot_of(c, c.llrPtr, s + 1, q, lgG));
     const uint32_t* lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
     int i = g;
+    if (s + 1 >= c.smemStages) { // parent block in the L2 scratch / global memory: 16 loads in flight
+        for (; i + 7 * G < n; i += 8 * G) {
+            float a[8], b[8], r[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) { a[t] = src(i + t * G); b[t] = src(i + t * G + n); }
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                const int it = i + t * G;
+                r[t] = ISG ? g_f32(a[t], b[t], (lb[it >> 5] >> (it & 31)) << 31) : f_f32(a[t], b[t]);
+            }
+#pragma unroll
+            for (int t = 0; t < 8; ++t) sclf_store(c, s, (uint32_t)q, i + t * G, r[t]);
+        }
+    }
     for (; i + 3 * G < n; i += 4 * G) {
         float a[4], b[4], r[4];
 #pragma unroll

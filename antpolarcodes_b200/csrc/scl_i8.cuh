@@ -142,6 +142,18 @@ POLAR_DEV void scl_f_words(const uint32_t* src, int ss, bool chan, uint32_t* dst
         const int words = 1 << (s - 2);
         const uint32_t* srcb = src + words * ss;
         int w = g;
+        if (SG) { // parent block in the L2 scratch / global memory: eight butterflies (16 loads) in flight
+            for (; w + 7 * G < words; w += 8 * G) {
+                uint32_t a[8], b[8];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    a[t] = scl_ld<SG>(src + (w + t * G) * ss, chan);
+                    b[t] = scl_ld<SG>(srcb + (w + t * G) * ss, chan);
+                }
+#pragma unroll
+                for (int t = 0; t < 8; ++t) scl_st<DG>(dst + (w + t * G) * ds, f4(a[t], b[t]));
+            }
+        }
         for (; w + 3 * G < words; w += 4 * G) { // four independent butterflies in flight
             uint32_t a[4], b[4];
 #pragma unroll
@@ -167,6 +179,19 @@ POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_
         const int words = 1 << (s - 2);
         const uint32_t* srcb = src + words * ss;
         int w = g;
+        if (G == 1 && SG) { // parent block in the L2 scratch / global memory: 16 loads in flight
+            for (; w + 7 < words; w += 8) {
+                uint32_t a[8], b[8];
+                const uint32_t lw = lb[w >> 3];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    a[t] = scl_ld<SG>(src + (w + t) * ss, chan);
+                    b[t] = scl_ld<SG>(srcb + (w + t) * ss, chan);
+                }
+#pragma unroll
+                for (int t = 0; t < 8; ++t) scl_st<DG>(dst + (w + t) * ds, g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t))));
+            }
+        }
         if (G == 1) { // a lane owns the path: the four words of a batch share one word of left bits
             for (; w + 3 < words; w += 4) {
                 uint32_t a[4], b[4];
