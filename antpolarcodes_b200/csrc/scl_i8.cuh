@@ -127,7 +127,7 @@ template <bool SG>
 POLAR_DEV uint32_t scl_ld(const uint32_t* p, bool chan)
 {
     if (!SG) return *p;
-    return chan ? __ldg(p) : __ldcg(p);
+    return chan ? __ldcs(p) : __ldcg(p);
 }
 template <bool DG>
 POLAR_DEV void scl_st(uint32_t* p, uint32_t v)
@@ -586,8 +586,15 @@ POLAR_DEV void scl_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSpc
     }
     px = group_xor(px, lgG);
     int par = __popc(px & 0x80808080u) & 1;
-    int val[4], idx[4];
-    scl_weak_search<4>(src, s, lgG, g, val, idx); // a rate-1 leaf only uses the two weakest
+    int val[4] = { 0, 0, 0, 0 }, idx[4] = { 0, 0, 0, 0 };
+    if (isSpc) {
+        scl_weak_search<4>(src, s, lgG, g, val, idx);
+    } else { // a rate-1 leaf only needs the two weakest
+        int v2[2], i2[2];
+        scl_weak_search<2>(src, s, lgG, g, v2, i2);
+        val[0] = v2[0]; val[1] = v2[1];
+        idx[0] = i2[0]; idx[1] = i2[1];
+    }
     int a0 = val[0], a1 = val[1], a2 = val[2], a3 = val[3];
     uint32_t pk01 = (uint32_t)idx[0] | ((uint32_t)idx[1] << 16), pk23 = (uint32_t)idx[2] | ((uint32_t)idx[3] << 16);
     if (lgG) { // lane q (the path's state) fetches what the path's lane group computed
