@@ -9,6 +9,7 @@
 // MSB-first bytes with coalesced 4-byte stores.
 #pragma once
 #include "primitives.cuh"
+#include <algorithm>
 
 namespace polar {
 
@@ -137,9 +138,115 @@ __global__ void __launch_bounds__(256) encode_kernel(const __grid_constant__ Enc
     }
 }
 
+// ---------------------------------------------------------------- one frame per thread (N = 32 W <= 1024, kb % 4 == 0)
+// The whole codeword lives in W registers of the thread: no shuffles, no per-frame synchronisation.  The info
+// bytes of the block's 128 frames are staged (coalesced) as big-endian words in a padded [frame][word] tile, so
+// that a run of info positions is one funnel shift; codewords leave through the same kind of tile.
+template <int W>
+__global__ void __launch_bounds__(128) encode_thread_kernel(const __grid_constant__ EncodeParams p)
+{
+    extern __shared__ __align__(16) uint32_t esm[];
+    const int tid = threadIdx.x, kbw = p.kb >> 2, istride = kbw + 1 + ((kbw & 1) ? 1 : 0); // odd stride: conflict free
+    constexpr int ostride = W + 1;
+    uint32_t* sin = esm;                          // 128 x istride big-endian info words
+    uint32_t* sout = esm + 128 * istride;         // 128 x ostride codeword words
+    const long long nBlocks = (p.nFrames + 127) >> 7;
+    for (long long blk = blockIdx.x; blk < nBlocks; blk += gridDim.x) {
+        const long long f0 = blk << 7;
+        const int nHere = (int)min(128LL, p.nFrames - f0);
+        uint32_t* ginfo = reinterpret_cast<uint32_t*>(p.info + f0 * p.kb);
+        for (int idx = tid; idx < nHere * kbw; idx += 128) {
+            const int f = idx / kbw, i = idx - f * kbw;
+            sin[f * istride + i] = __byte_perm(ginfo[idx], 0u, 0x0123u);
+        }
+        __syncthreads();
+        const uint32_t* mine = sin + tid * istride;
+        if (p.crcBits) { // Detector::generate: the checksum is linear in the info bits (crc_host.h); trailer bits weigh 0
+            uint32_t crc = p.genInit;
+            for (int i = 0; i < kbw; ++i) {
+                const uint32_t w = mine[i];
+#pragma unroll 8
+                for (int b = 0; b < 32; ++b) crc ^= __ldg(p.genTab + 32 * i + b) & (0u - ((w >> (31 - b)) & 1u));
+            }
+            uint32_t last = mine[kbw - 1];
+            if (p.crcBits == 8) last = (last & ~0xFFu) | (crc & 0xFFu);
+            else if (p.crcBits == 16) last = (last & ~0xFFFFu) | (crc & 0xFFFFu);   // big-endian trailer: crc16.cpp:35-43
+            else last = __byte_perm(crc, 0u, 0x0123u);                             // native little-endian u32: crc32.cpp:55-66
+            sin[tid * istride + kbw - 1] = last;
+            if (tid < nHere) ginfo[tid * kbw + kbw - 1] = __byte_perm(last, 0u, 0x0123u);
+        }
+        uint32_t word[W];
+#pragma unroll
+        for (int j = 0; j < W; ++j) {
+            const uint2 t = __ldg(p.wordTab + j);
+            uint32_t m = t.x, v = 0;
+            int k = (int)t.y;
+            while (m) { // uniform: every thread of the grid walks the same runs
+                const int b = __ffs(m) - 1;
+                const uint32_t rest = ~(m >> b);
+                const int len = rest ? __ffs(rest) - 1 : 32;
+                const int wi = k >> 5;
+                const uint32_t x = __funnelshift_l(mine[wi + 1], mine[wi], k & 31); // stream bit k on top (pad word is masked off)
+                const uint32_t field = __brev(x) & (len == 32 ? 0xFFFFFFFFu : (1u << len) - 1u);
+                v |= field << b;
+                m = len + b >= 32 ? 0u : m & (0xFFFFFFFFu << (b + len));
+                k += len;
+            }
+            word[j] = v;
+        }
+        for (int pass = 0; pass < (p.systematic ? 2 : 1); ++pass) {
+#pragma unroll
+            for (int j = 0; j < W; ++j) {
+                if (pass) word[j] &= __ldg(p.wordTab + j).x;
+                word[j] = inword_transform(word[j]);
+            }
+#pragma unroll
+            for (int d = 1; d < W; d <<= 1)
+#pragma unroll
+                for (int j = 0; j < W; ++j)
+                    if (!(j & d)) word[j] ^= word[j + d];
+        }
+#pragma unroll
+        for (int j = 0; j < W; ++j) sout[tid * ostride + j] = __byte_perm(__brev(word[j]), 0u, 0x0123u);
+        __syncthreads();
+        uint32_t* gcode = reinterpret_cast<uint32_t*>(p.code + f0 * p.nb);
+        for (int idx = tid; idx < nHere * W; idx += 128) {
+            const int f = idx / W, j = idx - f * W;
+            gcode[idx] = sout[f * ostride + j];
+        }
+        __syncthreads();
+    }
+}
+
+template <int W>
+inline int launch_encode_thread(const EncodeParams& p, int numSMs, cudaStream_t st)
+{
+    const int kbw = p.kb >> 2, istride = kbw + 1 + ((kbw & 1) ? 1 : 0);
+    const size_t smem = (size_t)128 * (istride + W + 1) * 4;
+    if (smem > 48 * 1024) {
+        if (cudaFuncSetAttribute((const void*)encode_thread_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return -1;
+    }
+    const long long nBlocks = (p.nFrames + 127) >> 7;
+    const int grid = (int)std::min<long long>(nBlocks, (long long)numSMs * 16);
+    encode_thread_kernel<W><<<grid, 128, smem, st>>>(p);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
 inline int launch_encode(const EncodeParams& p, int numSMs, cudaStream_t st)
 {
     const int W = p.N >= 32 ? p.N >> 5 : 1;
+    // one frame per thread whenever the codeword fits the registers and the info block is whole words
+    if (p.N >= 32 && p.N <= 1024 && (p.kb & 3) == 0 && p.kb >= 4) {
+        switch (W) {
+        case 1: return launch_encode_thread<1>(p, numSMs, st);
+        case 2: return launch_encode_thread<2>(p, numSMs, st);
+        case 4: return launch_encode_thread<4>(p, numSMs, st);
+        case 8: return launch_encode_thread<8>(p, numSMs, st);
+        case 16: return launch_encode_thread<16>(p, numSMs, st);
+        case 32: return launch_encode_thread<32>(p, numSMs, st);
+        }
+    }
     const int fpw = W < 32 ? 32 / W : 1;
     const long long groups = (p.nFrames + fpw - 1) / fpw;
     const int warpsPerBlock = 8;
