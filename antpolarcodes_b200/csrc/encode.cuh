@@ -18,6 +18,8 @@ struct EncodeParams {
     uint8_t* code;          // nFrames x nb
     const uint2* wordTab;   // per code word: x = mask of info positions, y = number of info bits before it
     const uint32_t* genTab; // per info bit: CRC contribution
+    const uint32_t* runTab; // [0..W]: first run of each code word; then the runs: b | len << 5 | first info bit << 11
+    int runBase;            // offset of the run entries inside runTab
     uint32_t genInit;
     long long nFrames;
     int N, lgN, K, kb, nb, crcBits, systematic;
@@ -150,13 +152,14 @@ __global__ void __launch_bounds__(128) encode_thread_kernel(const __grid_constan
     constexpr int ostride = W + 1;
     uint32_t* sin = esm;                          // 128 x istride big-endian info words
     uint32_t* sout = esm + 128 * istride;         // 128 x ostride codeword words
+    const uint32_t kbwRecip = 0xFFFFFFFFu / (uint32_t)kbw + 1u; // ceil(2^32 / kbw)
     const long long nBlocks = (p.nFrames + 127) >> 7;
     for (long long blk = blockIdx.x; blk < nBlocks; blk += gridDim.x) {
         const long long f0 = blk << 7;
         const int nHere = (int)min(128LL, p.nFrames - f0);
         uint32_t* ginfo = reinterpret_cast<uint32_t*>(p.info + f0 * p.kb);
         for (int idx = tid; idx < nHere * kbw; idx += 128) {
-            const int f = idx / kbw, i = idx - f * kbw;
+            const int f = kbw == 1 ? idx : (int)__umulhi((uint32_t)idx, kbwRecip), i = idx - f * kbw; // idx < 2^13: exact
             sin[f * istride + i] = __byte_perm(ginfo[idx], 0u, 0x0123u);
         }
         __syncthreads();
@@ -178,19 +181,14 @@ __global__ void __launch_bounds__(128) encode_thread_kernel(const __grid_constan
         uint32_t word[W];
 #pragma unroll
         for (int j = 0; j < W; ++j) {
-            const uint2 t = __ldg(p.wordTab + j);
-            uint32_t m = t.x, v = 0;
-            int k = (int)t.y;
-            while (m) { // uniform: every thread of the grid walks the same runs
-                const int b = __ffs(m) - 1;
-                const uint32_t rest = ~(m >> b);
-                const int len = rest ? __ffs(rest) - 1 : 32;
-                const int wi = k >> 5;
+            uint32_t v = 0;
+            const int r1 = (int)__ldg(p.runTab + j + 1);
+            for (int r = (int)__ldg(p.runTab + j); r < r1; ++r) { // uniform: every thread of the grid walks the same runs
+                const uint32_t e = __ldg(p.runTab + p.runBase + r);
+                const int b = e & 31u, len = (e >> 5) & 63u, k = e >> 11, wi = k >> 5;
                 const uint32_t x = __funnelshift_l(mine[wi + 1], mine[wi], k & 31); // stream bit k on top (pad word is masked off)
-                const uint32_t field = __brev(x) & (len == 32 ? 0xFFFFFFFFu : (1u << len) - 1u);
+                const uint32_t field = __brev(x) & (0xFFFFFFFFu >> (32 - len));
                 v |= field << b;
-                m = len + b >= 32 ? 0u : m & (0xFFFFFFFFu << (b + len));
-                k += len;
             }
             word[j] = v;
         }

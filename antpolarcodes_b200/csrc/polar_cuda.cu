@@ -387,6 +387,32 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
                 break;
             }
         }
+        if (kind == POLAR_KIND_ENC) {
+            // encoder: per code word the runs of consecutive information positions (b | len << 5 | first info bit << 11)
+            // behind a table of run offsets per word
+            std::vector<uint32_t> tab(nWords + 1, 0u), runs;
+            for (int w = 0; w < nWords; ++w) {
+                tab[w] = (uint32_t)runs.size();
+                uint32_t m = wordTab[w].x;
+                int k = (int)wordTab[w].y;
+                while (m) {
+                    const int b = __builtin_ctz(m);
+                    const uint32_t rest = ~(m >> b);
+                    const int len = rest ? __builtin_ctz(rest) : 32;
+                    runs.push_back((uint32_t)b | ((uint32_t)len << 5) | ((uint32_t)k << 11));
+                    m = len + b >= 32 ? 0u : m & (0xFFFFFFFFu << (b + len));
+                    k += len;
+                }
+            }
+            tab[nWords] = (uint32_t)runs.size();
+            tab.insert(tab.end(), runs.begin(), runs.end());
+            c->nRuns = nWords + 1; // offset of the run entries inside the table
+            if ((e = cudaMalloc(&c->dRuns, tab.size() * sizeof(uint32_t))) != cudaSuccess ||
+                (e = cudaMemcpy(c->dRuns, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
+                rc = fail(POLAR_E_CUDA, std::string("run table upload: ") + cudaGetErrorString(e));
+                break;
+            }
+        }
         if (kind != POLAR_KIND_ENC) {
             rc = setup_decoder_geometry(c);
         } else {
@@ -519,6 +545,7 @@ int polar_cuda_encode_batch(polar_code_t c, uint8_t* info, int mem, size_t nFram
     p.N = c->N; p.lgN = c->lgN; p.K = c->K; p.kb = c->kb; p.nb = std::max(1, c->N / 8);
     p.crcBits = c->crcBits; p.systematic = c->systematic;
     p.wordTab = c->dWordTab; p.genTab = c->dGenTab; p.genInit = c->genInit;
+    p.runTab = c->dRuns; p.runBase = c->nRuns;
     p.nFrames = (long long)nFrames;
     if (mem == POLAR_MEM_HOST) {
         int rc = ensure_staging(c, nFrames, 0);

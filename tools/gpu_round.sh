@@ -22,7 +22,7 @@ for V in ${VARIANTS:-}; do
 done
 if [ $RC -eq 0 ] && [ "${NCU:-1}" = "1" ]; then
   for WL in ${NCU_WLS:-scl8 fastssc}; do
-    if [ $WL = scl8 ]; then KRN=scl_i8_kernel; FR=131072; elif [ $WL = scl8_f32 ]; then KRN=scl_f32_kernel; FR=65536; elif [ $WL = encode ]; then KRN=encode_kernel; FR=1048576; elif [ $WL = fastssc_f32 ]; then KRN=fastssc_f32_kernel; FR=262144; else KRN=fastssc_i8_kernel; FR=262144; fi
+    if [ $WL = scl8 ]; then KRN=scl_i8_kernel; FR=131072; elif [ $WL = scl8_f32 ]; then KRN=scl_f32_kernel; FR=65536; elif [ $WL = encode ]; then KRN=encode_thread_kernel; FR=4194304; elif [ $WL = fastssc_f32 ]; then KRN=fastssc_f32_kernel; FR=262144; else KRN=fastssc_i8_kernel; FR=262144; fi
     CMD="python bench.py --workload $WL --steps 2 --warmup 1 --frames $FR --e2e-frames 8192"
     $CMD > $OUT/${TAG}_ncu_plain_$WL.log 2>&1 &&
     ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches_$WL.csv $CMD > $OUT/${TAG}_ncu_list_$WL.log 2>&1
