@@ -274,7 +274,14 @@ def run_encoder(args, wl):
         e2e_val = world * e2e_frames * args.steps * K / (e2e_ms * 1e-3) / 1e9
         bpf = K // 8 + N // 8
         hbm = frames * bpf / (k_ms * 1e-3) / 1e9
-        roof = {"bound": "hbm", "achieved": hbm, "peak": hbm_peak, "unit": "GB/s", "frac": hbm / hbm_peak, "traffic": None,
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+            if tj:
+                traffic = tj["dram_bytes"] / tj["frames"] * frames
+        except Exception:
+            pass
+        roof = {"bound": "hbm", "achieved": hbm, "peak": hbm_peak, "unit": "GB/s", "frac": hbm / hbm_peak, "traffic": traffic,
                 "peak_source": which + " hbm copy", "algorithmic_bytes": bpf * frames, "kernel_ms": k_ms,
                 "frames_per_launch": frames}
         cpu = None
