@@ -123,14 +123,14 @@ POLAR_DEV void sc_g_range(ScCtx& c, const Src& src, uint32_t* dst, int pos, int 
 #pragma unroll
             for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
 #pragma unroll
-            for (int t = 0; t < 8; ++t) dst[(w + t) << 5] = g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t)));
+            for (int t = 0; t < 8; ++t) dst[(w + t) << 5] = g4(a[t], b[t], nibble_to_msb(lw >> (4 * t)));
         }
         return;
     }
     for (; w < we; ++w) {
         const int bp = pos + 4 * w;
         const uint32_t nib = SC_ROW(c, c.bitRow + (bp >> 5)) >> (bp & 31);
-        dst[(w) << 5] = g4(src.a(w), src.b(w), nibble_to_bytemask(nib));
+        dst[(w) << 5] = g4(src.a(w), src.b(w), nibble_to_msb(nib));
     }
 }
 
@@ -148,7 +148,7 @@ POLAR_DEV void sc_g_r1_range(ScCtx& c, const Src& src, int s, int pos, int wb, i
         for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
         uint32_t rw = 0;
 #pragma unroll
-        for (int t = 0; t < 8; ++t) rw |= sign_nibble(g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t)))) << (4 * t);
+        for (int t = 0; t < 8; ++t) rw |= sign_nibble(g4(a[t], b[t], nibble_to_msb(lw >> (4 * t)))) << (4 * t);
         SC_ROW(c, c.bitRow + (pos >> 5) + hw + j) = rw;
         SC_ROW(c, c.bitRow + (pos >> 5) + j) = lw ^ rw;
     }
@@ -165,10 +165,10 @@ POLAR_DEV void sc_g_r1_short(ScCtx& c, const Src& src, int s, int pos)
     if (s >= 2) {
         const int words = 1 << (s - 2); // <= 4
         for (int w = 0; w < words; ++w)
-            rbits |= sign_nibble(g4(src.a(w), src.b(w), nibble_to_bytemask(lbits >> (4 * w)))) << (4 * w);
+            rbits |= sign_nibble(g4(src.a(w), src.b(w), nibble_to_msb(lbits >> (4 * w)))) << (4 * w);
     } else { // h == 2: both halves in one word
         const uint32_t x = src.a(0);
-        rbits = sign_nibble(g4(x, x >> 16, nibble_to_bytemask(lbits & 3u))) & 3u;
+        rbits = sign_nibble(g4(x, x >> 16, nibble_to_msb(lbits & 3u))) & 3u;
     }
     const uint32_t both = (lbits ^ rbits) | (rbits << h);
     const uint32_t clr = (mask | (mask << h)) << sh;
@@ -341,7 +341,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
                     else if (code == OP_G_0R) dst[0] = adds4(x, x >> 16);
                     else if (code == OP_G) {
                         const uint32_t nib = (SC_ROW(c, c.bitRow + (pos >> 5)) >> (pos & 31)) & 3u;
-                        dst[0] = g4(x, x >> 16, nibble_to_bytemask(nib));
+                        dst[0] = g4(x, x >> 16, nibble_to_msb(nib));
                     } else sc_g_r1_short(c, src, s, pos);
                     break;
                 }

@@ -650,7 +650,7 @@ __global__ void test_fg_kernel(const uint32_t* a, const uint32_t* b, const uint3
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= words) return;
     f[i] = f4(a[i], b[i]);
-    g[i] = g4(a[i], b[i], nibble_to_bytemask(sign_nibble(bits[i])));
+    g[i] = g4(a[i], b[i], nibble_to_msb(sign_nibble(bits[i])));
 }
 } // namespace
 

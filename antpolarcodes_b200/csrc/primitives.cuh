@@ -43,6 +43,9 @@ POLAR_DEV uint32_t nibble_to_bytemask(uint32_t nib)
     return (((nib & 0xFu) * 0x00204081u) & 0x01010101u) * 0xFFu;
 }
 
+// low nibble (bit k) -> most significant bit of byte k (all g4 needs: its PRMTs replicate that bit)
+POLAR_DEV uint32_t nibble_to_msb(uint32_t nib) { return (nib & 0xFu) * 0x10204081u; }
+
 // min-sum f on four int8 pairs.  16 ALU ops per 4 elements.
 POLAR_DEV uint32_t f4(uint32_t a, uint32_t b)
 {
@@ -59,10 +62,11 @@ POLAR_DEV uint32_t f4(uint32_t a, uint32_t b)
     return (m ^ (sh * 0xFFu)) + sh;
 }
 
-// g on four int8 pairs: bit ? sat(b - a) : sat(b + a); `neg` has 0xFF in the bytes whose left bit is 1.
+// g on four int8 pairs: bit ? sat(b - a) : sat(b + a); `neg` carries the left bit of element k in the most
+// significant bit of byte k (nibble_to_msb; the other bits are ignored).
 POLAR_DEV uint32_t g4(uint32_t a, uint32_t b, uint32_t neg)
 {
-    const uint32_t me = prmt(neg, 0u, 0x2200u), mo = prmt(neg, 0u, 0x3311u);
+    const uint32_t me = prmt(neg, 0u, 0xAA88u), mo = prmt(neg, 0u, 0xBB99u); // sign-replicating selectors
     uint32_t ae = sext_even(a), ao = sext_odd(a);
     const uint32_t be = sext_even(b), bo = sext_odd(b);
     // conditional two's-complement negate in 16 bits (-(-128) = +128 is representable here)

@@ -189,7 +189,7 @@ POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_
                     b[t] = scl_ld<SG>(srcb + (w + t) * ss, chan);
                 }
 #pragma unroll
-                for (int t = 0; t < 8; ++t) scl_st<DG>(dst + (w + t) * ds, g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t))));
+                for (int t = 0; t < 8; ++t) scl_st<DG>(dst + (w + t) * ds, g4(a[t], b[t], nibble_to_msb(lw >> (4 * t))));
             }
         }
         if (G == 1) { // a lane owns the path: the four words of a batch share one word of left bits
@@ -202,7 +202,7 @@ POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_
                     b[t] = scl_ld<SG>(srcb + (w + t) * ss, chan);
                 }
 #pragma unroll
-                for (int t = 0; t < 4; ++t) scl_st<DG>(dst + (w + t) * ds, g4(a[t], b[t], nibble_to_bytemask(lw >> (4 * t))));
+                for (int t = 0; t < 4; ++t) scl_st<DG>(dst + (w + t) * ds, g4(a[t], b[t], nibble_to_msb(lw >> (4 * t))));
             }
         }
         for (; w + 3 * G < words; w += 4 * G) {
@@ -215,15 +215,15 @@ POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_
                 n[t] = lb[wt >> 3] >> ((wt & 7) * 4);
             }
 #pragma unroll
-            for (int t = 0; t < 4; ++t) scl_st<DG>(dst + (w + t * G) * ds, g4(a[t], b[t], nibble_to_bytemask(n[t])));
+            for (int t = 0; t < 4; ++t) scl_st<DG>(dst + (w + t * G) * ds, g4(a[t], b[t], nibble_to_msb(n[t])));
         }
         for (; w < words; w += G) {
             const uint32_t nib = lb[w >> 3] >> ((w & 7) * 4);
-            scl_st<DG>(dst + w * ds, g4(scl_ld<SG>(src + w * ss, chan), scl_ld<SG>(srcb + w * ss, chan), nibble_to_bytemask(nib)));
+            scl_st<DG>(dst + w * ds, g4(scl_ld<SG>(src + w * ss, chan), scl_ld<SG>(srcb + w * ss, chan), nibble_to_msb(nib)));
         }
     } else if (g == 0) {
         const uint32_t x = scl_ld<SG>(src, chan);
-        scl_st<DG>(dst, g4(x, x >> 16, nibble_to_bytemask(lb[0] & 3u)));
+        scl_st<DG>(dst, g4(x, x >> 16, nibble_to_msb(lb[0] & 3u)));
     }
 }
 
