@@ -17,6 +17,7 @@ _HERE = _os.path.dirname(_os.path.abspath(__file__))
 _LIB_PATH = _os.path.join(_HERE, "libpolar_cuda.so")
 
 KIND_ENC, KIND_FASTSSC_I8, KIND_FASTSSC_F32, KIND_SCL_I8, KIND_SCL_F32 = range(5)
+KIND_ADAPTIVE_I8, KIND_ADAPTIVE_F32, KIND_ADAPTIVE_MIXED = 5, 6, 7
 MEM_HOST, MEM_DEVICE = 0, 1
 LLR_I8, LLR_F32 = 0, 1
 
@@ -25,6 +26,7 @@ EXPORTS = [
     "polar_cuda_code_destroy", "polar_cuda_decode_batch", "polar_cuda_encode_batch",
     "polar_cuda_crc_generate", "polar_cuda_crc_check", "polar_cuda_frozen_bits", "polar_cuda_code_info",
     "polar_cuda_code_schedule", "polar_cuda_code_launches", "polar_cuda_test_fg", "polar_cuda_schedule_stats",
+    "polar_cuda_code_fallbacks",
 ]
 
 
@@ -60,6 +62,8 @@ def lib():
         l.polar_cuda_code_schedule.argtypes = [vp, vp, i]
         l.polar_cuda_code_launches.argtypes = [vp]
         l.polar_cuda_code_launches.restype = _c.c_long
+        l.polar_cuda_code_fallbacks.argtypes = [vp]
+        l.polar_cuda_code_fallbacks.restype = _c.c_long
         l.polar_cuda_test_fg.argtypes = [vp, vp, vp, i, vp, vp]
         _lib = l
     return _lib
@@ -154,6 +158,9 @@ class _Code:
     def launches(self):
         return int(lib().polar_cuda_code_launches(self._h))
 
+    def fallbacks(self):
+        return int(lib().polar_cuda_code_fallbacks(self._h))
+
 
 class PolarEncoder:
     """Encoding::ButterflyFipPacked behind the pypolar PolarEncoder surface (encoder_python.cc:28-61)."""
@@ -231,25 +238,36 @@ class PolarEncoder:
 class PolarDecoder:
     """Decoding::create(blockLength, listSize, frozenBits, decoderType) behind the pypolar PolarDecoder
     surface (decoder_python.cc:21-74).  listSize 1 -> Fast-SSC, listSize > 1 -> SCL; "char" = int8
-    arithmetic (FastSscFipChar / SclFipChar), "float" = fp32.  Like the reference's makeDecoder
-    (decoder.cpp:85) a fresh decoder checks CRC8 until setErrorDetection is called."""
+    arithmetic (FastSscFipChar / SclFipChar), "float" = fp32, "mixed" with listSize > 1 = AdaptiveFloat
+    (decoder.cpp:37-38,74-76: Fast-SSC first, the list decoder only on detector failures).  Like the
+    reference's makeDecoder (decoder.cpp:85) a fresh decoder checks CRC8 until setErrorDetection is called.
 
-    def __init__(self, blockLength, listSize, frozenBitPositions, decoderType="char", device=0):
+    ``adaptive=True`` (not in pypolar, whose factory cannot reach them) selects the adaptive classes the
+    reference's simulator builds directly: "char" -> AdaptiveChar, "float" -> AdaptiveFloat, "mixed" ->
+    AdaptiveMixed (int8 Fast-SSC + fp32 list decoder)."""
+
+    def __init__(self, blockLength, listSize, frozenBitPositions, decoderType="char", device=0, adaptive=False):
         t = str(decoderType).lower()
         if "char" in t:
-            flt = False
+            flavour = "char"
         elif "float" in t:
-            flt = True
-        elif "mixed" in t or "scan" in t:
+            flavour = "float"
+        elif "mixed" in t:
+            flavour = "mixed"
+        elif "scan" in t:
             raise RuntimeError("decoder type '%s' is outside the GPU hot path" % decoderType)
         else:
             raise ValueError("Unknown PolarDecoder type!")
         self._N, self._L = int(blockLength), int(listSize)
         self._frozen = _np.ascontiguousarray(frozenBitPositions, _np.uint32).copy()
-        if self._L <= 1:
-            self._kind = KIND_FASTSSC_F32 if flt else KIND_FASTSSC_I8
+        if adaptive:
+            self._kind = {"char": KIND_ADAPTIVE_I8, "float": KIND_ADAPTIVE_F32, "mixed": KIND_ADAPTIVE_MIXED}[flavour]
+        elif self._L <= 1:  # decoder.cpp:44-46: below two paths everything but "char" is the float Fast-SSC
+            self._kind = KIND_FASTSSC_I8 if flavour == "char" else KIND_FASTSSC_F32
+        elif flavour == "mixed":
+            self._kind = KIND_ADAPTIVE_F32
         else:
-            self._kind = KIND_SCL_F32 if flt else KIND_SCL_I8
+            self._kind = KIND_SCL_F32 if flavour == "float" else KIND_SCL_I8
         self._sys, self._crc, self._dev, self._code = True, 8, device, None
 
     def _get(self):
@@ -290,6 +308,10 @@ class PolarDecoder:
 
     def info(self):
         return self._get().info()
+
+    def fallbacks(self):
+        """adaptive decoders: frames redone by the list decoder so far"""
+        return self._get().fallbacks()
 
     def decode_vector(self, llr):
         """float32[N] or int8[N] -> uint8[K/8]; the detector verdict is dropped, as in decoder_python.cc."""

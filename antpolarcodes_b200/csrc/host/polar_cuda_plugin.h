@@ -8,6 +8,8 @@
 //   PolarCode::Decoding::FastSscCudaFloat  next to FastSscAvxFloat  (fastssc_avx_float.h:283)
 //   PolarCode::Decoding::SclCudaChar       next to SclFipChar       (scl_fip_char.h:391)
 //   PolarCode::Decoding::SclCudaFloat      next to SclAvxFloat      (scl_avx_float.h:407)
+//   PolarCode::Decoding::AdaptiveCudaChar / AdaptiveCudaFloat / AdaptiveCudaMixed
+//                                          next to AdaptiveChar / AdaptiveFloat / AdaptiveMixed (adaptive_char.h:26)
 //   PolarCode::Decoding::makeCudaDecoder   like makeDecoder         (decoder.cpp:50-87)
 //   PolarCode::Encoding::ButterflyCudaPacked next to ButterflyFipPacked (butterfly_fip_packed.h:25)
 //
@@ -81,9 +83,11 @@ class CudaDecoder : public Decoder
     CudaDetail::Handle mHandle;
     size_t mListSize;
     int mDevice;
+    int mAdaptiveKind; // POLAR_KIND_ADAPTIVE_* or -1
 
     int kind() const
     {
+        if (mAdaptiveKind >= 0) return mAdaptiveKind;
         if (mListSize > 1) return FLOAT ? POLAR_KIND_SCL_F32 : POLAR_KIND_SCL_I8;
         return FLOAT ? POLAR_KIND_FASTSSC_F32 : POLAR_KIND_FASTSSC_I8;
     }
@@ -93,8 +97,9 @@ class CudaDecoder : public Decoder
     }
 
 public:
-    CudaDecoder(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int device = 0)
-        : mListSize(listSize), mDevice(device)
+    CudaDecoder(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int device = 0,
+                int adaptiveKind = -1)
+        : mListSize(listSize), mDevice(device), mAdaptiveKind(adaptiveKind)
     {
         initialize(blockLength, frozenBits);
     }
@@ -129,6 +134,9 @@ public:
                                                   mOutputContainer, &ok, nullptr));
         return ok != 0;
     }
+
+    // adaptive kinds: frames the list decoder had to redo so far
+    long fallbacks() { return polar_cuda_code_fallbacks(code()); }
 
     // nFrames x blockLength() LLRs in, nFrames x ceil(infoLength()/8) bytes and nFrames verdicts out.
     // Host buffers: returns when the results are in place.  Device buffers: asynchronous on `stream`.
@@ -173,8 +181,30 @@ public:
         : CudaDecoder<true>(blockLength, listSize, frozenBits, device) {}
 };
 
-// makeDecoder (decoder.cpp:50-87) for the GPU types: decoder_impl 0 = char, 1 = float; like the CPU factory a
-// fresh decoder checks CRC8.
+// Adaptive decoders (adaptive_char.cpp:34-46): Fast-SSC on every frame, the list decoder on the detector failures.
+// The float container of the Mixed flavour keeps the LLRs as floats: the int8 Fast-SSC pass quantises them on the
+// device (like FastSscFipChar::setSignal would), the fp32 list decoder reads them as they are.
+class AdaptiveCudaChar : public CudaDecoder<false>
+{
+public:
+    AdaptiveCudaChar(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int device = 0)
+        : CudaDecoder<false>(blockLength, listSize, frozenBits, device, POLAR_KIND_ADAPTIVE_I8) {}
+};
+class AdaptiveCudaFloat : public CudaDecoder<true>
+{
+public:
+    AdaptiveCudaFloat(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int device = 0)
+        : CudaDecoder<true>(blockLength, listSize, frozenBits, device, POLAR_KIND_ADAPTIVE_F32) {}
+};
+class AdaptiveCudaMixed : public CudaDecoder<true>
+{
+public:
+    AdaptiveCudaMixed(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits, int device = 0)
+        : CudaDecoder<true>(blockLength, listSize, frozenBits, device, POLAR_KIND_ADAPTIVE_MIXED) {}
+};
+
+// makeDecoder (decoder.cpp:50-87) for the GPU types: decoder_impl 0 = char, 1 = float, 2 = adaptive float (what
+// Decoding::create maps "mixed" to); like the CPU factory a fresh decoder checks CRC8.
 inline Decoder* makeCudaDecoder(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits,
                                 int decoder_impl = 0, int device = 0)
 {
@@ -184,6 +214,7 @@ inline Decoder* makeCudaDecoder(size_t blockLength, size_t listSize, const std::
         else dec = new FastSscCudaChar(blockLength, frozenBits, device);
     } else {
         if (decoder_impl == 1) dec = new SclCudaFloat(blockLength, listSize, frozenBits, device);
+        else if (decoder_impl == 2) dec = new AdaptiveCudaFloat(blockLength, listSize, frozenBits, device);
         else dec = new SclCudaChar(blockLength, listSize, frozenBits, device);
     }
     dec->setErrorDetection(new ErrorDetection::CRC8());

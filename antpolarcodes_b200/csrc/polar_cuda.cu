@@ -72,6 +72,18 @@ struct polar_code {
     cudaStream_t pipe[2] = { nullptr, nullptr }; // HOST-buffer calls: double-buffered copy / compute pipeline
     cudaEvent_t pipeDone[2] = { nullptr, nullptr };
     long launches = 0;
+    // adaptive kinds: the two decoders and the compaction scratch
+    polar_code* fast = nullptr;
+    polar_code* list = nullptr;
+    uint32_t* dFailIdx = nullptr;  // frame numbers the list decoder redoes
+    uint32_t* dFailCount = nullptr;
+    uint32_t* hFailCount = nullptr; // pinned
+    void* dGather = nullptr;       // dense LLR rows of those frames
+    uint8_t* dOutC = nullptr;
+    uint8_t* dOkC = nullptr;
+    size_t idxFrames = 0, gatherFrames = 0;
+    int gatherRowBytes = 0;
+    long fallbacks = 0;
 };
 
 namespace {
@@ -294,6 +306,10 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab);
     cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
     cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns);
+    cudaFree(c->dFailIdx); cudaFree(c->dFailCount); cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
+    if (c->hFailCount) cudaFreeHost(c->hFailCount);
+    polar_cuda_code_destroy(c->fast);
+    polar_cuda_code_destroy(c->list);
     for (int i = 0; i < 2; ++i) {
         if (c->pipe[i]) cudaStreamDestroy(c->pipe[i]);
         if (c->pipeDone[i]) cudaEventDestroy(c->pipeDone[i]);
@@ -307,7 +323,33 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
 {
     if (!out) return fail(POLAR_E_ARG, "out is null");
     *out = nullptr;
-    if (kind < POLAR_KIND_ENC || kind > POLAR_KIND_SCL_F32) return fail(POLAR_E_ARG, "unknown kind");
+    if (kind < POLAR_KIND_ENC || kind > POLAR_KIND_ADAPTIVE_MIXED) return fail(POLAR_E_ARG, "unknown kind");
+    if (kind >= POLAR_KIND_ADAPTIVE_I8) {
+        // AdaptiveChar / AdaptiveFloat / AdaptiveMixed constructors (adaptive_char.cpp:15-26): one Fast-SSC and one
+        // list decoder over the same code, detector and systematic flag
+        const int fastKind = kind == POLAR_KIND_ADAPTIVE_F32 ? POLAR_KIND_FASTSSC_F32 : POLAR_KIND_FASTSSC_I8;
+        const int listKind = kind == POLAR_KIND_ADAPTIVE_I8 ? POLAR_KIND_SCL_I8 : POLAR_KIND_SCL_F32;
+        polar_code_t fast = nullptr, list = nullptr;
+        int rc = polar_cuda_code_create(device, fastKind, N, frozen, nFrozen, 1, systematic, crcBits, &fast);
+        if (rc) return rc;
+        if (listSize > 1) {
+            rc = polar_cuda_code_create(device, listKind, N, frozen, nFrozen, listSize, systematic, crcBits, &list);
+            if (rc) { const std::string msg = g_lastError; polar_cuda_code_destroy(fast); return fail(rc, msg); }
+        }
+        polar_code* c = new polar_code;
+        c->device = device; c->kind = kind; c->N = N; c->lgN = fast->lgN; c->K = fast->K; c->kb = fast->kb;
+        c->L = listSize > 1 ? listSize : 1; c->systematic = fast->systematic; c->crcBits = crcBits;
+        c->numSMs = fast->numSMs;
+        c->frozen = fast->frozen;
+        c->fast = fast; c->list = list;
+        if (cudaMalloc(&c->dFailCount, sizeof(uint32_t)) != cudaSuccess ||
+            cudaMallocHost(&c->hFailCount, sizeof(uint32_t)) != cudaSuccess) {
+            polar_cuda_code_destroy(c);
+            return fail(POLAR_E_CUDA, "adaptive decoder: counter allocation failed");
+        }
+        *out = c;
+        return POLAR_OK;
+    }
     if (N < 8 || N > 4096 || (N & (N - 1))) return fail(POLAR_E_ARG, "block length must be a power of two in [8, 4096]");
     if (nFrozen < 0 || nFrozen > N || (nFrozen && !frozen)) return fail(POLAR_E_ARG, "bad frozen set");
     if (crcBits != 0 && crcBits != 8 && crcBits != 16 && crcBits != 32) return fail(POLAR_E_ARG, "CRC INVALID SIZE!");
@@ -467,6 +509,98 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
     return POLAR_OK;
 }
 
+// AdaptiveChar::decode (adaptive_char.cpp:34-46) over a batch with DEVICE buffers: Fast-SSC on every frame; the
+// frames it fails are compacted, gathered into a dense batch for the list decoder and scattered back.
+static int adaptive_on_device(polar_code* c, const void* llr, int llrType, size_t nFrames, uint8_t* out, uint8_t* ok,
+                              cudaStream_t st)
+{
+    polar_code* fast = c->fast;
+    int rc = decode_on_device(fast, llr, llrType, nFrames, out, ok, st);
+    if (rc || !c->list) return rc;
+    if (nFrames > c->idxFrames) {
+        cudaFree(c->dFailIdx);
+        c->dFailIdx = nullptr; c->idxFrames = 0;
+        CUDA_TRY(cudaMalloc(&c->dFailIdx, nFrames * sizeof(uint32_t)));
+        c->idxFrames = nFrames;
+    }
+    CUDA_TRY(cudaMemsetAsync(c->dFailCount, 0, sizeof(uint32_t), st));
+    const int cgrid = (int)std::min<long long>(((long long)nFrames + 255) / 256, (long long)c->numSMs * 8);
+    adaptive_compact_kernel<<<cgrid, 256, 0, st>>>(ok, (long long)nFrames, c->dFailIdx, c->dFailCount);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(c->hFailCount, c->dFailCount, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st)); // the list decoder's grid is sized by the count
+    const size_t nFail = *c->hFailCount;
+    if (!nFail) return POLAR_OK;
+    c->fallbacks += (long)nFail;
+    // the list decoder reads what its CPU twin would: the int8 copy for SclFipChar, the float LLRs for SclAvxFloat
+    const bool listF32 = c->list->kind == POLAR_KIND_SCL_F32;
+    const void* src = llr;
+    if (!listF32 && llrType == POLAR_LLR_F32) src = fast->dQuant; // quantised once by the Fast-SSC pass
+    const int rowBytes = c->N * (listF32 ? 4 : 1);
+    if (nFail > c->gatherFrames || rowBytes > c->gatherRowBytes) {
+        cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
+        c->dGather = nullptr; c->dOutC = c->dOkC = nullptr; c->gatherFrames = 0;
+        const size_t cap = std::max(nFail, std::min(nFrames, std::max<size_t>(1024, 2 * nFail)));
+        const int rb = std::max(rowBytes, c->gatherRowBytes);
+        CUDA_TRY(cudaMalloc(&c->dGather, cap * (size_t)rb));
+        CUDA_TRY(cudaMalloc(&c->dOutC, cap * (size_t)c->kb));
+        CUDA_TRY(cudaMalloc(&c->dOkC, cap));
+        c->gatherFrames = cap; c->gatherRowBytes = rb;
+    }
+    const bool v16 = rowBytes % 16 == 0 && ((uintptr_t)src & 15) == 0;
+    const long long vecs = (long long)nFail * (rowBytes / (v16 ? 16 : 4));
+    const int ggrid = (int)std::min<long long>((vecs + 255) / 256, (long long)c->numSMs * 16);
+    if (v16)
+        adaptive_gather_kernel<uint4><<<ggrid, 256, 0, st>>>(static_cast<const uint4*>(src), c->dFailIdx, (long long)nFail,
+                                                             rowBytes / 16, static_cast<uint4*>(c->dGather));
+    else
+        adaptive_gather_kernel<uint32_t><<<ggrid, 256, 0, st>>>(static_cast<const uint32_t*>(src), c->dFailIdx, (long long)nFail,
+                                                                rowBytes / 4, static_cast<uint32_t*>(c->dGather));
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    rc = decode_on_device(c->list, c->dGather, listF32 ? POLAR_LLR_F32 : POLAR_LLR_I8, nFail, c->dOutC, c->dOkC, st);
+    if (rc) return rc;
+    const long long bytes = (long long)nFail * c->kb;
+    const int sgrid = (int)std::min<long long>((bytes + 255) / 256, (long long)c->numSMs * 16);
+    adaptive_scatter_kernel<<<sgrid, 256, 0, st>>>(c->dOutC, c->dOkC, c->dFailIdx, (long long)nFail, c->kb, out, ok);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return POLAR_OK;
+}
+
+static int adaptive_decode_batch(polar_code* c, const void* llr, int llrType, int mem, size_t nFrames, uint8_t* info_out,
+                                 uint8_t* ok_out, cudaStream_t st)
+{
+    if (c->kind != POLAR_KIND_ADAPTIVE_I8 && llrType != POLAR_LLR_F32)
+        return fail(POLAR_E_ARG, "AdaptiveFloat / AdaptiveMixed take float LLRs");
+    const int eb = llrType == POLAR_LLR_F32 ? 4 : 1;
+    if (mem == POLAR_MEM_DEVICE) {
+        uint8_t* okDev = ok_out;
+        if (!okDev) {
+            int rc = ensure_staging(c, nFrames, 0);
+            if (rc) return rc;
+            okDev = c->dOk;
+        }
+        return adaptive_on_device(c, llr, llrType, nFrames, info_out, okDev, st);
+    }
+    // HOST buffers: staged through the device in chunks of about 64 MB of LLRs
+    const size_t chunk = std::min(nFrames, std::max<size_t>(1, ((size_t)env_int("POLAR_CUDA_CHUNK_MB", 64) << 20) / ((size_t)c->N * eb)));
+    int rc = ensure_staging(c, chunk, eb);
+    if (rc) return rc;
+    const uint8_t* src = static_cast<const uint8_t*>(llr);
+    for (size_t f0 = 0; f0 < nFrames; f0 += chunk) {
+        const size_t n = std::min(chunk, nFrames - f0);
+        CUDA_TRY(cudaMemcpyAsync(c->dLlr, src + f0 * c->N * eb, n * c->N * (size_t)eb, cudaMemcpyHostToDevice, st));
+        rc = adaptive_on_device(c, c->dLlr, llrType, n, c->dOut, c->dOk, st);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpyAsync(info_out + f0 * c->kb, c->dOut, n * (size_t)c->kb, cudaMemcpyDeviceToHost, st));
+        if (ok_out) CUDA_TRY(cudaMemcpyAsync(ok_out + f0, c->dOk, n, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    return POLAR_OK;
+}
+
 int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int mem, size_t nFrames,
                             uint8_t* info_out, uint8_t* ok_out, void* stream)
 {
@@ -479,6 +613,7 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
         return fail(POLAR_E_ARG, "an fp32 decoder takes float LLRs");
     CUDA_TRY(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
+    if (c->kind >= POLAR_KIND_ADAPTIVE_I8) return adaptive_decode_batch(c, llr, llrType, mem, nFrames, info_out, ok_out, st);
     const int eb = llrType == POLAR_LLR_F32 ? 4 : 1;
     if (mem == POLAR_MEM_DEVICE) {
         uint8_t* okDev = ok_out;
@@ -594,6 +729,11 @@ int polar_cuda_frozen_bits(int N, int K, float designSnr, const char* type, uint
 int polar_cuda_code_info(polar_code_t c, struct polar_code_info* info)
 {
     if (!c || !info) return fail(POLAR_E_ARG, "null argument");
+    if (c->fast) { // adaptive: geometry and algorithmic figures of the Fast-SSC pass every frame takes
+        int rc = polar_cuda_code_info(c->fast, info);
+        info->kind = c->kind; info->listSize = c->L;
+        return rc;
+    }
     memset(info, 0, sizeof(*info));
     info->kind = c->kind; info->N = c->N; info->K = c->K; info->listSize = c->L;
     info->systematic = c->systematic; info->crcBits = c->crcBits;
@@ -611,12 +751,19 @@ int polar_cuda_code_info(polar_code_t c, struct polar_code_info* info)
 int polar_cuda_code_schedule(polar_code_t c, uint32_t* ops, int maxOps)
 {
     if (!c) return fail(POLAR_E_ARG, "null code handle");
+    if (c->fast) c = c->fast;
     const int n = (int)c->ops.size();
     if (ops) memcpy(ops, c->ops.data(), sizeof(uint32_t) * std::min(n, maxOps));
     return n;
 }
 
-long polar_cuda_code_launches(polar_code_t c) { return c ? c->launches : 0; }
+long polar_cuda_code_launches(polar_code_t c)
+{
+    if (!c) return 0;
+    return c->launches + (c->fast ? c->fast->launches : 0) + (c->list ? c->list->launches : 0);
+}
+
+long polar_cuda_code_fallbacks(polar_code_t c) { return c ? c->fallbacks : 0; }
 
 int polar_cuda_schedule_stats(int kind, int N, const uint32_t* frozen, int nFrozen, int listSize, long* counts,
                               long* sizes, double* laneOpsPerFrame)

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- info-bit Gbit/s of the batched polar decoders on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload scl8|fastssc|scl32]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload scl8|fastssc|scl32|adaptive8|...]
 
 A "step" is one decode pass over one batch of synthetic noisy codewords (AWGN/BPSK, Eb/N0 = 2 dB,
 int8 LLRs).  Headline workload = BASELINE configs[2]: SCL L=8 + CRC16, N=1024 K=512,
@@ -36,6 +36,8 @@ WORKLOADS = {
                      label="SCL fp32 L=8 + CRC16, N=1024 K=512, 5G frozen set, Eb/N0=2dB"),
     "encode": dict(N=256, K=128, ctype="BB", L=1, crc=0, frames=1 << 22, e2e_frames=1 << 21, encoder=True,
                    label="packed butterfly encoder, systematic, N=256 K=128, BB frozen set"),
+    "adaptive8": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 20, e2e_frames=1 << 19, adaptive=True,
+                      label="AdaptiveChar (Fast-SSC int8, SCL L=8 on CRC16 failures), N=1024 K=512, 5G frozen set, Eb/N0=2dB"),
     "scl32": dict(N=2048, K=1024, ctype="BB", L=32, crc=32, frames=1 << 16, e2e_frames=1 << 16,
                   label="SCL L=32 + CRC32, N=2048 K=1024, BB frozen set, int8 LLR, Eb/N0=2dB"),
 }
@@ -126,8 +128,11 @@ def ref_threads():
 
 def time_reference(wl, frozen, llr_host, seconds_target, threads):
     """The unmodified reference decoders (oracle/_ref) on the host cores, one decoder object per thread."""
-    from polar_testlib import KIND_FASTSSC_F32, KIND_FASTSSC_I8, KIND_SCL_F32, KIND_SCL_I8, ref_decode
-    if wl.get("fmt") == "f32":
+    from polar_testlib import KIND_ADAPTIVE_I8, KIND_FASTSSC_F32, KIND_FASTSSC_I8, KIND_SCL_F32, KIND_SCL_I8, ref_decode
+    if wl.get("adaptive"):  # AdaptiveChar only takes float LLRs (adaptive_char.cpp:60-64); its quantiser maps them back
+        kind = KIND_ADAPTIVE_I8
+        llr_host = np.ascontiguousarray(llr_host, np.float32)
+    elif wl.get("fmt") == "f32":
         kind = KIND_SCL_F32 if wl["L"] > 1 else KIND_FASTSSC_F32
     else:
         kind = KIND_SCL_I8 if wl["L"] > 1 else KIND_FASTSSC_I8
@@ -330,10 +335,14 @@ def run_ours(args, wl):
     e2e_frames = min(args.e2e_frames or wl["e2e_frames"], frames)
     frozen = ap.frozen_bits(N, K, 0.0, wl["ctype"])
     f32 = wl.get("fmt") == "f32"
-    dec = ap.PolarDecoder(N, L, frozen, "float" if f32 else "char", device=local)
+    adaptive = bool(wl.get("adaptive"))
+    dec = ap.PolarDecoder(N, L, frozen, "float" if f32 else "char", device=local, adaptive=adaptive)
     dec.setErrorDetection(crc)
     dec.setSystematic(True)
     info = dec.info()
+    lane_ops_list = 0.0
+    if adaptive:  # algorithmic work of the list pass, charged per frame that falls through
+        lane_ops_list = ap._Code(ap.KIND_SCL_I8, N, frozen, L, True, crc, local).info().laneOpsPerFrame
 
     # frames are sharded by rank: every rank decodes its own `frames` frames (weak scaling), no
     # data-path collective
@@ -370,6 +379,12 @@ def run_ours(args, wl):
     kernel_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
     launches = dec._get().launches() - launches0
     clocks = sampler.stop() if rank == 0 else None
+    redo_frac = 0.0
+    if adaptive:
+        fb0 = dec.fallbacks()
+        step()
+        torch.cuda.synchronize(device)
+        redo_frac = (dec.fallbacks() - fb0) / frames
 
     # correctness of what was timed: frame errors vs the transmitted payload + verdicts
     frame_err = int((out != sent).any(dim=1).sum().item())
@@ -408,9 +423,10 @@ def run_ours(args, wl):
         sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
         alu_peak_max = 148 * 128 * sm_max * 1e6 / 1e12     # T lane-ops/s at max clock
         alu_peak_run = 148 * 128 * sm_mhz * 1e6 / 1e12
-        alu = fps * info.laneOpsPerFrame / 1e12
+        lane_ops = info.laneOpsPerFrame + redo_frac * lane_ops_list
+        alu = fps * lane_ops / 1e12
         hbm = fps * info.bytesPerFrame / 1e9
-        alu_bound = (info.laneOpsPerFrame / (alu_peak_max * 1e12)) > (info.bytesPerFrame / (hbm_peak * 1e9))
+        alu_bound = (lane_ops / (alu_peak_max * 1e12)) > (info.bytesPerFrame / (hbm_peak * 1e9))
         traffic, traffic_src = None, None
         try:  # DRAM bytes per launch from the committed ncu capture of this kernel (profiles/traffic.json)
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
@@ -424,7 +440,7 @@ def run_ours(args, wl):
                 "frac": (alu / alu_peak_max) if alu_bound else hbm / hbm_peak, "traffic": traffic,
                 "peak_source": which + (" sm_max_mhz x 148 SM x 128 lanes" if alu_bound else " hbm copy"),
                 "frac_at_run_clock": alu / alu_peak_run,
-                "alu": {"lane_ops_per_frame": info.laneOpsPerFrame, "achieved_T": alu, "peak_T": alu_peak_max},
+                "alu": {"lane_ops_per_frame": lane_ops, "achieved_T": alu, "peak_T": alu_peak_max},
                 "hbm": {"bytes_per_frame": info.bytesPerFrame, "achieved_GBs": hbm, "peak_GBs": hbm_peak,
                         "frac": hbm / hbm_peak},
                 "traffic_source": traffic_src, "algorithmic_bytes": info.bytesPerFrame * frames,
@@ -446,7 +462,8 @@ def run_ours(args, wl):
                 "config": {"workload": wl["label"], "frames_per_step_per_gpu": frames, "e2e_frames_per_step_per_gpu": e2e_frames,
                            "list_size": L, "crc_bits": crc, "cache": "inputs larger than L2 (%d MiB of LLRs per step)" % (frames * N * (4 if f32 else 1) >> 20),
                            "warps_per_block": info.warpsPerBlock, "blocks_per_sm": info.blocksPerSM,
-                           "smem_per_warp": info.smemPerWarp, "schedule_ops": info.nOps, "parallelism": "frames sharded x%d" % world},
+                           "smem_per_warp": info.smemPerWarp, "schedule_ops": info.nOps, "parallelism": "frames sharded x%d" % world,
+                           **({"list_decoder_frame_fraction": redo_frac} if adaptive else {})},
                 "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": e2e_frames * N * (4 if f32 else 1),
                         "d2h_bytes_per_step": e2e_frames * (K // 8 + 1), "matches_device_run": e2e_match},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,

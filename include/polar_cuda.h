@@ -30,7 +30,12 @@ enum polar_kind {
     POLAR_KIND_FASTSSC_I8 = 1,  /* Decoding::FastSscFipChar       fastssc_fip_char.h:298      */
     POLAR_KIND_FASTSSC_F32 = 2, /* Decoding::FastSscAvxFloat      fastssc_avx_float.h:283     */
     POLAR_KIND_SCL_I8 = 3,      /* Decoding::SclFipChar           scl_fip_char.h:391          */
-    POLAR_KIND_SCL_F32 = 4      /* Decoding::SclAvxFloat          scl_avx_float.h:407         */
+    POLAR_KIND_SCL_F32 = 4,     /* Decoding::SclAvxFloat          scl_avx_float.h:407         */
+    /* adaptive decoders: Fast-SSC on every frame, the list decoder only on the frames whose Fast-SSC result
+     * fails the detector (adaptive_char.cpp:34-46); listSize 1 = Fast-SSC only, like the reference */
+    POLAR_KIND_ADAPTIVE_I8 = 5,    /* Decoding::AdaptiveChar   FastSscFipChar  + SclFipChar   adaptive_char.h:26  */
+    POLAR_KIND_ADAPTIVE_F32 = 6,   /* Decoding::AdaptiveFloat  FastSscAvxFloat + SclAvxFloat  adaptive_float.h    */
+    POLAR_KIND_ADAPTIVE_MIXED = 7  /* Decoding::AdaptiveMixed  FastSscFipChar  + SclAvxFloat  adaptive_mixed.h    */
 };
 
 enum polar_mem { POLAR_MEM_HOST = 0, POLAR_MEM_DEVICE = 1 };
@@ -63,7 +68,10 @@ int polar_cuda_code_destroy(polar_code_t code);
  *   info_out : nFrames x ceil(K/8) bytes;  ok_out : nFrames bytes (the bool decode() returns)
  *   mem      : where llr / info_out / ok_out live (all three the same)
  *   stream   : cudaStream_t (0 = default stream).  HOST buffers are copied synchronously;
- *              DEVICE buffers are processed asynchronously on the stream. */
+ *              DEVICE buffers are processed asynchronously on the stream (adaptive kinds wait once on the
+ *              stream for the count of failed frames before they launch the list decoder).
+ * Adaptive kinds: ADAPTIVE_I8 takes int8 or float LLRs (float is quantised once, both decoders see the int8
+ * copy, like AdaptiveChar::setSignal, adaptive_char.cpp:60-64); ADAPTIVE_F32 and ADAPTIVE_MIXED take float. */
 int polar_cuda_decode_batch(polar_code_t code, const void* llr, int llrType, int mem, size_t nFrames,
                             uint8_t* info_out, uint8_t* ok_out, void* stream);
 
@@ -98,6 +106,9 @@ int polar_cuda_schedule_stats(int kind, int N, const uint32_t* frozen, int nFroz
                               long* sizes, double* laneOpsPerFrame);
 /* number of kernel launches issued through this handle so far (bench's gpu_launches) */
 long polar_cuda_code_launches(polar_code_t code);
+/* adaptive kinds: frames the list decoder had to redo, summed over all decode calls on this handle so far
+ * (the `!success && mListSize > 1` branch of AdaptiveChar::decode, adaptive_char.cpp:39); 0 for other kinds */
+long polar_cuda_code_fallbacks(polar_code_t code);
 
 /* Primitive self-test hooks (golden vectors of decodingtest.cpp:504-737): element-wise F / G over
  * n int8 values on the device, through the very device functions the decoders use. */

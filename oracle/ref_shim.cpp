@@ -10,10 +10,14 @@
 //   PolarCode::Decoding::FastSscAvxFloat      (src/polarcode/decoding/fastssc_avx_float.cpp:940-955)
 //   PolarCode::Decoding::SclFipChar           (src/polarcode/decoding/scl_fip_char.cpp:801-855)
 //   PolarCode::Decoding::SclAvxFloat          (src/polarcode/decoding/scl_avx_float.cpp:696-750)
+//   PolarCode::Decoding::AdaptiveChar / AdaptiveFloat / AdaptiveMixed  (src/polarcode/decoding/adaptive_char.cpp:34-46)
 //   PolarCode::ErrorDetection::create         (src/polarcode/errordetection/errordetector.cpp:23-67)
 // No reference source is copied here; this file only calls the public API.
 #include <polarcode/bitcontainer.h>
 #include <polarcode/construction/constructor.h>
+#include <polarcode/decoding/adaptive_char.h>
+#include <polarcode/decoding/adaptive_float.h>
+#include <polarcode/decoding/adaptive_mixed.h>
 #include <polarcode/decoding/decoder.h>
 #include <polarcode/decoding/fastssc_avx_float.h>
 #include <polarcode/decoding/fastssc_fip_char.h>
@@ -35,7 +39,8 @@ using namespace PolarCode;
 namespace {
 
 // kind values shared with include/polar_cuda.h (POLAR_KIND_*)
-enum { KIND_ENC = 0, KIND_FASTSSC_I8 = 1, KIND_FASTSSC_F32 = 2, KIND_SCL_I8 = 3, KIND_SCL_F32 = 4 };
+enum { KIND_ENC = 0, KIND_FASTSSC_I8 = 1, KIND_FASTSSC_F32 = 2, KIND_SCL_I8 = 3, KIND_SCL_F32 = 4,
+       KIND_ADAPTIVE_I8 = 5, KIND_ADAPTIVE_F32 = 6, KIND_ADAPTIVE_MIXED = 7 };
 
 struct RefCode {
     int kind = 0;
@@ -52,6 +57,9 @@ Decoding::Decoder* make_decoder(const RefCode& c)
     case KIND_FASTSSC_F32: d = new Decoding::FastSscAvxFloat(c.N, c.frozen); break;
     case KIND_SCL_I8: d = new Decoding::SclFipChar(c.N, c.L, c.frozen); break;
     case KIND_SCL_F32: d = new Decoding::SclAvxFloat(c.N, c.L, c.frozen); break;
+    case KIND_ADAPTIVE_I8: d = new Decoding::AdaptiveChar(c.N, c.L, c.frozen); break;
+    case KIND_ADAPTIVE_F32: d = new Decoding::AdaptiveFloat(c.N, c.L, c.frozen); break;
+    case KIND_ADAPTIVE_MIXED: d = new Decoding::AdaptiveMixed(c.N, c.L, c.frozen); break;
     default: return nullptr;
     }
     d->setSystematic(c.systematic != 0);
@@ -116,7 +124,8 @@ int polar_ref_encode(void* h, uint8_t* info, uint8_t* code, long nFrames)
 }
 
 // Decode nFrames with nThreads worker threads (one decoder object per thread, disjoint
-// contiguous slices).  llr is int8 for *_I8 kinds, float for *_F32 kinds.  repeat > 1
+// contiguous slices).  llr is int8 for *_I8 kinds, float for *_F32 kinds and for all three adaptive kinds (the
+// adaptive classes only override setSignal(const float*), adaptive_char.cpp:60-64).  repeat > 1
 // re-decodes the same pool (for timing).  Returns elapsed seconds (decode loop only) or < 0.
 double polar_ref_decode(void* h, const void* llr, long nFrames, uint8_t* out, uint8_t* ok,
                         int nThreads, int repeat)
@@ -125,7 +134,7 @@ double polar_ref_decode(void* h, const void* llr, long nFrames, uint8_t* out, ui
     if (nThreads < 1) nThreads = 1;
     if (repeat < 1) repeat = 1;
     const size_t kb = (c->K + 7) / 8;
-    const bool isFloat = (c->kind == KIND_FASTSSC_F32 || c->kind == KIND_SCL_F32);
+    const bool isFloat = (c->kind == KIND_FASTSSC_F32 || c->kind == KIND_SCL_F32 || c->kind >= KIND_ADAPTIVE_I8);
     std::vector<Decoding::Decoder*> decs(nThreads, nullptr);
     try {
         for (int t = 0; t < nThreads; ++t) decs[t] = make_decoder(*c);

@@ -8,6 +8,9 @@
 #include <polar_cuda_plugin.h>
 
 #include <polarcode/construction/constructor.h>
+#include <polarcode/decoding/adaptive_char.h>
+#include <polarcode/decoding/adaptive_float.h>
+#include <polarcode/decoding/adaptive_mixed.h>
 #include <polarcode/decoding/fastssc_avx_float.h>
 #include <polarcode/decoding/fastssc_fip_char.h>
 #include <polarcode/decoding/scl_avx_float.h>
@@ -154,6 +157,78 @@ static void runCase(const Case& c, bool sys)
                 c.impl ? "float" : "char", c.crc, (int)sys, c.ctype, c.frames, okCount);
 }
 
+// Adaptive decoders: the reference's AdaptiveChar / AdaptiveFloat / AdaptiveMixed (adaptive_char.cpp:34-46) against
+// AdaptiveCudaChar / Float / Mixed through Decoder*, float LLRs (the only setSignal the reference classes override).
+// flavour 0 char, 1 float, 2 mixed.  The fp32 list decoder inside Float / Mixed is history dependent: fresh object per frame.
+static Decoding::Decoder* makeRefAdaptive(int flavour, int N, int L, const std::vector<unsigned>& frozen, int crc)
+{
+    Decoding::Decoder* d = flavour == 0   ? (Decoding::Decoder*)new Decoding::AdaptiveChar(N, L, frozen)
+                           : flavour == 1 ? (Decoding::Decoder*)new Decoding::AdaptiveFloat(N, L, frozen)
+                                          : (Decoding::Decoder*)new Decoding::AdaptiveMixed(N, L, frozen);
+    d->setErrorDetection(ErrorDetection::create(crc, "crc"));
+    return d;
+}
+
+static void runAdaptive(int flavour, int N, int K, int L, int crc, int frames, const char* ctype, float ebn0)
+{
+    const std::vector<unsigned> frozen = Construction::frozen_bits(N, K, 0.0f, ctype);
+    const int kb = K / 8, nb = N / 8;
+    std::mt19937 rng(77u + N + 3u * flavour);
+    std::unique_ptr<Encoding::Encoder> enc(new Encoding::ButterflyFipPacked(N, frozen));
+    enc->setErrorDetection(ErrorDetection::create(crc, "crc"));
+    const float sigma = 1.0f / std::sqrt(2.0f * ((float)K / N) * std::pow(10.0f, ebn0 / 10.0f));
+    std::normal_distribution<float> noise(0.0f, sigma);
+    std::vector<float> fl((size_t)frames * N);
+    for (int f = 0; f < frames; ++f) {
+        std::vector<unsigned char> a(kb), cw(nb);
+        for (auto& b : a) b = (unsigned char)(rng() & 0xFF);
+        enc->encode_vector(a.data(), cw.data());
+        for (int i = 0; i < N; ++i) {
+            const int bit = (cw[i / 8] >> (7 - i % 8)) & 1;
+            const float y = (1.0f - 2.0f * bit) + noise(rng);
+            fl[(size_t)f * N + i] = flavour == 0 ? 10.0f * y : 2.0f * y / (sigma * sigma);
+        }
+    }
+    std::unique_ptr<Decoding::Decoder> refDec(makeRefAdaptive(flavour, N, L, frozen, crc));
+    std::unique_ptr<Decoding::Decoder> gpuDec(flavour == 0   ? (Decoding::Decoder*)new Decoding::AdaptiveCudaChar(N, L, frozen)
+                                              : flavour == 1 ? (Decoding::Decoder*)new Decoding::AdaptiveCudaFloat(N, L, frozen)
+                                                             : (Decoding::Decoder*)new Decoding::AdaptiveCudaMixed(N, L, frozen));
+    gpuDec->setErrorDetection(ErrorDetection::create(crc, "crc"));
+    std::vector<unsigned char> want((size_t)frames * kb), wantOk(frames), got(want.size()), gotOk(frames);
+    int oneBad = 0, okCount = 0;
+    for (int f = 0; f < frames; ++f) {
+        if (flavour != 0) refDec.reset(makeRefAdaptive(flavour, N, L, frozen, crc));
+        const bool r = refDec->decode_vector(&fl[(size_t)f * N], &want[(size_t)f * kb]);
+        wantOk[f] = r ? 1 : 0;
+        okCount += r;
+        if (f < 12) {
+            std::vector<unsigned char> o(kb);
+            const bool g = gpuDec->decode_vector(&fl[(size_t)f * N], o.data());
+            if (g != r || std::memcmp(o.data(), &want[(size_t)f * kb], kb)) ++oneBad;
+        }
+    }
+    long redone;
+    if (flavour == 0) {
+        auto* d = static_cast<Decoding::CudaDecoder<false>*>(gpuDec.get());
+        const long before = d->fallbacks();
+        d->decode_batch(fl.data(), frames, got.data(), gotOk.data());
+        redone = d->fallbacks() - before;
+    } else {
+        auto* d = static_cast<Decoding::CudaDecoder<true>*>(gpuDec.get());
+        const long before = d->fallbacks();
+        d->decode_batch(fl.data(), frames, got.data(), gotOk.data());
+        redone = d->fallbacks() - before;
+    }
+    int batchBad = 0;
+    for (int f = 0; f < frames; ++f)
+        if (gotOk[f] != wantOk[f] || std::memcmp(&got[(size_t)f * kb], &want[(size_t)f * kb], kb)) ++batchBad;
+    CHECK(oneBad == 0, "adaptive decode_vector flavour=%d N=%d L=%d: %d of 12 frames differ", flavour, N, L, oneBad);
+    CHECK(batchBad == 0, "adaptive decode_batch flavour=%d N=%d L=%d: %d of %d frames differ", flavour, N, L, batchBad, frames);
+    CHECK(redone > 0 && redone < frames, "adaptive flavour=%d: %ld of %d frames fell through to the list decoder", flavour, redone, frames);
+    std::printf("adaptive %s N=%d K=%d L=%d crc=%d: %d frames, %ld redone by the list decoder, %d pass the detector\n",
+                flavour == 0 ? "char" : flavour == 1 ? "float" : "mixed", N, K, L, crc, frames, redone, okCount);
+}
+
 int main(int argc, char** argv)
 {
     if (polar_cuda_device_count() < 1) {
@@ -171,6 +246,13 @@ int main(int argc, char** argv)
         if (quick && n++ >= 3) break;
         runCase(c, true);
         runCase(c, false);
+    }
+    runAdaptive(0, 1024, 512, 8, 16, 96, "5G", 1.5f);
+    if (!quick) {
+        runAdaptive(1, 1024, 512, 8, 16, 32, "5G", 1.5f);
+        runAdaptive(2, 1024, 512, 8, 16, 32, "5G", 1.5f);
+        runAdaptive(0, 256, 128, 4, 8, 128, "BB", 1.0f);
+        runAdaptive(2, 256, 128, 4, 8, 64, "BB", 1.0f);
     }
     // error behaviour: the reference throws std::logic_error("CRC INVALID SIZE!") for an unknown CRC width
     // (errordetector.cpp:33-35); a block length that is not a power of two is an invalid argument

@@ -14,6 +14,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 KIND_ENC, KIND_FASTSSC_I8, KIND_FASTSSC_F32, KIND_SCL_I8, KIND_SCL_F32 = range(5)
+KIND_ADAPTIVE_I8, KIND_ADAPTIVE_F32, KIND_ADAPTIVE_MIXED = 5, 6, 7
+# adaptive kind -> (Fast-SSC kind, list kind) (adaptive_char.cpp:24-25, adaptive_float.cpp, adaptive_mixed.cpp:24-25)
+ADAPTIVE_PARTS = {KIND_ADAPTIVE_I8: (KIND_FASTSSC_I8, KIND_SCL_I8), KIND_ADAPTIVE_F32: (KIND_FASTSSC_F32, KIND_SCL_F32),
+                  KIND_ADAPTIVE_MIXED: (KIND_FASTSSC_I8, KIND_SCL_F32)}
 NODE_NAMES = ["F", "G", "C", "G_R1", "G_0R", "R0", "R1", "REP", "REP2", "SPC", "ZERO_SPC", "ZERO_ONE"]
 
 _c = ctypes
@@ -126,7 +130,35 @@ def ref_decode_fresh(kind, N, frozen, llr, L=1, systematic=1, crc=0):
 
 
 def is_float_kind(kind):
-    return kind in (KIND_FASTSSC_F32, KIND_SCL_F32)
+    return kind in (KIND_FASTSSC_F32, KIND_SCL_F32, KIND_ADAPTIVE_F32, KIND_ADAPTIVE_MIXED)
+
+
+def ref_decode_adaptive(kind, N, frozen, llr, L, systematic=1, crc=0, fresh=False):
+    """The reference's AdaptiveChar / AdaptiveFloat / AdaptiveMixed objects.  They only take float LLRs
+    (adaptive_char.cpp:60-64); int8 LLRs are widened, which CharContainer::insertLlr maps back unchanged.
+    fresh = one new object per frame (the fp32 list decoder inside is history dependent, see ref_decode_fresh)."""
+    f = np.ascontiguousarray(llr, np.float32)
+    if fresh:
+        return ref_decode_fresh(kind, N, frozen, f, L, systematic, crc)
+    o, k, _ = ref_decode(kind, N, frozen, f, L, systematic, crc)
+    return o, k
+
+
+def oracle_decode_adaptive(kind, N, frozen, llr, L, systematic=1, crc=0):
+    """AdaptiveChar::decode (adaptive_char.cpp:34-46) composed from the oracle's Fast-SSC and list decoders:
+    the list decoder's result replaces the Fast-SSC one wherever the detector rejected it (and L > 1).
+    Returns (info, ok, number of frames the list decoder redid)."""
+    fastKind, listKind = ADAPTIVE_PARTS[kind]
+    llr = np.ascontiguousarray(llr)
+    as_i8 = (lambda x: x if x.dtype == np.int8 else oracle_quantize(x))
+    fin = llr if is_float_kind(fastKind) else as_i8(llr)
+    out, ok = oracle_decode(fastKind, N, frozen, fin, 1, systematic, crc)
+    bad = np.flatnonzero(ok == 0)
+    if L > 1 and len(bad):
+        lin = llr if is_float_kind(listKind) else as_i8(llr)
+        o2, k2 = oracle_decode(listKind, N, frozen, lin[bad], L, systematic, crc)
+        out[bad], ok[bad] = o2, k2
+    return out, ok, (len(bad) if L > 1 else 0)
 
 
 def workload(name, kind, N, frozen, n, crc, seed=None):
