@@ -26,7 +26,9 @@ EXPORTS = [
     "polar_cuda_code_destroy", "polar_cuda_decode_batch", "polar_cuda_encode_batch",
     "polar_cuda_crc_generate", "polar_cuda_crc_check", "polar_cuda_frozen_bits", "polar_cuda_code_info",
     "polar_cuda_code_schedule", "polar_cuda_code_launches", "polar_cuda_test_fg", "polar_cuda_schedule_stats",
-    "polar_cuda_code_fallbacks",
+    "polar_cuda_code_fallbacks", "polar_cuda_puncturer_positions", "polar_cuda_puncturer_create",
+    "polar_cuda_puncturer_destroy", "polar_cuda_puncturer_parent_length", "polar_cuda_puncture_batch",
+    "polar_cuda_depuncture_batch", "polar_cuda_puncture_packed_batch",
 ]
 
 
@@ -65,6 +67,13 @@ def lib():
         l.polar_cuda_code_fallbacks.argtypes = [vp]
         l.polar_cuda_code_fallbacks.restype = _c.c_long
         l.polar_cuda_test_fg.argtypes = [vp, vp, vp, i, vp, vp]
+        l.polar_cuda_puncturer_positions.argtypes = [i, vp, i, vp]
+        l.polar_cuda_puncturer_create.argtypes = [i, i, vp, i, _c.POINTER(vp)]
+        l.polar_cuda_puncturer_destroy.argtypes = [vp]
+        l.polar_cuda_puncturer_parent_length.argtypes = [vp]
+        l.polar_cuda_puncture_batch.argtypes = [vp, vp, i, i, sz, vp, vp]
+        l.polar_cuda_depuncture_batch.argtypes = [vp, vp, i, i, sz, vp, vp]
+        l.polar_cuda_puncture_packed_batch.argtypes = [vp, vp, i, sz, vp, vp]
         _lib = l
     return _lib
 
@@ -74,6 +83,8 @@ def _check(rc):
         msg = lib().polar_cuda_last_error().decode()
         if rc == -1:
             raise ValueError(msg)        # std::invalid_argument / std::logic_error in the reference
+        if rc == -5:
+            raise IndexError(msg)        # std::out_of_range (pybind11 translates it to IndexError)
         raise RuntimeError(msg)
     return rc
 
@@ -359,6 +370,111 @@ class PolarDecoder:
             raise RuntimeError("llr, out and ok must live in the same memory space")
         _check(lib().polar_cuda_decode_batch(self._get()._h, lp, lt, mem, n, op, kp, stream))
         return out, ok
+
+
+class Puncturer:
+    """PolarCode::Puncturer behind the pypolar surface (puncturer_python.cc:19-150): rate matching by dropping the
+    first parentBlockLength - blockLength frozen positions of the parent code word.  The one-vector methods
+    (puncture / depuncture / puncturePacked) keep the binding's signatures; the *_batch methods take
+    [nFrames, ...] numpy arrays (host) or torch CUDA tensors."""
+
+    def __init__(self, blockLength, frozenBitPositions, device=0):
+        self._M = int(blockLength)
+        self._frozen = _np.ascontiguousarray(frozenBitPositions, _np.uint32).copy()
+        out = _np.zeros(max(2 * self._M, 8), _np.uint32)
+        n = _check(lib().polar_cuda_puncturer_positions(self._M, self._frozen.ctypes.data, len(self._frozen),
+                                                        out.ctypes.data))
+        self._pos = out[:n].copy()
+        self._parent = 1
+        while self._parent < self._M:
+            self._parent <<= 1
+        self._dev, self._h = device, None
+
+    def _get(self):
+        if self._h is None:
+            h = _c.c_void_p()
+            _check(lib().polar_cuda_puncturer_create(int(self._dev), self._M, self._frozen.ctypes.data,
+                                                     len(self._frozen), _c.byref(h)))
+            self._h = h
+        return self._h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None:
+            lib().polar_cuda_puncturer_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def blockLength(self):
+        return self._M
+
+    def parentBlockLength(self):
+        return self._parent
+
+    def blockOutputPositions(self):
+        return [int(p) for p in self._pos]
+
+    @staticmethod
+    def _elem(x):
+        size = x.element_size() if _is_torch(x) else x.dtype.itemsize
+        if size not in (1, 4, 8):
+            raise RuntimeError("elements must be 1, 4 or 8 bytes wide (uint8 / int8, float32, float64)")
+        return size
+
+    def _run(self, fn, x, in_cols, out_cols, packed=False, out=None, stream=0):
+        if x.ndim != 2 or x.shape[1] != in_cols:
+            raise RuntimeError("Input vector size mismatch!")
+        n = x.shape[0]
+        if out is None:
+            if _is_torch(x):
+                import torch
+                out = torch.empty((n, out_cols), dtype=x.dtype, device=x.device)
+            else:
+                x = _np.ascontiguousarray(x)
+                out = _np.empty((n, out_cols), x.dtype)
+        ip, mem = _buf(x)
+        op, mem2 = _buf(out)
+        if mem != mem2:
+            raise RuntimeError("input and output must live in the same memory space")
+        if packed:
+            _check(fn(self._get(), ip, mem, n, op, stream))
+        else:
+            _check(fn(self._get(), ip, self._elem(x), mem, n, op, stream))
+        return out
+
+    def puncture_batch(self, x, out=None, stream=0):
+        """[nFrames, parentBlockLength] -> [nFrames, blockLength]"""
+        return self._run(lib().polar_cuda_puncture_batch, x, self._parent, self._M, out=out, stream=stream)
+
+    def depuncture_batch(self, x, out=None, stream=0):
+        """[nFrames, blockLength] -> [nFrames, parentBlockLength], punctured positions 0 (an erasure as an LLR)"""
+        return self._run(lib().polar_cuda_depuncture_batch, x, self._M, self._parent, out=out, stream=stream)
+
+    def puncturePacked_batch(self, x, out=None, stream=0):
+        """[nFrames, parentBlockLength/8] uint8 -> [nFrames, blockLength/8] uint8, bits MSB first"""
+        if self._M % 8:
+            raise ValueError("packed puncturing needs a block length that is a multiple of 8")
+        return self._run(lib().polar_cuda_puncture_packed_batch, x, self._parent // 8, self._M // 8, packed=True,
+                         out=out, stream=stream)
+
+    def _one(self, batch_fn, vec, length, dtype=None):
+        a = _np.ascontiguousarray(vec) if dtype is None else _np.ascontiguousarray(vec, dtype)
+        if a.dtype not in (_np.uint8, _np.float32, _np.float64):
+            a = a.astype(_np.float64)   # the binding's overload order: double first (puncturer_python.cc:45-60)
+        if a.ndim != 1:
+            raise RuntimeError("Number of dimensions must be one")
+        if a.size != length:
+            raise RuntimeError("Input vector size mismatch!")
+        return batch_fn(a.reshape(1, -1))[0]
+
+    def puncture(self, vec):
+        return self._one(self.puncture_batch, vec, self._parent)
+
+    def depuncture(self, vec):
+        return self._one(self.depuncture_batch, vec, self._M)
+
+    def puncturePacked(self, vec):
+        return self._one(self.puncturePacked_batch, vec, self._parent // 8, _np.uint8)
 
 
 def test_fg(a, b, bits):

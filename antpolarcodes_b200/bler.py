@@ -71,7 +71,9 @@ def main(argv=None):
     p.add_argument("--crc", type=int, default=16)
     p.add_argument("--construction", default="5G")
     p.add_argument("--design-snr", type=float, default=0.0)
-    p.add_argument("--type", default="char", choices=["char", "float"])
+    p.add_argument("--type", default="char", choices=["char", "float", "mixed"])
+    p.add_argument("--adaptive", action="store_true",
+                   help="Fast-SSC first, the list decoder only on detector failures (the Adaptive* decoders pcsim uses by default)")
     p.add_argument("--ebn0", default="0:4:1")
     p.add_argument("--frames", type=float, default=1e5, help="frames per point (whole job)")
     p.add_argument("--batch", type=int, default=1 << 16)
@@ -88,13 +90,13 @@ def main(argv=None):
     frozen = ap.frozen_bits(a.N, a.K, a.design_snr, a.construction)
     enc = ap.PolarEncoder(a.N, frozen, device=local)
     enc.setErrorDetection(a.crc)
-    dec = ap.PolarDecoder(a.N, a.L, frozen, a.type, device=local)
+    dec = ap.PolarDecoder(a.N, a.L, frozen, a.type, device=local, adaptive=a.adaptive or a.type == "mixed")
     dec.setErrorDetection(a.crc)
     gen = torch.Generator(device=device)
     lo, hi = frame_range(int(a.frames), rank, world)
     for i, eb in enumerate(_parse_sweep(a.ebn0)):
         gen.manual_seed(0xB1E5 + 1000 * i + rank)
-        c = run_point(torch, enc, dec, a.N, a.K, a.crc, eb, hi - lo, a.batch, gen, device, "f32" if a.type == "float" else "i8")
+        c = run_point(torch, enc, dec, a.N, a.K, a.crc, eb, hi - lo, a.batch, gen, device, "i8" if a.type == "char" else "f32")
         tot = reduce_counters(c, device)                   # the one collective of the job
         if rank == 0:
             f = max(tot["frames"], 1)
@@ -103,7 +105,7 @@ def main(argv=None):
             print(json.dumps({"ebn0_db": eb, "N": a.N, "K": a.K, "L": a.L, "crc": a.crc, "type": a.type, "n_gpus": world,
                               "frames": tot["frames"], "bler": bler, "bler_ci95": ci,
                               "ber": tot["bit_errors"] / (f * (a.K - a.crc)), "detected": tot["detected"],
-                              "undetected": tot["undetected"]}), flush=True)
+                              "undetected": tot["undetected"], "adaptive": bool(a.adaptive or a.type == "mixed")}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 

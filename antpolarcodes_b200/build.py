@@ -25,8 +25,9 @@ def build(force=False, verbose=False):
         return OUT
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", OUT]
+          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", OUT + ".tmp"]
     subprocess.check_call(cmd, cwd=CSRC)
+    os.replace(OUT + ".tmp", OUT)  # never leave a half-written library where a snapshot or a loader can see it
     return OUT
 
 

@@ -7,6 +7,7 @@
 #include "encode.cuh"
 #include "fastssc_f32.cuh"
 #include "fastssc_i8.cuh"
+#include "puncture.cuh"
 #include "schedule.h"
 #include "scl_f32.cuh"
 #include "scl_i8.cuh"
@@ -785,6 +786,178 @@ int polar_cuda_schedule_stats(int kind, int N, const uint32_t* frozen, int nFroz
     }
     if (laneOpsPerFrame) *laneOpsPerFrame = st.laneOps;
     return (int)ops.size();
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------- rate matching (Puncturer)
+struct polar_puncturer {
+    int device = 0, blockLength = 0, parent = 0;
+    std::vector<uint32_t> pos;
+    uint32_t* dPos = nullptr;  // blockLength kept positions (padded to a multiple of 8 entries)
+    int32_t* dInv = nullptr;   // parent entries: index into the punctured block or -1
+};
+
+namespace {
+
+int puncturer_positions(int blockLength, const uint32_t* frozen, int nFrozen, std::vector<uint32_t>& pos, int& parent)
+{
+    if (blockLength < 1 || blockLength > (1 << 20)) return fail(POLAR_E_ARG, "bad punctured block length");
+    if (nFrozen < 0 || (nFrozen && !frozen)) return fail(POLAR_E_ARG, "bad frozen set");
+    parent = 1;
+    while (parent < blockLength) parent <<= 1; // round_up_power_of_two (puncturer.cpp:18-28)
+    const int nPunct = parent - blockLength;
+    if (nPunct > nFrozen)
+        return fail(POLAR_E_RANGE, "Number of required puncturing positions exceeds frozen bit positions!");
+    // inverse_set_difference (puncturer.cpp:30-43) of the first nPunct frozen positions (std::set_difference wants
+    // them ascending, which frozen sets are)
+    std::vector<uint8_t> cut(parent, 0);
+    for (int i = 0; i < nPunct; ++i) {
+        if (frozen[i] >= (uint32_t)parent || (i && frozen[i] <= frozen[i - 1]))
+            return fail(POLAR_E_ARG, "frozen indices must be sorted, unique and < parent block length");
+        cut[frozen[i]] = 1;
+    }
+    pos.clear();
+    for (int i = 0; i < parent; ++i)
+        if (!cut[i]) pos.push_back((uint32_t)i);
+    return POLAR_OK;
+}
+
+// run `launch(dIn, dOut)` on device buffers; HOST buffers are staged through temporary device memory
+template <typename F>
+int with_device_buffers(int device, const void* in, size_t inBytes, void* out, size_t outBytes, int mem, cudaStream_t st, F launch)
+{
+    CUDA_TRY(cudaSetDevice(device));
+    if (mem == POLAR_MEM_DEVICE) {
+        launch(in, out);
+        CUDA_TRY(cudaGetLastError());
+        return POLAR_OK;
+    }
+    void *dIn = nullptr, *dOut = nullptr;
+    if (cudaMalloc(&dIn, inBytes) != cudaSuccess || cudaMalloc(&dOut, outBytes) != cudaSuccess) {
+        cudaFree(dIn);
+        cudaGetLastError();
+        return fail(POLAR_E_NOMEM, "staging buffers for the puncturer");
+    }
+    cudaError_t e = cudaMemcpyAsync(dIn, in, inBytes, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) { launch(dIn, dOut); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dOut, outBytes, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(dIn); cudaFree(dOut);
+    if (e != cudaSuccess) return fail(POLAR_E_CUDA, std::string("puncturer: ") + cudaGetErrorString(e));
+    return POLAR_OK;
+}
+
+int copy_grid(long long items) { return (int)std::min<long long>((items + 255) / 256, 148LL * 32); }
+
+} // namespace
+
+extern "C" {
+
+int polar_cuda_puncturer_positions(int blockLength, const uint32_t* frozen, int nFrozen, uint32_t* out)
+{
+    std::vector<uint32_t> pos;
+    int parent = 0;
+    int rc = puncturer_positions(blockLength, frozen, nFrozen, pos, parent);
+    if (rc) return rc;
+    if (out) memcpy(out, pos.data(), pos.size() * sizeof(uint32_t));
+    return (int)pos.size();
+}
+
+int polar_cuda_puncturer_destroy(polar_puncturer_t p)
+{
+    if (!p) return POLAR_OK;
+    cudaSetDevice(p->device);
+    cudaFree(p->dPos); cudaFree(p->dInv);
+    delete p;
+    return POLAR_OK;
+}
+
+int polar_cuda_puncturer_create(int device, int blockLength, const uint32_t* frozen, int nFrozen, polar_puncturer_t* out)
+{
+    if (!out) return fail(POLAR_E_ARG, "out is null");
+    *out = nullptr;
+    std::vector<uint32_t> pos;
+    int parent = 0;
+    int rc = puncturer_positions(blockLength, frozen, nFrozen, pos, parent);
+    if (rc) return rc;
+    if (cudaSetDevice(device) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(POLAR_E_CUDA, "cudaSetDevice failed (no CUDA device?)");
+    }
+    polar_puncturer* p = new polar_puncturer;
+    p->device = device; p->blockLength = blockLength; p->parent = parent; p->pos = pos;
+    std::vector<uint32_t> padded(pos);
+    padded.resize((pos.size() + 7) & ~(size_t)7, 0u);
+    std::vector<int32_t> inv((parent + 3) & ~3, -1);
+    for (size_t j = 0; j < pos.size(); ++j) inv[pos[j]] = (int32_t)j;
+    cudaError_t e;
+    if ((e = cudaMalloc(&p->dPos, padded.size() * sizeof(uint32_t))) != cudaSuccess ||
+        (e = cudaMalloc(&p->dInv, inv.size() * sizeof(int32_t))) != cudaSuccess ||
+        (e = cudaMemcpy(p->dPos, padded.data(), padded.size() * sizeof(uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(p->dInv, inv.data(), inv.size() * sizeof(int32_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
+        polar_cuda_puncturer_destroy(p);
+        return fail(POLAR_E_CUDA, std::string("puncturer tables: ") + cudaGetErrorString(e));
+    }
+    *out = p;
+    return POLAR_OK;
+}
+
+int polar_cuda_puncturer_parent_length(polar_puncturer_t p) { return p ? p->parent : fail(POLAR_E_ARG, "null puncturer"); }
+
+int polar_cuda_puncture_batch(polar_puncturer_t p, const void* in, int elemBytes, int mem, size_t nFrames, void* out, void* stream)
+{
+    if (!p) return fail(POLAR_E_ARG, "null puncturer");
+    if (elemBytes != 1 && elemBytes != 4 && elemBytes != 8) return fail(POLAR_E_ARG, "element size must be 1, 4 or 8 bytes");
+    if (nFrames == 0) return POLAR_OK;
+    if (!in || !out) return fail(POLAR_E_ARG, "null buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long total = (long long)nFrames * p->blockLength;
+    return with_device_buffers(p->device, in, nFrames * (size_t)p->parent * elemBytes, out, (size_t)total * elemBytes, mem, st,
+                               [&](const void* dIn, void* dOut) {
+        const int grid = copy_grid(total);
+        if (elemBytes == 1)
+            puncture_kernel<uint8_t><<<grid, 256, 0, st>>>((const uint8_t*)dIn, p->dPos, p->blockLength, p->parent, (long long)nFrames, (uint8_t*)dOut);
+        else if (elemBytes == 4)
+            puncture_kernel<uint32_t><<<grid, 256, 0, st>>>((const uint32_t*)dIn, p->dPos, p->blockLength, p->parent, (long long)nFrames, (uint32_t*)dOut);
+        else
+            puncture_kernel<unsigned long long><<<grid, 256, 0, st>>>((const unsigned long long*)dIn, p->dPos, p->blockLength, p->parent, (long long)nFrames, (unsigned long long*)dOut);
+    });
+}
+
+int polar_cuda_depuncture_batch(polar_puncturer_t p, const void* in, int elemBytes, int mem, size_t nFrames, void* out, void* stream)
+{
+    if (!p) return fail(POLAR_E_ARG, "null puncturer");
+    if (elemBytes != 1 && elemBytes != 4 && elemBytes != 8) return fail(POLAR_E_ARG, "element size must be 1, 4 or 8 bytes");
+    if (nFrames == 0) return POLAR_OK;
+    if (!in || !out) return fail(POLAR_E_ARG, "null buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long total = (long long)nFrames * p->parent;
+    return with_device_buffers(p->device, in, nFrames * (size_t)p->blockLength * elemBytes, out, (size_t)total * elemBytes, mem, st,
+                               [&](const void* dIn, void* dOut) {
+        if (elemBytes == 1 && p->parent % 4 == 0 && ((uintptr_t)dOut & 3) == 0)
+            depuncture_i8x4_kernel<<<copy_grid(total / 4), 256, 0, st>>>((const int8_t*)dIn, p->dInv, p->blockLength, p->parent, (long long)nFrames, (uint32_t*)dOut);
+        else if (elemBytes == 1)
+            depuncture_kernel<uint8_t><<<copy_grid(total), 256, 0, st>>>((const uint8_t*)dIn, p->dInv, p->blockLength, p->parent, (long long)nFrames, (uint8_t*)dOut);
+        else if (elemBytes == 4)
+            depuncture_kernel<uint32_t><<<copy_grid(total), 256, 0, st>>>((const uint32_t*)dIn, p->dInv, p->blockLength, p->parent, (long long)nFrames, (uint32_t*)dOut);
+        else
+            depuncture_kernel<unsigned long long><<<copy_grid(total), 256, 0, st>>>((const unsigned long long*)dIn, p->dInv, p->blockLength, p->parent, (long long)nFrames, (unsigned long long*)dOut);
+    });
+}
+
+int polar_cuda_puncture_packed_batch(polar_puncturer_t p, const uint8_t* in, int mem, size_t nFrames, uint8_t* out, void* stream)
+{
+    if (!p) return fail(POLAR_E_ARG, "null puncturer");
+    if (p->blockLength % 8 || p->parent % 8) return fail(POLAR_E_ARG, "packed puncturing needs block lengths that are multiples of 8");
+    if (nFrames == 0) return POLAR_OK;
+    if (!in || !out) return fail(POLAR_E_ARG, "null buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long total = (long long)nFrames * (p->blockLength / 8);
+    return with_device_buffers(p->device, in, nFrames * (size_t)(p->parent / 8), out, (size_t)total, mem, st,
+                               [&](const void* dIn, void* dOut) {
+        puncture_packed_kernel<<<copy_grid(total), 256, 0, st>>>((const uint8_t*)dIn, p->dPos, p->blockLength, p->parent, (long long)nFrames, (uint8_t*)dOut);
+    });
 }
 
 } // extern "C"

@@ -46,7 +46,8 @@ enum polar_error {
     POLAR_E_ARG = -1,      /* invalid argument (std::invalid_argument in the C++ layer) */
     POLAR_E_UNSUPPORTED = -2,
     POLAR_E_CUDA = -3,     /* CUDA runtime failure (std::runtime_error) */
-    POLAR_E_NOMEM = -4
+    POLAR_E_NOMEM = -4,
+    POLAR_E_RANGE = -5     /* std::out_of_range in the C++ layer (Puncturer, puncturer.cpp:51-54) */
 };
 
 const char* polar_cuda_last_error(void);
@@ -87,6 +88,28 @@ int polar_cuda_crc_check(int crcBits, const uint8_t* data, int bytes); /* 1 = pa
 /* Construction::frozen_bits: type "BB" (Bhattacharyya), "BE" (beta expansion) or "5G".
  * Writes N-K sorted indices to out; returns the count or a negative error. */
 int polar_cuda_frozen_bits(int N, int K, float designSnr, const char* type, uint32_t* out);
+
+/* Rate matching either side of the coder: PolarCode::Puncturer (include/polarcode/puncturer.h:29-101,
+ * src/polarcode/puncturer.cpp:45-85).  parentBlockLength = next power of two >= blockLength; the first
+ * (parent - blockLength) entries of the frozen set are punctured, every other position is kept in ascending order.
+ *   positions : pure host; writes the blockLength kept positions (blockOutputPositions()), returns their count,
+ *               POLAR_E_RANGE when more positions would have to be punctured than there are frozen bits
+ *   puncture  : out[f][j] = in[f][pos[j]]                        in: nFrames x parent, out: nFrames x blockLength
+ *   depuncture: out[f][pos[j]] = in[f][j], every other entry 0   in: nFrames x blockLength, out: nFrames x parent
+ *   puncture_packed: the same gather on MSB-first packed bits    in: nFrames x parent/8, out: nFrames x blockLength/8
+ * elemBytes = 1 (int8 / uint8), 4 (float) or 8 (double), the three types the pypolar binding instantiates
+ * (puncturer_python.cc:45-145). */
+typedef struct polar_puncturer* polar_puncturer_t;
+int polar_cuda_puncturer_positions(int blockLength, const uint32_t* frozen, int nFrozen, uint32_t* out);
+int polar_cuda_puncturer_create(int device, int blockLength, const uint32_t* frozen, int nFrozen, polar_puncturer_t* out);
+int polar_cuda_puncturer_destroy(polar_puncturer_t p);
+int polar_cuda_puncturer_parent_length(polar_puncturer_t p);
+int polar_cuda_puncture_batch(polar_puncturer_t p, const void* in, int elemBytes, int mem, size_t nFrames, void* out,
+                              void* stream);
+int polar_cuda_depuncture_batch(polar_puncturer_t p, const void* in, int elemBytes, int mem, size_t nFrames, void* out,
+                                void* stream);
+int polar_cuda_puncture_packed_batch(polar_puncturer_t p, const uint8_t* in, int mem, size_t nFrames, uint8_t* out,
+                                     void* stream);
 
 /* Introspection for tests, bench and the roofline. */
 struct polar_code_info {

@@ -30,6 +30,12 @@ int8_t oracle_f_i8(int8_t a, int8_t b);
 int8_t oracle_g_i8(int8_t a, int8_t b, int8_t bit);
 int8_t oracle_rep_sum_i8(const int8_t* x, int n);
 
+/* Rate matching: Puncturer (puncturer.cpp:45-85, puncturer.h:71-100).  pos = kept positions of the parent block. */
+int oracle_puncturer_positions(int blockLength, const uint32_t* frozen, int nFrozen, uint32_t* pos);
+void oracle_puncture(const uint32_t* pos, int nPos, int elem, const uint8_t* in, uint8_t* out);
+void oracle_depuncture(const uint32_t* pos, int nPos, int parent, int elem, const uint8_t* in, uint8_t* out);
+void oracle_puncture_packed(const uint32_t* pos, int nPos, const uint8_t* in, uint8_t* out);
+
 /* Encoder (butterfly_fip_packed.cpp:45-70).  info: nFrames x K/8 (CRC written in place),
  * code: nFrames x N/8, both MSB-first packed. */
 int oracle_encode(int N, const uint32_t* frozen, int nFrozen, int systematic, int crcBits,

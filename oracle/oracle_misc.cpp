@@ -126,3 +126,50 @@ extern "C" int oracle_encode(int N, const uint32_t* frozen, int nFrozen, int sys
     }
     return 0;
 }
+
+// ---------------------------------------------------------------- rate matching (TEST INFRASTRUCTURE, like the rest)
+// Puncturer (puncturer.cpp:45-61): parent length = next power of two; the first (parent - blockLength) frozen
+// positions are punctured, every other position of the parent code word is kept, in ascending order.
+// Returns the number of kept positions written to `pos` (= blockLength) or -1 (std::out_of_range upstream).
+extern "C" int oracle_puncturer_positions(int blockLength, const uint32_t* frozen, int nFrozen, uint32_t* pos)
+{
+    uint32_t parent = (uint32_t)blockLength - 1; // round_up_power_of_two, puncturer.cpp:18-28
+    parent |= parent >> 1; parent |= parent >> 2; parent |= parent >> 4; parent |= parent >> 8; parent |= parent >> 16;
+    ++parent;
+    const int nPunct = (int)parent - blockLength;
+    if (nPunct > nFrozen) return -1;
+    int n = 0, fi = 0;
+    // inverse_set_difference (puncturer.cpp:30-43): 0..parent-1 minus the SORTED prefix of the frozen set
+    for (uint32_t i = 0; i < parent; ++i) {
+        while (fi < nPunct && frozen[fi] < i) ++fi;
+        if (fi < nPunct && frozen[fi] == i) continue;
+        pos[n++] = i;
+    }
+    return n;
+}
+
+// puncture<T> (puncturer.h:71-79): out[j] = in[pos[j]]; elem = bytes per element
+extern "C" void oracle_puncture(const uint32_t* pos, int nPos, int elem, const uint8_t* in, uint8_t* out)
+{
+    for (int j = 0; j < nPos; ++j) std::memcpy(out + (size_t)j * elem, in + (size_t)pos[j] * elem, elem);
+}
+
+// depuncture<T> (puncturer.h:93-100): zero fill the parent block, then out[pos[j]] = in[j]
+extern "C" void oracle_depuncture(const uint32_t* pos, int nPos, int parent, int elem, const uint8_t* in, uint8_t* out)
+{
+    std::memset(out, 0, (size_t)parent * elem);
+    for (int j = 0; j < nPos; ++j) std::memcpy(out + (size_t)pos[j] * elem, in + (size_t)j * elem, elem);
+}
+
+// puncturePacked (puncturer.cpp:65-85): MSB-first bit j of the output = MSB-first bit pos[j] of the input
+extern "C" void oracle_puncture_packed(const uint32_t* pos, int nPos, const uint8_t* in, uint8_t* out)
+{
+    for (int b = 0; b < nPos / 8; ++b) {
+        uint8_t v = 0;
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t p = pos[8 * b + i];
+            v |= (uint8_t)(((in[p / 8] >> (7 - p % 8)) & 1) << (7 - i));
+        }
+        out[b] = v;
+    }
+}

@@ -25,6 +25,7 @@
 #include <polarcode/decoding/scl_fip_char.h>
 #include <polarcode/encoding/butterfly_fip_packed.h>
 #include <polarcode/errordetection/errordetector.h>
+#include <polarcode/puncturer.h>
 
 #include <atomic>
 #include <chrono>
@@ -198,6 +199,34 @@ void polar_ref_quantize(const float* llr, int8_t* out, int N)
     CharContainer c(N);
     c.insertLlr(llr);
     c.getSoftBits(out);
+}
+
+// PolarCode::Puncturer (src/polarcode/puncturer.cpp:45-85, include/polarcode/puncturer.h:71-100).
+// mode 0: positions -> out (uint32, returns count); 1: puncture<T>; 2: depuncture<T>; 3: puncturePacked.  -1 = threw.
+int polar_ref_puncturer(int blockLength, const uint32_t* frozen, int nFrozen, int mode, int elem, const void* in, void* out)
+{
+    try {
+        Puncturer p(blockLength, std::vector<unsigned>(frozen, frozen + nFrozen));
+        if (mode == 0) {
+            std::vector<unsigned> pos = p.blockOutputPositions();
+            for (size_t i = 0; i < pos.size(); ++i) static_cast<uint32_t*>(out)[i] = pos[i];
+            return (int)pos.size();
+        }
+        if (mode == 3) { p.puncturePacked(static_cast<unsigned char*>(out), static_cast<const unsigned char*>(in)); return 0; }
+        if (elem == 1) {
+            if (mode == 1) p.puncture(static_cast<uint8_t*>(out), static_cast<const uint8_t*>(in));
+            else p.depuncture(static_cast<uint8_t*>(out), static_cast<const uint8_t*>(in));
+        } else if (elem == 4) {
+            if (mode == 1) p.puncture(static_cast<float*>(out), static_cast<const float*>(in));
+            else p.depuncture(static_cast<float*>(out), static_cast<const float*>(in));
+        } else {
+            if (mode == 1) p.puncture(static_cast<double*>(out), static_cast<const double*>(in));
+            else p.depuncture(static_cast<double*>(out), static_cast<const double*>(in));
+        }
+        return (int)p.parentBlockLength();
+    } catch (...) {
+        return -1;
+    }
 }
 
 int polar_ref_hw_threads() { return (int)std::thread::hardware_concurrency(); }

@@ -277,3 +277,65 @@ def stress_llrs(N, nFrames, seed=2, scale=40.0):
     rng = np.random.default_rng(seed)
     y = scale * rng.standard_normal(size=(nFrames, N))
     return np.clip(np.rint(y), -128, 127).astype(np.int8)
+
+
+# ---------------------------------------------------------------- rate matching (Puncturer)
+def _punct_api():
+    o = oracle()
+    o.oracle_puncturer_positions.argtypes = [_i, _vp, _i, _vp]
+    o.oracle_puncture.argtypes = [_vp, _i, _i, _vp, _vp]
+    o.oracle_depuncture.argtypes = [_vp, _i, _i, _i, _vp, _vp]
+    o.oracle_puncture_packed.argtypes = [_vp, _i, _vp, _vp]
+    return o
+
+
+def oracle_puncturer_positions(M, frozen):
+    _punct_api()
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    pos = np.zeros(2 * M + 8, np.uint32)
+    n = oracle().oracle_puncturer_positions(M, _ptr(frozen), len(frozen), _ptr(pos))
+    return None if n < 0 else pos[:n].copy()
+
+
+def oracle_puncture(pos, x):
+    x = np.ascontiguousarray(x)
+    out = np.zeros((x.shape[0], len(pos)), x.dtype)
+    for r in range(x.shape[0]):
+        _punct_api().oracle_puncture(_ptr(pos), len(pos), x.dtype.itemsize, ctypes.c_void_p(x[r].ctypes.data), ctypes.c_void_p(out[r].ctypes.data))
+    return out
+
+
+def oracle_depuncture(pos, parent, x):
+    x = np.ascontiguousarray(x)
+    out = np.full((x.shape[0], parent), 77, x.dtype)
+    for r in range(x.shape[0]):
+        _punct_api().oracle_depuncture(_ptr(pos), len(pos), parent, x.dtype.itemsize, ctypes.c_void_p(x[r].ctypes.data), ctypes.c_void_p(out[r].ctypes.data))
+    return out
+
+
+def oracle_puncture_packed(pos, x):
+    x = np.ascontiguousarray(x, np.uint8)
+    out = np.zeros((x.shape[0], len(pos) // 8), np.uint8)
+    for r in range(x.shape[0]):
+        _punct_api().oracle_puncture_packed(_ptr(pos), len(pos), ctypes.c_void_p(x[r].ctypes.data), ctypes.c_void_p(out[r].ctypes.data))
+    return out
+
+
+def ref_puncturer(M, frozen, mode, x=None, parent=None):
+    """The reference's Puncturer object: mode 0 positions, 1 puncture, 2 depuncture, 3 puncturePacked (row by row)."""
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    fn = ref().polar_ref_puncturer
+    fn.restype = ctypes.c_int
+    fn.argtypes = [_i, _vp, _i, _i, _i, _vp, _vp]
+    if mode == 0:
+        pos = np.zeros(2 * M + 8, np.uint32)
+        n = fn(M, _ptr(frozen), len(frozen), 0, 0, None, _ptr(pos))
+        return None if n < 0 else pos[:n].copy()
+    x = np.ascontiguousarray(x)
+    cols = {1: M, 2: parent, 3: M // 8}[mode]
+    out = np.zeros((x.shape[0], cols), x.dtype)
+    for r in range(x.shape[0]):
+        rc = fn(M, _ptr(frozen), len(frozen), mode, x.dtype.itemsize, ctypes.c_void_p(x[r].ctypes.data),
+                ctypes.c_void_p(out[r].ctypes.data))
+        assert rc >= 0
+    return out

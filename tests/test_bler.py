@@ -28,3 +28,19 @@ def test_bler_sweep(gpu, capsys, dtype):
     for p in pts:
         assert p["undetected"] <= p["bler"] * p["frames"] + 1e-9
         assert p["detected"] + p["undetected"] >= p["bler"] * p["frames"] - 1e-9
+
+
+@pytest.mark.gpu
+def test_bler_sweep_adaptive_equals_list_decoder(gpu, capsys):
+    """Same seeds, same frames: wherever Fast-SSC passes the CRC the adaptive decoder keeps its answer, so its block
+    error rate can only differ from the list decoder's through undetected Fast-SSC errors (rare with CRC16)."""
+    from antpolarcodes_b200 import bler
+    common = ["--N", "512", "--K", "256", "--L", "8", "--crc", "16", "--construction", "BB", "--ebn0", "1,3",
+              "--frames", "20000", "--batch", "8192"]
+    bler.main(common)
+    plain = [json.loads(l) for l in capsys.readouterr().out.strip().splitlines()]
+    bler.main(common + ["--adaptive"])
+    ada = [json.loads(l) for l in capsys.readouterr().out.strip().splitlines()]
+    for p, a in zip(plain, ada):
+        assert a["adaptive"] and a["frames"] == p["frames"]
+        assert abs(a["bler"] - p["bler"]) <= 3 * p["bler_ci95"] + 1e-3, (p, a)
