@@ -12,6 +12,7 @@
 //                                          next to AdaptiveChar / AdaptiveFloat / AdaptiveMixed (adaptive_char.h:26)
 //   PolarCode::Decoding::makeCudaDecoder   like makeDecoder         (decoder.cpp:50-87)
 //   PolarCode::Encoding::ButterflyCudaPacked next to ButterflyFipPacked (butterfly_fip_packed.h:25)
+//   PolarCode::CudaPuncturer               a Puncturer (puncturer.h:29) with batched device methods
 //
 // The one-frame virtual API (decode_vector / decode / encode_vector / encode) is served by a batch of one --
 // correct, and as slow as a kernel launch; throughput comes from decode_batch / encode_batch, the entry points
@@ -24,6 +25,7 @@
 #include <polarcode/encoding/encoder.h>
 #include <polarcode/errordetection/crc8.h>
 #include <polarcode/errordetection/errordetector.h>
+#include <polarcode/puncturer.h>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -34,8 +36,9 @@ namespace CudaDetail {
 
 inline void check(int rc)
 {
-    if (rc == POLAR_OK) return;
+    if (rc >= POLAR_OK) return;
     const std::string msg = polar_cuda_last_error();
+    if (rc == POLAR_E_RANGE) throw std::out_of_range(msg); // Puncturer's constructor (puncturer.cpp:51-54)
     if (rc == POLAR_E_ARG) throw std::invalid_argument(msg); // the reference's convention for bad parameters
     throw std::runtime_error(msg);
 }
@@ -272,4 +275,44 @@ public:
 };
 
 } // namespace Encoding
+
+// Rate matching: the base class keeps the one-vector puncture<T> / depuncture<T> / puncturePacked (host loops over
+// mOutputPositions); the *_batch methods run the same index copies over nFrames rows on the device.
+class CudaPuncturer : public Puncturer
+{
+    polar_puncturer_t mHandle = nullptr;
+
+public:
+    CudaPuncturer(const size_t blockLength, const std::vector<unsigned> frozenBitPositions, int device = 0)
+        : Puncturer(blockLength, frozenBitPositions) // throws std::out_of_range like the reference
+    {
+        CudaDetail::check(polar_cuda_puncturer_create(device, (int)blockLength, frozenBitPositions.data(),
+                                                      (int)frozenBitPositions.size(), &mHandle));
+    }
+    ~CudaPuncturer() override { polar_cuda_puncturer_destroy(mHandle); }
+    CudaPuncturer(const CudaPuncturer&) = delete;
+    CudaPuncturer& operator=(const CudaPuncturer&) = delete;
+
+    // nFrames x parentBlockLength() elements in, nFrames x blockLength() out
+    template <typename T>
+    void puncture_batch(T* pOutput, const T* pInput, size_t nFrames, bool deviceBuffers = false, void* stream = nullptr)
+    {
+        CudaDetail::check(polar_cuda_puncture_batch(mHandle, pInput, (int)sizeof(T), deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
+                                                    nFrames, pOutput, stream));
+    }
+    // nFrames x blockLength() in, nFrames x parentBlockLength() out, punctured positions 0
+    template <typename T>
+    void depuncture_batch(T* pOutput, const T* pInput, size_t nFrames, bool deviceBuffers = false, void* stream = nullptr)
+    {
+        CudaDetail::check(polar_cuda_depuncture_batch(mHandle, pInput, (int)sizeof(T), deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
+                                                      nFrames, pOutput, stream));
+    }
+    void puncturePacked_batch(unsigned char* pOutput, const unsigned char* pInput, size_t nFrames, bool deviceBuffers = false,
+                              void* stream = nullptr)
+    {
+        CudaDetail::check(polar_cuda_puncture_packed_batch(mHandle, pInput, deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
+                                                           nFrames, pOutput, stream));
+    }
+};
+
 } // namespace PolarCode

@@ -229,6 +229,41 @@ static void runAdaptive(int flavour, int N, int K, int L, int crc, int frames, c
                 flavour == 0 ? "char" : flavour == 1 ? "float" : "mixed", N, K, L, crc, frames, redone, okCount);
 }
 
+// Puncturer (puncturer.h:29-101) vs CudaPuncturer: same positions, the batched device copies equal the base-class loops.
+static void runPuncturer(int M, int N, int K, int frames)
+{
+    const std::vector<unsigned> frozen = Construction::frozen_bits(N, K, 0.0f, "BB");
+    Puncturer ref(M, frozen);
+    CudaPuncturer gpu(M, frozen);
+    CHECK(gpu.blockLength() == ref.blockLength() && gpu.parentBlockLength() == ref.parentBlockLength() &&
+              gpu.blockOutputPositions() == ref.blockOutputPositions(), "puncturer geometry M=%d", M);
+    std::mt19937 rng(M);
+    std::vector<float> x((size_t)frames * N), px((size_t)frames * M), wantP(px.size()), dx(x.size()), wantD(x.size());
+    for (auto& v : x) v = (float)(int)(rng() % 255) - 127.0f;
+    gpu.puncture_batch(px.data(), x.data(), frames);
+    for (int f = 0; f < frames; ++f) ref.puncture(&wantP[(size_t)f * M], &x[(size_t)f * N]);
+    CHECK(px == wantP, "puncture_batch<float> M=%d", M);
+    gpu.depuncture_batch(dx.data(), px.data(), frames);
+    for (int f = 0; f < frames; ++f) ref.depuncture(&wantD[(size_t)f * N], &wantP[(size_t)f * M]);
+    CHECK(dx == wantD, "depuncture_batch<float> M=%d", M);
+    std::vector<char> c((size_t)frames * M), dc((size_t)frames * N), wantC(dc.size());
+    for (auto& v : c) v = (char)(rng() & 0xFF);
+    gpu.depuncture_batch(dc.data(), c.data(), frames);
+    for (int f = 0; f < frames; ++f) ref.depuncture(&wantC[(size_t)f * N], &c[(size_t)f * M]);
+    CHECK(dc == wantC, "depuncture_batch<char> M=%d", M);
+    if (M % 8 == 0) {
+        std::vector<unsigned char> b((size_t)frames * N / 8), pb((size_t)frames * M / 8), wantB(pb.size());
+        for (auto& v : b) v = (unsigned char)(rng() & 0xFF);
+        gpu.puncturePacked_batch(pb.data(), b.data(), frames);
+        for (int f = 0; f < frames; ++f) ref.puncturePacked(&wantB[(size_t)f * M / 8], &b[(size_t)f * N / 8]);
+        CHECK(pb == wantB, "puncturePacked_batch M=%d", M);
+    }
+    bool threw = false;
+    try { CudaPuncturer bad(N / 2 + 1, std::vector<unsigned>(frozen.begin(), frozen.begin() + 3)); } catch (const std::out_of_range&) { threw = true; }
+    CHECK(threw, "too many punctured positions must throw std::out_of_range");
+    std::printf("puncturer M=%d parent=%d: %d frames\n", M, N, frames);
+}
+
 int main(int argc, char** argv)
 {
     if (polar_cuda_device_count() < 1) {
@@ -247,6 +282,8 @@ int main(int argc, char** argv)
         runCase(c, true);
         runCase(c, false);
     }
+    runPuncturer(1000, 1024, 512, 64);
+    runPuncturer(203, 256, 100, 33);
     runAdaptive(0, 1024, 512, 8, 16, 96, "5G", 1.5f);
     if (!quick) {
         runAdaptive(1, 1024, 512, 8, 16, 32, "5G", 1.5f);
