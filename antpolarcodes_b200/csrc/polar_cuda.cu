@@ -585,18 +585,52 @@ static int adaptive_decode_batch(polar_code* c, const void* llr, int llrType, in
         }
         return adaptive_on_device(c, llr, llrType, nFrames, info_out, okDev, st);
     }
-    // HOST buffers: staged through the device in chunks of about 64 MB of LLRs
-    const size_t chunk = std::min(nFrames, std::max<size_t>(1, ((size_t)env_int("POLAR_CUDA_CHUNK_MB", 64) << 20) / ((size_t)c->N * eb)));
-    int rc = ensure_staging(c, chunk, eb);
+    // HOST buffers: chunks of about 128 MB of LLRs (large enough that the failed frames of a chunk still fill the list
+    // kernel's grid), double buffered over two internal streams.  The H2D copy of chunk k+1 is queued before chunk k is
+    // decoded, so it runs under both kernels of chunk k; the kernels of consecutive chunks are chained by events
+    // (they share the compaction scratch and the decoders' spill buffers).
+    size_t chunk = std::max<size_t>(1, ((size_t)env_int("POLAR_CUDA_ADAPTIVE_CHUNK_MB", 128) << 20) / ((size_t)c->N * eb));
+    if (const char* v = getenv("POLAR_CUDA_CHUNK_MB")) // the knob of the plain decoders overrides, when set
+        if (*v) chunk = std::max<size_t>(1, ((size_t)atoi(v) << 20) / ((size_t)c->N * eb));
+    if (chunk * 2 > nFrames || !env_int("POLAR_CUDA_PIPELINE", 1)) chunk = nFrames;
+    const size_t nChunks = (nFrames + chunk - 1) / chunk;
+    const int depth = nChunks > 1 ? 2 : 1;
+    int rc = ensure_staging(c, chunk * depth, eb);
     if (rc) return rc;
+    if (depth == 2 && !c->pipe[0]) {
+        for (int i = 0; i < 2; ++i) {
+            CUDA_TRY(cudaStreamCreateWithFlags(&c->pipe[i], cudaStreamNonBlocking));
+            CUDA_TRY(cudaEventCreateWithFlags(&c->pipeDone[i], cudaEventDisableTiming));
+        }
+    }
+    CUDA_TRY(cudaStreamSynchronize(st));
     const uint8_t* src = static_cast<const uint8_t*>(llr);
-    for (size_t f0 = 0; f0 < nFrames; f0 += chunk) {
-        const size_t n = std::min(chunk, nFrames - f0);
-        CUDA_TRY(cudaMemcpyAsync(c->dLlr, src + f0 * c->N * eb, n * c->N * (size_t)eb, cudaMemcpyHostToDevice, st));
-        rc = adaptive_on_device(c, c->dLlr, llrType, n, c->dOut, c->dOk, st);
+    auto stageIn = [&](size_t k) -> cudaError_t {
+        const size_t f0 = k * chunk, n = std::min(chunk, nFrames - f0);
+        const int h = depth == 2 ? (int)(k & 1) : 0;
+        uint8_t* dL = static_cast<uint8_t*>(c->dLlr) + (size_t)h * chunk * c->N * eb;
+        return cudaMemcpyAsync(dL, src + f0 * c->N * eb, n * c->N * (size_t)eb, cudaMemcpyHostToDevice, depth == 2 ? c->pipe[h] : st);
+    };
+    CUDA_TRY(stageIn(0));
+    for (size_t k = 0; k < nChunks; ++k) {
+        const size_t f0 = k * chunk, n = std::min(chunk, nFrames - f0);
+        const int h = depth == 2 ? (int)(k & 1) : 0;
+        cudaStream_t s = depth == 2 ? c->pipe[h] : st;
+        uint8_t* dL = static_cast<uint8_t*>(c->dLlr) + (size_t)h * chunk * c->N * eb;
+        uint8_t* dO = c->dOut + (size_t)h * chunk * c->kb;
+        uint8_t* dK = c->dOk + (size_t)h * chunk;
+        if (k + 1 < nChunks) CUDA_TRY(stageIn(k + 1)); // behind the D2H of chunk k-1 on that stream
+        if (depth == 2 && k > 0) CUDA_TRY(cudaStreamWaitEvent(s, c->pipeDone[h ^ 1], 0));
+        rc = adaptive_on_device(c, dL, llrType, n, dO, dK, s);
         if (rc) return rc;
-        CUDA_TRY(cudaMemcpyAsync(info_out + f0 * c->kb, c->dOut, n * (size_t)c->kb, cudaMemcpyDeviceToHost, st));
-        if (ok_out) CUDA_TRY(cudaMemcpyAsync(ok_out + f0, c->dOk, n, cudaMemcpyDeviceToHost, st));
+        if (depth == 2) CUDA_TRY(cudaEventRecord(c->pipeDone[h], s));
+        CUDA_TRY(cudaMemcpyAsync(info_out + f0 * c->kb, dO, n * (size_t)c->kb, cudaMemcpyDeviceToHost, s));
+        if (ok_out) CUDA_TRY(cudaMemcpyAsync(ok_out + f0, dK, n, cudaMemcpyDeviceToHost, s));
+    }
+    if (depth == 2) {
+        CUDA_TRY(cudaStreamSynchronize(c->pipe[0]));
+        CUDA_TRY(cudaStreamSynchronize(c->pipe[1]));
+    } else {
         CUDA_TRY(cudaStreamSynchronize(st));
     }
     return POLAR_OK;

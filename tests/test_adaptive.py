@@ -146,11 +146,25 @@ def test_adaptive_all_fail_and_none_fail(gpu):
     assert redone >= 290 and np.array_equal(out, eo) and np.array_equal(ok, ek)
     clean = awgn_llrs(N, fz, 5000, 12.0, crc, seed=3)[0]
     before = dec.fallbacks()
-    os.environ["POLAR_CUDA_CHUNK_MB"] = "1"   # 4096 frames per chunk: two chunks
-    try:
-        out, ok = dec.decode_batch(clean)
-    finally:
-        del os.environ["POLAR_CUDA_CHUNK_MB"]
+    out, ok = dec.decode_batch(clean)
     eo, ek, redone = oracle_decode_adaptive(KIND_ADAPTIVE_I8, N, fz, clean, L, 1, crc)
     assert redone == 0 and dec.fallbacks() == before and ok.all()
+    assert np.array_equal(out, eo) and np.array_equal(ok, ek)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", [KIND_ADAPTIVE_I8, KIND_ADAPTIVE_MIXED])
+def test_adaptive_host_pipeline(gpu, kind):
+    """HOST-buffer calls split into double-buffered chunks (a ragged last one) give what one device call gives."""
+    N, K, L, crc, n = 256, 128, 4, 16, 13001
+    fz = _frozen(N, K, "BB")
+    llr = adaptive_llrs(kind, N, fz, n, crc, 1.5, seed=21)
+    dec = _decoder(kind, N, L, fz, crc)
+    os.environ["POLAR_CUDA_CHUNK_MB"] = "1"   # 4096 int8 / 1024 float frames per chunk
+    try:
+        out, ok = dec.decode_batch(llr)
+    finally:
+        del os.environ["POLAR_CUDA_CHUNK_MB"]
+    eo, ek, redone = oracle_decode_adaptive(kind, N, fz, llr, L, 1, crc)
+    assert 0 < redone < n and dec.fallbacks() == redone
     assert np.array_equal(out, eo) and np.array_equal(ok, ek)
