@@ -26,7 +26,7 @@ EXPORTS = [
     "polar_cuda_code_destroy", "polar_cuda_decode_batch", "polar_cuda_encode_batch",
     "polar_cuda_crc_generate", "polar_cuda_crc_check", "polar_cuda_frozen_bits", "polar_cuda_code_info",
     "polar_cuda_code_schedule", "polar_cuda_code_launches", "polar_cuda_test_fg", "polar_cuda_schedule_stats",
-    "polar_cuda_code_fallbacks", "polar_cuda_puncturer_positions", "polar_cuda_puncturer_create",
+    "polar_cuda_code_fallbacks", "polar_cuda_schedule_cache_stats", "polar_cuda_puncturer_positions", "polar_cuda_puncturer_create",
     "polar_cuda_puncturer_destroy", "polar_cuda_puncturer_parent_length", "polar_cuda_puncture_batch",
     "polar_cuda_depuncture_batch", "polar_cuda_puncture_packed_batch",
 ]
@@ -475,6 +475,13 @@ class Puncturer:
 
     def puncturePacked(self, vec):
         return self._one(self.puncturePacked_batch, vec, self._parent // 8, _np.uint8)
+
+
+def schedule_cache_stats():
+    """(entries, hits, misses) of the per-process cache of compiled node programs."""
+    h, m = _c.c_long(0), _c.c_long(0)
+    n = lib().polar_cuda_schedule_cache_stats(_c.byref(h), _c.byref(m))
+    return n, h.value, m.value
 
 
 def test_fg(a, b, bits):

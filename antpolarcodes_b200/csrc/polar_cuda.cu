@@ -15,6 +15,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <list>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -38,6 +40,41 @@ int fail(int code, const std::string& msg)
     } while (0)
 
 typedef void (*DecodeKernel)(const DecodeParams, const Schedule);
+
+// Compiled-schedule cache: decoder objects are rebuilt whenever setSystematic / setErrorDetection
+// change, one per host thread and per sweep point -- the node program only depends on (tree flavour, N, frozen set,
+// list size), so it is compiled once.  Small LRU, most recent first; entries are compared on the full frozen set.
+struct CachedSchedule {
+    int tk, N, L;
+    std::vector<uint32_t> frozen, ops;
+    ScheduleStats stats;
+};
+std::mutex g_schedMu;
+std::list<CachedSchedule> g_schedCache;
+long g_schedHits = 0, g_schedMisses = 0;
+constexpr size_t kSchedCacheEntries = 64;
+
+bool compile_schedule_cached(TreeKind tk, int N, const std::vector<uint32_t>& frozen, int L, std::vector<uint32_t>& ops,
+                             ScheduleStats& stats, const char** err)
+{
+    {
+        std::lock_guard<std::mutex> lk(g_schedMu);
+        for (auto it = g_schedCache.begin(); it != g_schedCache.end(); ++it)
+            if (it->tk == (int)tk && it->N == N && it->L == L && it->frozen == frozen) {
+                ops = it->ops;
+                stats = it->stats;
+                g_schedCache.splice(g_schedCache.begin(), g_schedCache, it);
+                ++g_schedHits;
+                return true;
+            }
+    }
+    if (!compile_schedule(tk, N, frozen, L, ops, stats, err)) return false;
+    std::lock_guard<std::mutex> lk(g_schedMu);
+    ++g_schedMisses;
+    g_schedCache.push_front(CachedSchedule{ (int)tk, N, L, frozen, ops, stats });
+    if (g_schedCache.size() > kSchedCacheEntries) g_schedCache.pop_back();
+    return true;
+}
 
 } // namespace
 
@@ -375,7 +412,7 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
         if (kind != POLAR_KIND_ENC) {
             TreeKind tk = kind == POLAR_KIND_SCL_I8 ? TREE_SCL_I8 : kind == POLAR_KIND_SCL_F32 ? TREE_SCL_F32
                           : kind == POLAR_KIND_FASTSSC_F32 ? TREE_FASTSSC_F32 : TREE_FASTSSC_I8;
-            if (!compile_schedule(tk, N, c->frozen, c->L, c->ops, c->stats, &err)) { rc = fail(POLAR_E_ARG, err); break; }
+            if (!compile_schedule_cached(tk, N, c->frozen, c->L, c->ops, c->stats, &err)) { rc = fail(POLAR_E_ARG, err); break; }
             memset(&c->sched, 0, sizeof(c->sched));
             memcpy(c->sched.ops, c->ops.data(), c->ops.size() * sizeof(uint32_t));
         } else {
@@ -800,6 +837,14 @@ long polar_cuda_code_launches(polar_code_t c)
 
 long polar_cuda_code_fallbacks(polar_code_t c) { return c ? c->fallbacks : 0; }
 
+int polar_cuda_schedule_cache_stats(long* hits, long* misses)
+{
+    std::lock_guard<std::mutex> lk(g_schedMu);
+    if (hits) *hits = g_schedHits;
+    if (misses) *misses = g_schedMisses;
+    return (int)g_schedCache.size();
+}
+
 int polar_cuda_schedule_stats(int kind, int N, const uint32_t* frozen, int nFrozen, int listSize, long* counts,
                               long* sizes, double* laneOpsPerFrame)
 {
@@ -813,7 +858,7 @@ int polar_cuda_schedule_stats(int kind, int N, const uint32_t* frozen, int nFroz
     ScheduleStats st;
     const char* err = nullptr;
     const bool isScl = (tk == TREE_SCL_I8 || tk == TREE_SCL_F32);
-    if (!compile_schedule(tk, N, f, isScl ? listSize : 1, ops, st, &err)) return fail(POLAR_E_ARG, err);
+    if (!compile_schedule_cached(tk, N, f, isScl ? listSize : 1, ops, st, &err)) return fail(POLAR_E_ARG, err);
     for (int i = 0; i < 32; ++i) {
         if (counts) counts[i] = i < (int)OP_COUNT ? st.count[i] : 0;
         if (sizes) sizes[i] = i < (int)OP_COUNT ? st.size[i] : 0;

@@ -127,6 +127,11 @@ int polar_cuda_code_schedule(polar_code_t code, uint32_t* ops, int maxOps); /* r
  * counts / sizes: 32 entries indexed by polar::OpCode; returns the op count or a negative error. */
 int polar_cuda_schedule_stats(int kind, int N, const uint32_t* frozen, int nFrozen, int listSize, long* counts,
                               long* sizes, double* laneOpsPerFrame);
+/* Compiled schedules are cached per process, keyed by (tree flavour, N, frozen set, list size): re-creating a code
+ * after setSystematic / setErrorDetection, or one decoder object per host thread, compiles the node program once
+ * (the reference rebuilds its node tree in every initialize(), fastssc_fip_char.cpp:592-614).  Returns the number
+ * of cached entries; hits / misses count lookups since the library was loaded. */
+int polar_cuda_schedule_cache_stats(long* hits, long* misses);
 /* number of kernel launches issued through this handle so far (bench's gpu_launches) */
 long polar_cuda_code_launches(polar_code_t code);
 /* adaptive kinds: frames the list decoder had to redo, summed over all decode calls on this handle so far

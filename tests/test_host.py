@@ -163,3 +163,26 @@ def test_sharding_world2_gloo(tmp_path):
     for n, w in ((7, 8), (1 << 20, 8), (1001, 3)):
         r = [frame_range(n, k, w) for k in range(w)]
         assert r[0][0] == 0 and r[-1][1] == n and all(r[i][1] == r[i + 1][0] for i in range(w - 1))
+
+
+def test_schedule_cache():
+    """SURVEY.md 8f-3: the node program of a (tree flavour, N, frozen set, list size) is compiled once per process;
+    a cached program is the same program (histogram, op count, lane-op total)."""
+    fz = ap.frozen_bits(512, 200, 0.0, "BE")
+    n0, h0, m0 = ap.schedule_cache_stats()
+    first = _hist(ap.KIND_SCL_I8, 512, fz, 4)
+    n1, h1, m1 = ap.schedule_cache_stats()
+    assert (h1, m1) == (h0, m0 + 1) and n1 == min(n0 + 1, 64)
+    again = _hist(ap.KIND_SCL_I8, 512, fz, 4)
+    assert ap.schedule_cache_stats()[1:] == (h1 + 1, m1)
+    assert np.array_equal(first[0], again[0]) and np.array_equal(first[1], again[1]) and first[2:] == again[2:]
+    _hist(ap.KIND_SCL_I8, 512, fz, 8)                     # another list size is another program
+    _hist(ap.KIND_FASTSSC_I8, 512, fz, 1)
+    fz2 = fz.copy()
+    fz2[-1] = 511 if fz[-1] != 511 else 510                # same length, different set
+    fz2.sort()
+    _hist(ap.KIND_SCL_I8, 512, fz2, 4)
+    assert ap.schedule_cache_stats()[2] == m1 + 3
+    for i in range(70):                                    # more distinct codes than entries: the LRU stays bounded
+        _hist(ap.KIND_FASTSSC_I8, 256, ap.frozen_bits(256, 60 + i, 0.0, "BB"), 1)
+    assert ap.schedule_cache_stats()[0] == 64
