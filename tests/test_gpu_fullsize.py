@@ -17,7 +17,7 @@ FULL = [  # kind, N, K, construction, L, crc, oracle-checked tile, full batch, f
     (KIND_SCL_I8, 1024, 512, "5G", 8, 16, 1024, 1 << 19, "char", False),        # configs[2], the headline
     (KIND_FASTSSC_I8, 1024, 512, "BB", 1, 0, 2048, 1 << 20, "char", False),     # configs[0]
     (KIND_FASTSSC_F32, 256, 128, "BB", 1, 0, 2048, 1 << 20, "float", False),    # configs[1]
-    (KIND_SCL_I8, 2048, 1024, "BB", 32, 32, 96, 1 << 15, "char", False),        # configs[3]
+    (KIND_SCL_I8, 2048, 1024, "BB", 32, 32, 128, 1 << 15, "char", False),        # configs[3]
     (KIND_ADAPTIVE_I8, 1024, 512, "5G", 8, 16, 1024, 1 << 20, "char", True),
 ]
 

@@ -219,3 +219,31 @@ def test_primitives_exhaustive(gpu):
         assert np.array_equal(f, nf)
         ng = np.clip(bi - ai if bitval < 0 else bi + ai, -128, 127).astype(np.int8)
         assert np.array_equal(g, ng)
+
+
+def test_empty_and_ragged_batches(gpu):
+    """Zero frames is a no-op for every entry point; batch sizes that do not fill a warp / a block / a grid wave
+    (1, 31, 33, one more than a wave) decode like the same frames inside a large batch."""
+    N, K, crc = 256, 128, 8
+    fz = ap.frozen_bits(N, K, 0.0, "BB")
+    enc = ap.PolarEncoder(N, fz)
+    enc.setErrorDetection(crc)
+    assert enc.encode_batch(np.zeros((0, K // 8), np.uint8)).shape == (0, N // 8)
+    for L, flavour, adaptive in ((1, "char", False), (4, "char", False), (1, "float", False), (4, "float", False),
+                                 (4, "char", True)):
+        dec = ap.PolarDecoder(N, L, fz, flavour, adaptive=adaptive)
+        dec.setErrorDetection(crc)
+        dt = np.float32 if flavour == "float" else np.int8
+        out, ok = dec.decode_batch(np.zeros((0, N), dt))
+        assert out.shape == (0, K // 8) and ok.shape == (0,)
+        wave = dec.info().gridBlocks * dec.info().warpsPerBlock * (32 // L if L > 1 and not adaptive else 32)
+        n = wave + 1
+        llr = awgn_llrs(N, fz, 512, 1.0, crc, fmt="f32" if flavour == "float" else "i8")[0]
+        llr = np.ascontiguousarray(np.tile(llr, ((n + 511) // 512, 1))[:n])
+        big, bigk = dec.decode_batch(llr)
+        for m in (1, 31, 33, 100):
+            o, k = dec.decode_batch(llr[:m])
+            assert np.array_equal(o, big[:m]) and np.array_equal(k, bigk[:m]), (L, flavour, adaptive, m)
+        assert np.array_equal(big[n - 1], big[(n - 1) % 512]) and bigk[n - 1] == bigk[(n - 1) % 512]
+    p = ap.Puncturer(200, fz)
+    assert p.depuncture_batch(np.zeros((0, 200), np.int8)).shape == (0, N)
