@@ -198,7 +198,8 @@ int setup_decoder_geometry(polar_code* c)
         // what sets the resident warp count; region A of the bit slots holds stages 0..lgN-1 (the root is
         // assembled by the epilogue), region B is a ping-pong pair.
         // (fp32 lists: one float per word, stage s at word 2^s - 1 of the slot)
-        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 10 ? (sclF32 ? 5 : 3) : c->lgN >= 9 ? (sclF32 ? 3 : 2) : (c->lgN >= 7 ? 1 : 0));
+        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 10 ? (sclF32 ? 5 : (c->lgN >= 11 && L >= 16 ? 4 : 3)) : // N=2048, L=32: 8 -> 10 resident warps, 1.56 -> 1.67 Gbit/s
+                                                  c->lgN >= 9 ? (sclF32 ? 3 : 2) : (c->lgN >= 7 ? 1 : 0));
         nSpill = std::max(0, std::min(nSpill, c->lgN - 5));
         if (sclF32) // keep a warp's footprint within reach of a few resident warps per SM
             while (nSpill < c->lgN - 5 && (size_t)32 * f32_woff(c->lgN - nSpill) * 4 > 96 * 1024) ++nSpill;
