@@ -83,15 +83,19 @@ CrcTables build_crc_tables(int crcBits, int K)
     t.syn.assign(K, 0);
     t.gen.assign(K, 0);
     if (!crcBits) return t;
-    const int bytes = K / 8;
-    std::vector<uint8_t> buf(bytes, 0);
-    t.synInit = crc_syndrome(crcBits, buf.data(), bytes);
-    t.genInit = crc_compute(crcBits, buf.data(), bytes);
-    const int tr = trailer_offset(crcBits, bytes);
+    // decoders check ceil(K/8) bytes (zero padded: fastssc_fip_char.cpp:627, scl_fip_char.cpp:808), the encoder
+    // generates over floor(K/8) (butterfly_fip_packed.cpp:48): the two differ when K is not a multiple of 8
+    const int cb = (K + 7) / 8, gb = K / 8;
+    std::vector<uint8_t> buf(cb, 0);
+    const bool canCheck = cb >= crcBits / 8 && (crcBits != 32 || cb >= 4);
+    const bool canGen = gb >= crcBits / 8 && (crcBits != 32 || gb >= 4);
+    if (canCheck) t.synInit = crc_syndrome(crcBits, buf.data(), cb);
+    if (canGen) t.genInit = crc_compute(crcBits, buf.data(), gb);
+    const int tr = trailer_offset(crcBits, gb);
     for (int k = 0; k < K; ++k) {
         buf[k >> 3] = (uint8_t)(0x80 >> (k & 7));
-        t.syn[k] = crc_syndrome(crcBits, buf.data(), bytes) ^ t.synInit;
-        t.gen[k] = ((k >> 3) < tr) ? (crc_compute(crcBits, buf.data(), bytes) ^ t.genInit) : 0u;
+        if (canCheck) t.syn[k] = crc_syndrome(crcBits, buf.data(), cb) ^ t.synInit;
+        if (canGen) t.gen[k] = ((k >> 3) < tr) ? (crc_compute(crcBits, buf.data(), gb) ^ t.genInit) : 0u;
         buf[k >> 3] = 0;
     }
     return t;

@@ -25,7 +25,7 @@ struct CrcTables {
     uint32_t genInit = 0;            // checksum of the all-zero payload
     std::vector<uint32_t> gen;       // per info bit k: checksum contribution (0 for trailer bits)
 };
-// K info bits (K % 8 == 0 when crcBits > 0)
+// K info bits; syn covers the ceil(K/8) zero-padded bytes a decoder checks, gen the floor(K/8) bytes an encoder signs
 CrcTables build_crc_tables(int crcBits, int K);
 
 } // namespace polar

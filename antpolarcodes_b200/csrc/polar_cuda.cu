@@ -110,6 +110,10 @@ struct polar_code {
     cudaStream_t pipe[2] = { nullptr, nullptr }; // HOST-buffer calls: double-buffered copy / compute pipeline
     cudaEvent_t pipeDone[2] = { nullptr, nullptr };
     long launches = 0;
+    // the spill / quantiser scratch belongs to the handle: a launch on another stream waits for the previous one
+    cudaEvent_t scratchFree = nullptr;
+    cudaStream_t scratchStream = nullptr;
+    bool scratchBusy = false;
     // adaptive kinds: the two decoders and the compaction scratch
     polar_code* fast = nullptr;
     polar_code* list = nullptr;
@@ -275,6 +279,11 @@ int setup_decoder_geometry(polar_code* c)
     const size_t perWarp = (size_t)g.warpW * 4;
     if (perWarp > (size_t)prop.sharedMemPerBlockOptin)
         return fail(POLAR_E_UNSUPPORTED, "code does not fit in shared memory (N x listSize too large)");
+    // The dynamic shared-memory limit belongs to the kernel FUNCTION on the device, not to this handle: it is raised
+    // to the device maximum once and never lowered, so handles with different geometries (and host threads that each
+    // own a decoder) can share one template instance.
+    CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)prop.sharedMemPerBlockOptin));
     int bestWarps = 0, bestW = 1, bestB = 1;
     const int forceW = env_int("POLAR_CUDA_WARPS_PER_BLOCK", 0);
     // equal resident warps: wide blocks first (one or two lockstep domains per SM keep the instruction fetch shared)
@@ -288,7 +297,6 @@ int setup_decoder_geometry(polar_code* c)
         if (!scl && w > (wide ? 16 : 8)) continue; // launch bounds of the Fast-SSC kernels
         const size_t smem = perWarp * w;
         if (smem > (size_t)prop.sharedMemPerBlockOptin) continue;
-        CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int nb = 0;
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)c->kernel, w * 32, smem));
         if (nb * w > bestWarps) { bestWarps = nb * w; bestW = w; bestB = nb; }
@@ -297,8 +305,6 @@ int setup_decoder_geometry(polar_code* c)
     c->warpsPerBlock = bestW;
     c->blocksPerSM = bestB;
     c->smemPerBlock = perWarp * bestW;
-    CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)c->smemPerBlock));
     if (g.spillWarpW) {
         const size_t words = (size_t)g.spillWarpW * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
         CUDA_TRY(cudaMalloc(&c->dSpill, words * sizeof(uint32_t)));
@@ -352,6 +358,7 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns);
     cudaFree(c->dFailIdx); cudaFree(c->dFailCount); cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
     if (c->hFailCount) cudaFreeHost(c->hFailCount);
+    if (c->scratchFree) cudaEventDestroy(c->scratchFree);
     polar_cuda_code_destroy(c->fast);
     polar_cuda_code_destroy(c->list);
     for (int i = 0; i < 2; ++i) {
@@ -398,9 +405,13 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
     if (nFrozen < 0 || nFrozen > N || (nFrozen && !frozen)) return fail(POLAR_E_ARG, "bad frozen set");
     if (crcBits != 0 && crcBits != 8 && crcBits != 16 && crcBits != 32) return fail(POLAR_E_ARG, "CRC INVALID SIZE!");
     const int K = N - nFrozen;
-    if (crcBits && (K % 8 != 0 || K < crcBits))
-        return fail(POLAR_E_ARG, "with a CRC, K must be a multiple of 8 and at least the CRC size");
-    if (crcBits == 32 && K / 8 < 4) return fail(POLAR_E_ARG, "CRC32 needs at least 4 info bytes");
+    // decoders hand ceil(K/8) zero-padded bytes to Detector::check (fastssc_fip_char.cpp:627, scl_fip_char.cpp:808),
+    // so K need not be a multiple of 8 there; the encoder signs floor(K/8) bytes (butterfly_fip_packed.cpp:48)
+    const int crcBytes = kind == POLAR_KIND_ENC ? K / 8 : (K + 7) / 8;
+    if (crcBits && crcBytes < crcBits / 8) return fail(POLAR_E_ARG, "with a CRC, the info block must be at least as long as the CRC");
+    if (crcBits && kind == POLAR_KIND_ENC && K % 8 != 0)
+        return fail(POLAR_E_ARG, "encoder with a CRC: K must be a multiple of 8");
+    if (crcBits == 32 && crcBytes < 4) return fail(POLAR_E_ARG, "CRC32 needs at least 4 info bytes");
     if (K < 1) return fail(POLAR_E_ARG, "no information bits");
     if (cudaSetDevice(device) != cudaSuccess) {
         cudaGetLastError();
@@ -525,6 +536,7 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
     p.spill = c->dSpill;
     p.runs = c->dRuns;
     p.nRuns = c->nRuns;
+    if (c->scratchBusy && c->scratchStream != st) CUDA_TRY(cudaStreamWaitEvent(st, c->scratchFree, 0));
     const bool f32Kind = (c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32);
     if (llrType == POLAR_LLR_F32 && !f32Kind) { // CharContainer::insertLlr(const float*): quantise once, decode the int8 copy
         const size_t need = nFrames * (size_t)c->N;
@@ -550,6 +562,12 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
     c->kernel<<<grid, c->warpsPerBlock * 32, c->smemPerBlock, st>>>(p, c->sched);
     c->launches++;
     CUDA_TRY(cudaGetLastError());
+    if (c->dSpill || c->dQuant) { // batches of one handle on different streams must not share the scratch concurrently
+        if (!c->scratchFree) CUDA_TRY(cudaEventCreateWithFlags(&c->scratchFree, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventRecord(c->scratchFree, st));
+        c->scratchStream = st;
+        c->scratchBusy = true;
+    }
     return POLAR_OK;
 }
 

@@ -175,6 +175,57 @@ double polar_ref_decode(void* h, const void* llr, long nFrames, uint8_t* out, ui
     return std::chrono::duration<double>(t1 - t0).count();
 }
 
+// polar_ref_decode with two more knobs:
+//   llrIsFloat : 1 = float LLRs whatever the kind -- the int8 decoders then quantise them themselves, which is what
+//                pcbench times (Decoder::decode_vector(const float*), benchmark/main_benchmark.cpp:202-241); 0 = int8;
+//                -1 = by kind, like polar_ref_decode
+//   fresh      : 1 = a NEW decoder object for every frame (SclAvxFloat keeps the winning metric of the previous
+//                frame, scl_avx_float.cpp:46-56,102-108)
+double polar_ref_decode_ex(void* h, const void* llr, int llrIsFloat, long nFrames, uint8_t* out, uint8_t* ok,
+                           int nThreads, int repeat, int fresh)
+{
+    RefCode* c = static_cast<RefCode*>(h);
+    if (nThreads < 1) nThreads = 1;
+    if (repeat < 1) repeat = 1;
+    const size_t kb = (c->K + 7) / 8;
+    bool isFloat = (c->kind == KIND_FASTSSC_F32 || c->kind == KIND_SCL_F32 || c->kind >= KIND_ADAPTIVE_I8);
+    if (llrIsFloat >= 0) isFloat = llrIsFloat != 0;
+    std::atomic<int> failed{ 0 };
+    auto worker = [&](int t) {
+        long lo = nFrames * t / nThreads, hi = nFrames * (t + 1) / nThreads;
+        Decoding::Decoder* d = nullptr;
+        try {
+            if (!fresh) d = make_decoder(*c);
+            for (int r = 0; r < repeat; ++r) {
+                for (long f = lo; f < hi; ++f) {
+                    if (fresh) d = make_decoder(*c);
+                    bool res;
+                    if (isFloat)
+                        res = d->decode_vector(static_cast<const float*>(llr) + f * c->N, out + f * kb);
+                    else
+                        res = d->decode_vector(static_cast<const char*>(llr) + f * c->N, out + f * kb);
+                    if (ok) ok[f] = res ? 1 : 0;
+                    if (fresh) { delete d; d = nullptr; }
+                }
+            }
+            delete d;
+        } catch (...) {
+            failed = 1;
+        }
+    };
+    auto t0 = std::chrono::steady_clock::now();
+    if (nThreads == 1) {
+        worker(0);
+    } else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nThreads; ++t) th.emplace_back(worker, t);
+        for (auto& x : th) x.join();
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    if (failed) return -2.0;
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
 // mode 0: generate (writes trailing check bytes in place), returns 0
 // mode 1: check, returns 1/0
 int polar_ref_crc(int crcBits, uint8_t* data, int bytes, int mode)

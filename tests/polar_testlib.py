@@ -116,6 +116,27 @@ def ref_decode(kind, N, frozen, llr, L=1, systematic=1, crc=0, threads=1, repeat
     return out, ok, t
 
 
+def ref_decode_ex(kind, N, frozen, llr, L=1, systematic=1, crc=0, threads=1, repeat=1, fresh=False):
+    """ref_decode that takes the LLR type from the array (float32 into an int8 decoder = the decoder's own quantiser,
+    as pcbench feeds it) and can build a fresh decoder object per frame (see ref_decode_fresh), multi-threaded."""
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    llr = np.ascontiguousarray(llr)
+    assert llr.dtype in (np.int8, np.float32)
+    nF = llr.shape[0]
+    K = N - len(frozen)
+    out = np.zeros((nF, (K + 7) // 8), np.uint8)
+    ok = np.zeros(nF, np.uint8)
+    fn = ref().polar_ref_decode_ex
+    fn.argtypes = [_vp, _vp, _i, _l, _vp, _vp, _i, _i, _i]
+    fn.restype = _d
+    h = ref().polar_ref_code_create(kind, N, _ptr(frozen), len(frozen), L, systematic, crc)
+    t = fn(h, _ptr(llr), 1 if llr.dtype == np.float32 else 0, nF, _ptr(out), _ptr(ok), threads, repeat, 1 if fresh else 0)
+    ref().polar_ref_code_destroy(h)
+    if t < 0:
+        raise RuntimeError("reference decode threw")
+    return out, ok, t
+
+
 def ref_decode_fresh(kind, N, frozen, llr, L=1, systematic=1, crc=0):
     """One NEW reference decoder object per frame.  Needed for SclAvxFloat: PathList never resets the metric
     of path 0 (scl_avx_float.cpp:20-56,102-108), so a reused object starts every frame from the previous
