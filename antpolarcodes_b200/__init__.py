@@ -14,7 +14,7 @@ import os as _os
 import numpy as _np
 
 _HERE = _os.path.dirname(_os.path.abspath(__file__))
-_LIB_PATH = _os.path.join(_HERE, "libpolar_cuda.so")
+_LIB_PATH = _os.environ.get("POLAR_CUDA_LIB") or _os.path.join(_HERE, "libpolar_cuda.so")  # the override is for A/B builds
 
 KIND_ENC, KIND_FASTSSC_I8, KIND_FASTSSC_F32, KIND_SCL_I8, KIND_SCL_F32 = range(5)
 KIND_ADAPTIVE_I8, KIND_ADAPTIVE_F32, KIND_ADAPTIVE_MIXED = 5, 6, 7
@@ -29,6 +29,8 @@ EXPORTS = [
     "polar_cuda_code_fallbacks", "polar_cuda_schedule_cache_stats", "polar_cuda_puncturer_positions", "polar_cuda_puncturer_create",
     "polar_cuda_puncturer_destroy", "polar_cuda_puncturer_parent_length", "polar_cuda_puncture_batch",
     "polar_cuda_depuncture_batch", "polar_cuda_puncture_packed_batch",
+    "polar_cuda_sim_create", "polar_cuda_sim_destroy", "polar_cuda_sim_run", "polar_cuda_sim_buffers", "polar_cuda_sim_launches",
+    "polar_cuda_test_philox",
 ]
 
 
@@ -74,6 +76,13 @@ def lib():
         l.polar_cuda_puncture_batch.argtypes = [vp, vp, i, i, sz, vp, vp]
         l.polar_cuda_depuncture_batch.argtypes = [vp, vp, i, i, sz, vp, vp]
         l.polar_cuda_puncture_packed_batch.argtypes = [vp, vp, i, sz, vp, vp]
+        l.polar_cuda_sim_create.argtypes = [i, i, vp, i, i, i, i, i, sz, _c.POINTER(vp)]
+        l.polar_cuda_sim_destroy.argtypes = [vp]
+        l.polar_cuda_sim_run.argtypes = [vp, _c.c_double, _c.c_double, _c.c_uint64, _c.c_uint32, _c.c_uint64, sz, vp, vp]
+        l.polar_cuda_sim_buffers.argtypes = [vp, _c.POINTER(vp), _c.POINTER(vp), _c.POINTER(vp), _c.POINTER(vp), _c.POINTER(sz)]
+        l.polar_cuda_sim_launches.argtypes = [vp, _c.POINTER(_c.c_long)]
+        l.polar_cuda_sim_launches.restype = _c.c_long
+        l.polar_cuda_test_philox.argtypes = [vp, vp, vp]
         _lib = l
     return _lib
 
@@ -475,6 +484,82 @@ class Puncturer:
 
     def puncturePacked(self, vec):
         return self._one(self.puncturePacked_batch, vec, self._parent // 8, _np.uint8)
+
+
+class LinkSimulator:
+    """The worker loop of the reference's pcsim (src/simulation/simulator.cpp:632-672) on one GPU: payload -> CRC -> encoder ->
+    BPSK -> AWGN -> amplifier / quantiser -> decoder -> error counters, every stage a kernel, no host round trip in between.
+    `counters` is a torch int64 CUDA tensor of 5 entries that run() ADDS to: runs, block errors, bit errors (over all K
+    info bits), reported errors (detector failures), undetected errors."""
+
+    COUNTERS = ("runs", "errors", "biterrors", "reported", "undetected")
+
+    def __init__(self, blockLength, listSize, frozenBitPositions, decoderType="char", crc=0, systematic=True, adaptive=False,
+                 device=0, batch=1 << 16):
+        kind = PolarDecoder(blockLength, listSize, frozenBitPositions, decoderType, device, adaptive)._kind
+        f = _np.ascontiguousarray(frozenBitPositions, _np.uint32)
+        self._h = _c.c_void_p()
+        self.N, self.K, self.batch, self.kind = int(blockLength), int(blockLength) - len(f), int(batch), kind
+        self.kb = (self.K + 7) // 8
+        _check(lib().polar_cuda_sim_create(int(device), self.N, f.ctypes.data, len(f), kind, max(int(listSize), 1),
+                                           int(bool(systematic)), int(crc), self.batch, _c.byref(self._h)))
+        self.is_float = kind in (KIND_FASTSSC_F32, KIND_SCL_F32, KIND_ADAPTIVE_F32, KIND_ADAPTIVE_MIXED)
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().polar_cuda_sim_destroy(self._h)
+            self._h = _c.c_void_p()
+
+    __del__ = close
+
+    def default_amplification(self, ebn0_db):
+        """pcsim's defaults: 10 ahead of the 8-bit quantiser (setup.cpp:58), 4 * 10^(Eb/N0 / 10) for float (simulator.cpp:377)"""
+        return 4.0 * 10.0 ** (ebn0_db / 10.0) if self.is_float else 10.0
+
+    def run(self, ebn0_db, seed, point, first_frame, n_frames, counters, amplification=None, stream=0):
+        if not (_is_torch(counters) and counters.is_cuda and counters.numel() >= 5 and counters.element_size() == 8):
+            raise RuntimeError("counters must be a CUDA int64 tensor with 5 entries")
+        amp = self.default_amplification(ebn0_db) if amplification is None else float(amplification)
+        _check(lib().polar_cuda_sim_run(self._h, float(ebn0_db), amp, int(seed), int(point), int(first_frame), int(n_frames),
+                                        counters.data_ptr(), stream))
+
+    def last_batch(self):
+        """(llr, sent, decoded, ok) of the last batch as torch tensors that alias the simulator's device buffers."""
+        import torch
+        p = [_c.c_void_p() for _ in range(4)]
+        n = _c.c_size_t()
+        _check(lib().polar_cuda_sim_buffers(self._h, _c.byref(p[0]), _c.byref(p[1]), _c.byref(p[2]), _c.byref(p[3]), _c.byref(n)))
+        n = n.value
+
+        def view(ptr, shape, dtype, itemsize):
+            nbytes = int(_np.prod(shape)) * itemsize
+
+            class _Holder:  # __cuda_array_interface__ over a raw device pointer
+                pass
+            h = _Holder()
+            h.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": dtype, "data": (ptr.value, False), "version": 2}
+            h.owner = self
+            return torch.as_tensor(h, device=torch.device("cuda", self.device))
+        llr = view(p[0], (n, self.N), "<f4" if self.is_float else "|i1", 4 if self.is_float else 1)
+        sent = view(p[1], (n, self.kb), "|u1", 1)
+        dec = view(p[2], (n, self.kb), "|u1", 1)
+        ok = view(p[3], (n,), "|u1", 1)
+        return llr, sent, dec, ok
+
+    def launches(self):
+        d = _c.c_long(0)
+        total = lib().polar_cuda_sim_launches(self._h, _c.byref(d))
+        return int(total), int(d.value)
+
+
+def test_philox(ctr, key):
+    """Philox4x32-10 of the device (known-answer hook)."""
+    c = _np.ascontiguousarray(ctr, _np.uint32)
+    k = _np.ascontiguousarray(key, _np.uint32)
+    out = _np.zeros(4, _np.uint32)
+    _check(lib().polar_cuda_test_philox(c.ctypes.data, k.ctypes.data, out.ctypes.data))
+    return out
 
 
 def schedule_cache_stats():

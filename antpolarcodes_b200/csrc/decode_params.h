@@ -29,6 +29,7 @@ struct DecodeParams {
     int smemStages;           // LLR stages [0, smemStages) live in shared memory, [smemStages, lgN) in `spill`
     int spillWarpW;           // words of `spill` per resident warp
     int lockstep;             // warps of a block meet at a barrier before every schedule step
+    int regStages;            // int8 list decoder: stages <= regStages live in registers (min(4, lgN - 2), or -1: none)
     // Fast-SSC (one frame per thread): rows of 32 words
     int llrRows, bitRows, tileRow, outRow, chanRow, nRuns;
 };
@@ -37,5 +38,8 @@ struct DecodeParams {
 __host__ __device__ inline int llr_woff(int s) { return s < 2 ? s : (1 << (s - 2)) + 1; }
 // word offset of stage s inside a bit array (stage s block = 2^s bits, at least one word)
 __host__ __device__ inline int bit_woff(int s) { return s <= 5 ? s : (1 << (s - 5)) + 4; }
+
+// fp32 decoders: word (row) offset of stage s (2^s floats)
+__host__ __device__ inline int f32_woff(int s) { return (1 << s) - 1; }
 
 } // namespace polar

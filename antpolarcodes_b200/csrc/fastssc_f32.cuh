@@ -32,7 +32,6 @@ struct ScfCtx {
 
 #define SCF_ROW(c, row) (c).sm[((row) << 5) + (c).lane]
 
-__host__ __device__ inline int f32_woff(int s) { return (1 << s) - 1; } // row of stage s (2^s floats)
 
 POLAR_DEV float* scf_stage(const ScfCtx& c, int s)
 {

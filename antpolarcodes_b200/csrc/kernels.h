@@ -1,0 +1,16 @@
+// Decoder kernels, one translation unit per family (scl_i8.cu, scl_f32.cu, fastssc_i8.cu, fastssc_f32.cu): the host
+// runtime (polar_cuda.cu) only sees these getters.
+#pragma once
+#include "decode_params.h"
+#include "schedule.h"
+
+namespace polar {
+
+typedef void (*DecodeKernel)(const DecodeParams, const Schedule);
+
+DecodeKernel scl_i8_kernel_for(int listSize);        // SclFipChar;      nullptr if listSize is not a power of two <= 32
+DecodeKernel scl_f32_kernel_for(int listSize);       // SclAvxFloat
+DecodeKernel fastssc_i8_kernel_for(bool wide);       // FastSscFipChar   (wide: 16-warp blocks at 128 registers)
+DecodeKernel fastssc_f32_kernel_for(bool wide);      // FastSscAvxFloat
+
+} // namespace polar

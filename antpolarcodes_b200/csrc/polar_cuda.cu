@@ -3,15 +3,15 @@
 
 #include "construct.h"
 #include "crc_host.h"
+#include "batch_kernels.cuh"
 #include "decode_params.h"
 #include "encode.cuh"
-#include "fastssc_f32.cuh"
-#include "fastssc_i8.cuh"
+#include "kernels.h"
 #include "puncture.cuh"
 #include "schedule.h"
-#include "scl_f32.cuh"
-#include "scl_i8.cuh"
+#include "sim.cuh"
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -38,8 +38,6 @@ int fail(int code, const std::string& msg)
         if (e__ != cudaSuccess)                                                                       \
             return fail(POLAR_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));           \
     } while (0)
-
-typedef void (*DecodeKernel)(const DecodeParams, const Schedule);
 
 // Compiled-schedule cache: decoder objects are rebuilt whenever setSystematic / setErrorDetection
 // change, one per host thread and per sweep point -- the node program only depends on (tree flavour, N, frozen set,
@@ -130,35 +128,6 @@ struct polar_code {
 
 namespace {
 
-template <int L>
-DecodeKernel scl_kernel_for() { return scl_i8_kernel<L>; }
-
-DecodeKernel pick_scl_kernel(int L)
-{
-    switch (L) {
-    case 1: return scl_kernel_for<1>();
-    case 2: return scl_kernel_for<2>();
-    case 4: return scl_kernel_for<4>();
-    case 8: return scl_kernel_for<8>();
-    case 16: return scl_kernel_for<16>();
-    case 32: return scl_kernel_for<32>();
-    }
-    return nullptr;
-}
-
-DecodeKernel pick_sclf_kernel(int L)
-{
-    switch (L) {
-    case 1: return scl_f32_kernel<1>;
-    case 2: return scl_f32_kernel<2>;
-    case 4: return scl_f32_kernel<4>;
-    case 8: return scl_f32_kernel<8>;
-    case 16: return scl_f32_kernel<16>;
-    case 32: return scl_f32_kernel<32>;
-    }
-    return nullptr;
-}
-
 int env_int(const char* name, int dflt)
 {
     const char* v = getenv(name);
@@ -183,6 +152,7 @@ int setup_decoder_geometry(polar_code* c)
     g.lockstep = env_int("POLAR_CUDA_LOCKSTEP", c->kind == POLAR_KIND_FASTSSC_I8 ? 128 : c->kind == POLAR_KIND_SCL_F32 ? 8 : 64);
     if (g.lockstep & (g.lockstep - 1)) g.lockstep = 1; // the kernels test pc & (lockstep - 1)
     g.rootLeaf = 0;
+    g.regStages = c->kind == POLAR_KIND_SCL_I8 ? std::min(env_int("POLAR_CUDA_REG_STAGES", 4), c->lgN - 2) : -1;
     g.bitB1 = 0;
     g.spillWarpW = 0;
     g.chanRow = -1;
@@ -229,7 +199,10 @@ int setup_decoder_geometry(polar_code* c)
         if (nSpill)
             g.spillWarpW = sclF32 ? 32 * ((1 << c->lgN) - (1 << g.smemStages))
                                   : 32 * ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
-        c->kernel = sclF32 ? pick_sclf_kernel(L) : pick_scl_kernel(L);
+        c->kernel = sclF32 ? scl_f32_kernel_for(L) : scl_i8_kernel_for(L);
+        if (!sclF32) // dense handler ids for the kernel's jump table (the fp32 kernel decodes (code, stage) itself)
+            for (size_t i = 0; i < c->ops.size(); ++i)
+                c->sched.ops[i] = (c->ops[i] & 0xFFFFu) | (scl_handler_id(c->ops[i], g.regStages) << 16);
     } else if (c->kind == POLAR_KIND_FASTSSC_F32) {
         // fp32 Fast-SSC: same row stack, one float per word; stage s sits at row 2^s - 1.  Stages from 6 up
         // (64 floats and more) go to the L2-resident scratch.
@@ -250,7 +223,7 @@ int setup_decoder_geometry(polar_code* c)
         g.warpW = rows * 32;
         if (nSpill) g.spillWarpW = 32 * (f32_woff(c->lgN) - f32_woff(g.smemStages));
         wide = env_int("POLAR_CUDA_SC_WIDE", 1) != 0;
-        c->kernel = wide ? (DecodeKernel)fastssc_f32_kernel<true> : (DecodeKernel)fastssc_f32_kernel<false>;
+        c->kernel = fastssc_f32_kernel_for(wide);
     } else {
         // One frame per thread; a warp's shared memory is a stack of 32-word rows: LLR stages below smemStages,
         // then the packed partial sums.  The top stages live in an L2-resident scratch with the same
@@ -273,7 +246,7 @@ int setup_decoder_geometry(polar_code* c)
         g.warpW = rows * 32;
         if (nSpill) g.spillWarpW = 32 * (llr_woff(c->lgN) - llr_woff(g.smemStages));
         wide = env_int("POLAR_CUDA_SC_WIDE", 1) != 0;
-        c->kernel = wide ? (DecodeKernel)fastssc_i8_kernel<true> : (DecodeKernel)fastssc_i8_kernel<false>;
+        c->kernel = fastssc_i8_kernel_for(wide);
     }
     if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
     const size_t perWarp = (size_t)g.warpW * 4;
@@ -299,6 +272,7 @@ int setup_decoder_geometry(polar_code* c)
         if (smem > (size_t)prop.sharedMemPerBlockOptin) continue;
         int nb = 0;
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)c->kernel, w * 32, smem));
+        nb = std::min(nb, env_int("POLAR_CUDA_MAX_BLOCKS_PER_SM", 64)); // experiments: cap the occupancy
         if (nb * w > bestWarps) { bestWarps = nb * w; bestW = w; bestB = nb; }
     }
     if (!bestWarps) return fail(POLAR_E_UNSUPPORTED, "kernel cannot be resident with this shared memory footprint");
@@ -1064,6 +1038,137 @@ int polar_cuda_puncture_packed_batch(polar_puncturer_t p, const uint8_t* in, int
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------- on-device link simulator (pcsim worker loop)
+struct polar_sim {
+    int device = 0, N = 0, K = 0, kb = 0, nb = 0, llrIsFloat = 0;
+    size_t batch = 0;
+    polar_code* enc = nullptr;
+    polar_code* dec = nullptr;
+    uint8_t *dInfo = nullptr, *dCode = nullptr, *dOut = nullptr, *dOk = nullptr;
+    void* dLlr = nullptr;
+    size_t lastFrames = 0;
+    long launches = 0;
+};
+
+extern "C" {
+
+int polar_cuda_sim_destroy(polar_sim_t s)
+{
+    if (!s) return POLAR_OK;
+    cudaSetDevice(s->device);
+    cudaFree(s->dInfo); cudaFree(s->dCode); cudaFree(s->dOut); cudaFree(s->dOk); cudaFree(s->dLlr);
+    polar_cuda_code_destroy(s->enc);
+    polar_cuda_code_destroy(s->dec);
+    delete s;
+    return POLAR_OK;
+}
+
+int polar_cuda_sim_create(int device, int N, const uint32_t* frozen, int nFrozen, int decoderKind, int listSize, int systematic,
+                          int crcBits, size_t batchFrames, polar_sim_t* out)
+{
+    if (!out) return fail(POLAR_E_ARG, "out is null");
+    *out = nullptr;
+    if (decoderKind < POLAR_KIND_FASTSSC_I8 || decoderKind > POLAR_KIND_ADAPTIVE_MIXED) return fail(POLAR_E_ARG, "not a decoder kind");
+    if (batchFrames < 1 || batchFrames > ((size_t)1 << 24)) return fail(POLAR_E_ARG, "batch must be 1 .. 2^24 frames");
+    polar_sim* s = new polar_sim;
+    s->device = device; s->N = N; s->batch = batchFrames;
+    int rc = polar_cuda_code_create(device, POLAR_KIND_ENC, N, frozen, nFrozen, 1, systematic, crcBits, &s->enc);
+    if (!rc) rc = polar_cuda_code_create(device, decoderKind, N, frozen, nFrozen, listSize, systematic, crcBits, &s->dec);
+    if (rc) { const std::string msg = g_lastError; polar_cuda_sim_destroy(s); return fail(rc, msg); }
+    s->K = s->enc->K; s->kb = s->enc->kb; s->nb = std::max(1, N / 8);
+    s->llrIsFloat = (decoderKind == POLAR_KIND_FASTSSC_F32 || decoderKind == POLAR_KIND_SCL_F32 ||
+                     decoderKind == POLAR_KIND_ADAPTIVE_F32 || decoderKind == POLAR_KIND_ADAPTIVE_MIXED) ? 1 : 0;
+    cudaError_t e;
+    if ((e = cudaMalloc(&s->dInfo, batchFrames * (size_t)s->kb)) != cudaSuccess ||
+        (e = cudaMalloc(&s->dCode, batchFrames * (size_t)s->nb)) != cudaSuccess ||
+        (e = cudaMalloc(&s->dOut, batchFrames * (size_t)s->kb)) != cudaSuccess ||
+        (e = cudaMalloc(&s->dOk, batchFrames)) != cudaSuccess ||
+        (e = cudaMalloc(&s->dLlr, batchFrames * (size_t)N * (s->llrIsFloat ? 4 : 1))) != cudaSuccess) {
+        polar_cuda_sim_destroy(s);
+        cudaGetLastError();
+        return fail(POLAR_E_NOMEM, std::string("simulator buffers: ") + cudaGetErrorString(e));
+    }
+    *out = s;
+    return POLAR_OK;
+}
+
+int polar_cuda_sim_run(polar_sim_t s, double ebn0_db, double amplification, uint64_t seed, uint32_t point, uint64_t firstFrame,
+                       size_t nFrames, unsigned long long* counters_dev, void* stream)
+{
+    if (!s) return fail(POLAR_E_ARG, "null simulator");
+    if (!counters_dev) return fail(POLAR_E_ARG, "null counters");
+    CUDA_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    SimParams p{};
+    p.info = s->dInfo; p.code = s->dCode; p.llr = s->dLlr;
+    p.seedLo = (uint32_t)seed; p.seedHi = (uint32_t)(seed >> 32) ^ (point * 0x9E3779B9u);
+    // simulator.cpp:821-838: Es/N0 = Eb/N0 * K / N (one bit per symbol), awgn.cpp:30-43: sigma = 1 / sqrt(2 Es/N0)
+    p.sigma = (float)(1.0 / std::sqrt(2.0 * std::pow(10.0, ebn0_db / 10.0) * (double)s->K / (double)s->N));
+    p.amplification = (float)amplification;
+    p.N = s->N; p.K = s->K; p.kb = s->kb; p.nb = s->nb; p.llrIsFloat = s->llrIsFloat;
+    const int numSMs = s->enc->numSMs;
+    for (size_t done = 0; done < nFrames; done += s->batch) {
+        const size_t n = std::min(s->batch, nFrames - done);
+        p.firstFrame = firstFrame + done;
+        p.nFrames = (long long)n;
+        const long long payloadThreads = (long long)n * ((s->kb + 15) / 16);
+        sim_payload_kernel<<<(int)std::min<long long>((payloadThreads + 255) / 256, (long long)numSMs * 8), 256, 0, st>>>(p);
+        CUDA_TRY(cudaGetLastError());
+        int rc = polar_cuda_encode_batch(s->enc, s->dInfo, POLAR_MEM_DEVICE, n, s->dCode, st);
+        if (rc) return rc;
+        const long long chanThreads = (long long)n * (s->N / 4);
+        sim_channel_kernel<<<(int)std::min<long long>((chanThreads + 255) / 256, (long long)numSMs * 16), 256, 0, st>>>(p);
+        CUDA_TRY(cudaGetLastError());
+        rc = polar_cuda_decode_batch(s->dec, s->dLlr, s->llrIsFloat ? POLAR_LLR_F32 : POLAR_LLR_I8, POLAR_MEM_DEVICE, n, s->dOut,
+                                     s->dOk, st);
+        if (rc) return rc;
+        sim_count_kernel<<<(int)std::min<long long>(((long long)n + 255) / 256, (long long)numSMs * 4), 256, 0, st>>>(
+            s->dInfo, s->dOut, s->dOk, (long long)n, s->kb, counters_dev);
+        CUDA_TRY(cudaGetLastError());
+        s->launches += 3;
+        s->lastFrames = n;
+    }
+    return POLAR_OK;
+}
+
+int polar_cuda_sim_buffers(polar_sim_t s, void** llr, uint8_t** sent, uint8_t** decoded, uint8_t** ok, size_t* frames)
+{
+    if (!s) return fail(POLAR_E_ARG, "null simulator");
+    if (llr) *llr = s->dLlr;
+    if (sent) *sent = s->dInfo;
+    if (decoded) *decoded = s->dOut;
+    if (ok) *ok = s->dOk;
+    if (frames) *frames = s->lastFrames;
+    return s->llrIsFloat;
+}
+
+long polar_cuda_sim_launches(polar_sim_t s, long* decoderLaunches)
+{
+    if (!s) return 0;
+    if (decoderLaunches) *decoderLaunches = polar_cuda_code_launches(s->dec);
+    return s->launches + polar_cuda_code_launches(s->enc) + polar_cuda_code_launches(s->dec);
+}
+
+// Philox4x32-10 known-answer hook (tests): out = philox(ctr, key)
+int polar_cuda_test_philox(const uint32_t* ctr, const uint32_t* key, uint32_t* out);
+
+} // extern "C"
+
+namespace {
+__global__ void test_philox_kernel(uint4 c, uint2 k, uint4* out) { *out = philox4x32_10(c, k); }
+} // namespace
+
+extern "C" int polar_cuda_test_philox(const uint32_t* ctr, const uint32_t* key, uint32_t* out)
+{
+    uint4* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, sizeof(uint4)));
+    test_philox_kernel<<<1, 1>>>(make_uint4(ctr[0], ctr[1], ctr[2], ctr[3]), make_uint2(key[0], key[1]), d);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpy(out, d, sizeof(uint4), cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return POLAR_OK;
+}
 
 // ---------------------------------------------------------------- primitive self-test
 namespace {

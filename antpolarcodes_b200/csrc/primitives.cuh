@@ -62,27 +62,22 @@ POLAR_DEV uint32_t f4(uint32_t a, uint32_t b)
     return (m ^ (sh * 0xFFu)) + sh;
 }
 
-// g on four int8 pairs: bit ? sat(b - a) : sat(b + a); `neg` carries the left bit of element k in the most
-// significant bit of byte k (nibble_to_msb; the other bits are ignored).
-POLAR_DEV uint32_t g4(uint32_t a, uint32_t b, uint32_t neg)
-{
-    const uint32_t me = prmt(neg, 0u, 0xAA88u), mo = prmt(neg, 0u, 0xBB99u); // sign-replicating selectors
-    uint32_t ae = sext_even(a), ao = sext_odd(a);
-    const uint32_t be = sext_even(b), bo = sext_odd(b);
-    // conditional two's-complement negate in 16 bits (-(-128) = +128 is representable here)
-    ae = __vadd2(ae ^ me, me & 0x00010001u);
-    ao = __vadd2(ao ^ mo, mo & 0x00010001u);
-    uint32_t re = __vmaxs2(__viaddmin_s16x2(be, ae, 0x007F007Fu), 0xFF80FF80u);
-    uint32_t ro = __vmaxs2(__viaddmin_s16x2(bo, ao, 0x007F007Fu), 0xFF80FF80u);
-    return pack_even_odd(re, ro);
-}
-
 // saturating a + b on four int8 pairs (g with an all-zero left block: fip_char.h:112-131; REP accumulate)
 POLAR_DEV uint32_t adds4(uint32_t a, uint32_t b)
 {
     uint32_t re = __vmaxs2(__viaddmin_s16x2(sext_even(a), sext_even(b), 0x007F007Fu), 0xFF80FF80u);
     uint32_t ro = __vmaxs2(__viaddmin_s16x2(sext_odd(a), sext_odd(b), 0x007F007Fu), 0xFF80FF80u);
     return pack_even_odd(re, ro);
+}
+
+// g on four int8 pairs: bit ? sat(b - a) : sat(b + a); `neg` carries the left bit of element k in the most
+// significant bit of byte k (nibble_to_msb; the other bits are ignored).
+// sat(b - a) = ~sat(~b + a) holds exactly on int8 (~x = -x - 1, and both saturation ends map onto each other), so the
+// conditional subtraction is one saturating add between two XORs with the byte mask of the left bits.
+POLAR_DEV uint32_t g4(uint32_t a, uint32_t b, uint32_t neg)
+{
+    const uint32_t m = prmt(neg, 0u, 0xBA98u); // 0xFF in byte k where the left bit is set (sign-replicating selectors)
+    return adds4(b ^ m, a) ^ m;
 }
 
 // exact sums of min(x,0) / max(x,0) over the four bytes (IDP.4A)

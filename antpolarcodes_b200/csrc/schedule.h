@@ -47,6 +47,29 @@ inline constexpr uint32_t make_op(uint32_t code, uint32_t stage, uint32_t lgPath
 #define POLAR_OP_FLAGS(w) (((w) >> 13) & 7u)
 #define POLAR_OP_POS(w) ((w) >> 16)
 
+// List decoders (int8): the host stores a dense handler id in bits 31..16 of every op word (`pos` is a Fast-SSC field), so
+// the kernel dispatches with one jump table.  regTop = highest stage held in registers (-1: none).
+enum SclHandler : uint32_t {
+    SCL_H_END = 0,
+    SCL_H_RS_F = 1, SCL_H_RS_G = 5, SCL_H_RS_C = 9, SCL_H_RS_R0 = 13, SCL_H_RS_REP = 17, SCL_H_RS_R1 = 21, SCL_H_RS_SPC = 25, // + (stage - 1)
+    SCL_H_F = 29, SCL_H_G, SCL_H_C, SCL_H_R0, SCL_H_REP, SCL_H_R1, SCL_H_SPC
+};
+inline uint32_t scl_handler_id(uint32_t op, int regTop)
+{
+    const uint32_t code = op & 63u, stage = (op >> 6) & 15u;
+    const bool rs = (int)stage <= regTop && stage >= 1;
+    switch (code) {
+    case OP_F: return rs ? SCL_H_RS_F + stage - 1 : SCL_H_F;
+    case OP_G: return rs ? SCL_H_RS_G + stage - 1 : SCL_H_G;
+    case OP_COMBINE: return rs ? SCL_H_RS_C + stage - 1 : SCL_H_C;
+    case OP_SCL_R0: return rs ? SCL_H_RS_R0 + stage - 1 : SCL_H_R0;
+    case OP_SCL_REP: return rs ? SCL_H_RS_REP + stage - 1 : SCL_H_REP;
+    case OP_SCL_R1: return rs ? SCL_H_RS_R1 + stage - 1 : SCL_H_R1;
+    case OP_SCL_SPC: return rs ? SCL_H_RS_SPC + stage - 1 : SCL_H_SPC;
+    }
+    return SCL_H_END;
+}
+
 static constexpr int MAX_OPS = 3072;
 struct Schedule {
     uint32_t ops[MAX_OPS];

@@ -55,8 +55,13 @@ struct SclCtx {
     uint32_t* sel;    // this lane's frame: select scratch (9 L words: candidate keys, swap history)
     int gl, fb;       // lane within the frame's group, first lane of the group
     int slotW, bitBW, bitB1, bitSlotW, lgN, smemStages;
+    int regTop;       // stages <= regTop (= min(4, lgN - 2)) live in the owning lane's registers
     int metric;
     unsigned long long llrPtr, lbPtr;
+    // register stages: LLR blocks of stage 4 / 3 / 2 / 1 in r[4..7] / r[2..3] / r[1] / r[0]; left-child bits of stage
+    // s in bits [2^s, 2^(s+1)) of ba; right-child bits of stage s in bb[s & 1]
+    uint32_t r[8];
+    uint32_t ba, bb[2];
 };
 
 POLAR_DEV void scl_set_own(unsigned long long& vec, int stage, int gl)
@@ -452,6 +457,99 @@ POLAR_DEV void scl_select(const SclCtx& c, const int (&cand)[FMAX], int lgF, int
     __syncwarp();
 }
 
+// Lists of at most 8 paths (M = P * F <= 64 candidates): the 32-bit key has room for the metric (|m| <= 128 N <= 2^19), the
+// CURRENT position (6 bits, inverted so that ties go to the lower position) and the ORIGINAL candidate index (6 bits), so
+// the winner of a step directly names the candidate it came from: no swap history, no walk back.  Steps are unrolled
+// (compile-time scratch addresses), the routine is compiled once per (L, fan-out) and called from every leaf handler.
+// Returns the key of list entry gl: metric = (key >> 12) - SCL_K32_BIAS, original candidate = key & 63.
+static constexpr int SCL_K32_BIAS = (1 << 20) - 1;
+template <int L, int LGF>
+__device__ __noinline__ uint32_t scl_select_k32(uint32_t* ks, int gl, int lgP, int nOut, int c0, int c1, int c2, int c3, int c4,
+                                                int c5, int c6, int c7)
+{
+    static_assert(L <= 8, "32-bit keys carry 6 + 6 position bits");
+    constexpr int F = 1 << LGF;
+    const int cand[8] = { c0, c1, c2, c3, c4, c5, c6, c7 };
+    uint32_t* mine = ks + (gl << LGF);
+    const bool act = gl < (1 << lgP);
+    uint32_t key[F];
+    uint32_t lmax = 0u;
+#pragma unroll
+    for (int k = 0; k < F; ++k) {
+        const uint32_t pos = (uint32_t)(gl << LGF) + k;
+        key[k] = act ? (((uint32_t)(cand[k] + SCL_K32_BIAS) << 12) | ((63u - pos) << 6) | pos) : 0u;
+        lmax = max(lmax, key[k]);
+    }
+    // the frame's scratch is aligned to L words (see setup_decoder_geometry), a lane's row to min(L, F) words
+    constexpr int VW = (L < F ? L : F) < 4 ? (L < F ? L : F) : 4;
+    if constexpr (VW == 4) {
+#pragma unroll
+        for (int k = 0; k < F; k += 4) *reinterpret_cast<uint4*>(mine + k) = make_uint4(key[k], key[k + 1], key[k + 2], key[k + 3]);
+    } else if constexpr (VW == 2) {
+#pragma unroll
+        for (int k = 0; k < F; k += 2) *reinterpret_cast<uint2*>(mine + k) = make_uint2(key[k], key[k + 1]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < F; ++k) mine[k] = key[k];
+    }
+    __syncwarp();
+    uint32_t outKey = 0u;
+#pragma unroll
+    for (int i = 0; i < L; ++i) {
+        if (i >= nOut) break;
+        const uint32_t best = list_max<L>(lmax);
+        if (gl == i) outKey = best;
+        const uint32_t pf = best & 0xFC0u; // (63 - position of the winner) << 6
+        const int pos = 63 - (int)(pf >> 6), wl = pos >> LGF;
+        const int il = i >> LGF;
+        const uint32_t ikey = ks[i]; // the element now at position i ...
+        __syncwarp();
+        if (gl == wl) ks[pos] = (ikey & ~0xFC0u) | pf; // ... moves to the winner's place
+        if (gl == il) ks[i] = 0u;                       // position i is final
+        __syncwarp();
+        if (gl == wl || gl == il) {
+            lmax = 0u;
+            if constexpr (VW == 4) {
+#pragma unroll
+                for (int k = 0; k < F; k += 4) {
+                    const uint4 a = *reinterpret_cast<const uint4*>(mine + k);
+                    lmax = max(max(lmax, a.x), max(max(a.y, a.z), a.w));
+                }
+            } else if constexpr (VW == 2) {
+#pragma unroll
+                for (int k = 0; k < F; k += 2) {
+                    const uint2 a = *reinterpret_cast<const uint2*>(mine + k);
+                    lmax = max(lmax, max(a.x, a.y));
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < F; ++k) lmax = max(lmax, mine[k]);
+            }
+        }
+    }
+    __syncwarp();
+    return outKey;
+}
+
+// Candidate pruning for any list size: 32-bit keys with the origin inside for L <= 8, the swap-history version above else.
+template <int L, int FMAX>
+POLAR_DEV void scl_prune(const SclCtx& c, const int (&cand)[FMAX], int lgF, int lgP, int nOut, int& outMet, int& outIdx)
+{
+    if constexpr (L <= 8) {
+        uint32_t k;
+        if constexpr (FMAX == 2) {
+            k = scl_select_k32<L, 1>(c.sel, c.gl, lgP, nOut, cand[0], cand[1], 0, 0, 0, 0, 0, 0);
+        } else {
+            if (lgF == 3) k = scl_select_k32<L, 3>(c.sel, c.gl, lgP, nOut, cand[0], cand[1], cand[2], cand[3], cand[4], cand[5], cand[6], cand[7]);
+            else k = scl_select_k32<L, 2>(c.sel, c.gl, lgP, nOut, cand[0], cand[1], cand[2], cand[3], 0, 0, 0, 0);
+        }
+        outMet = (int)(k >> 12) - SCL_K32_BIAS;
+        outIdx = (int)(k & 63u);
+    } else {
+        scl_select<L, FMAX>(c, cand, lgF, lgP, nOut, outMet, outIdx);
+    }
+}
+
 // After a fork: adopt the parent's lazy-copy vectors and metric.
 POLAR_DEV void scl_adopt(SclCtx& c, int outMet, int srcPath)
 {
@@ -534,7 +632,7 @@ POLAR_DEV void scl_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
     const int cand[2] = { c.metric + neg, c.metric - pos };
     const int lgPo = min(lgL, lgP + 1);
     int outMet, outIdx;
-    scl_select<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
+    scl_prune<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
     scl_adopt(c, outMet, (outIdx >> 1) & (L - 1));
     const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
     const int kq = lgGo ? __shfl_sync(FULL_MASK, outIdx & 1, c.fb + qo) : (outIdx & 1);
@@ -620,7 +718,7 @@ POLAR_DEV void scl_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSpc
     const int lgF = isSpc ? 3 : 2;
     const int lgPo = min(lgL, lgP + lgF);
     int outMet, outIdx;
-    scl_select<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
+    scl_prune<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
     const int srcPath = (outIdx >> lgF) & (L - 1), kind = outIdx & ((1 << lgF) - 1);
     const uint32_t s01 = __shfl_sync(FULL_MASK, pk01, c.fb + srcPath), s23 = __shfl_sync(FULL_MASK, pk23, c.fb + srcPath);
     const int sp = __shfl_sync(FULL_MASK, par, c.fb + srcPath);
@@ -684,9 +782,272 @@ POLAR_DEV void scl_extract_best_path(const DecodeParams& p, const SclCtx& c, uin
     }
 }
 
+// ---------------------------------------------------------------- register stages
+// Most nodes of a polar tree are small: at N = 1024, L = 8 (5G set) 171 of the 246 F / G / combine steps and 76 of the
+// 83 leaves work on blocks of at most 16 elements, always with lane = path.  Those blocks never touch shared memory:
+// a stage-s block (s <= 4) is 2^s int8 = at most four words of the owning lane's registers, its partial sums a bit
+// field of one register.  Every handler below is compiled per stage (compile-time word counts and register indices),
+// so a small step is its butterflies and nothing else; a fork moves the live register blocks with the lazy-copy
+// vectors (one shuffle per word).  Semantics: scl_fip_char.cpp:315-385 (inner nodes), :387-726 (leaves).
+template <int S> struct RegStage {
+    static_assert(S >= 1 && S <= 4, "register stages are 1..4");
+    static constexpr int W = S >= 2 ? 1 << (S - 2) : 1;             // words of the block
+    static constexpr int OFF = S == 4 ? 4 : S == 3 ? 2 : S == 2 ? 1 : 0;
+    static constexpr int NB = 1 << S;                                // elements = bits
+    static constexpr uint32_t MASK = (1u << NB) - 1u;
+    static constexpr uint32_t EMASK = S == 1 ? 0xFFFFu : 0xFFFFFFFFu; // valid bytes of word 0
+};
+
+// parent block (stage S + 1) of every path, split in halves: registers, or shared / spill / channel through the path's slot
+template <int S>
+POLAR_DEV void rs_load_parent(const SclCtx& c, uint32_t (&a)[RegStage<S>::W], uint32_t (&b)[RegStage<S>::W])
+{
+    constexpr int W = RegStage<S>::W;
+    bool inRegs = false;
+    if constexpr (S < 4) inRegs = S + 1 <= c.regTop;
+    if (inRegs) {
+        if constexpr (S == 1) {
+            a[0] = c.r[1];
+            b[0] = c.r[1] >> 16;
+        } else if constexpr (S < 4) {
+            constexpr int PO = RegStage<S + 1>::OFF;
+#pragma unroll
+            for (int w = 0; w < W; ++w) { a[w] = c.r[PO + w]; b[w] = c.r[PO + W + w]; }
+        }
+    } else {
+        const Words src = scl_llr_block(c, S + 1, (uint32_t)(c.llrPtr >> (5 * (S + 1))) & 31u);
+        if constexpr (S == 1) {
+            a[0] = src(0);
+            b[0] = a[0] >> 16;
+        } else {
+#pragma unroll
+            for (int w = 0; w < W; ++w) { a[w] = src(w); b[w] = src(w + W); }
+        }
+    }
+}
+
+template <int S, bool ISG>
+POLAR_DEV void rs_op_fg(SclCtx& c)
+{
+    constexpr int W = RegStage<S>::W, OFF = RegStage<S>::OFF;
+    uint32_t a[W], b[W];
+    rs_load_parent<S>(c, a, b);
+    if constexpr (ISG) {
+        const uint32_t lb = c.ba >> RegStage<S>::NB;
+#pragma unroll
+        for (int w = 0; w < W; ++w) c.r[OFF + w] = g4(a[w], b[w], nibble_to_msb(S == 1 ? (lb & 3u) : (lb >> (4 * w))));
+    } else {
+#pragma unroll
+        for (int w = 0; w < W; ++w) c.r[OFF + w] = f4(a[w], b[w]);
+    }
+}
+
+// bits of a finished stage-S node: left children wait in ba, right children go to the ping-pong pair
+template <int S>
+POLAR_DEV void rs_put_bits(SclCtx& c, uint32_t v, bool isRight)
+{
+    constexpr uint32_t M = RegStage<S>::MASK;
+    constexpr int NB = RegStage<S>::NB;
+    if (isRight) c.bb[S & 1] = v & M;
+    else c.ba = (c.ba & ~(M << NB)) | ((v & M) << NB);
+}
+
+template <int S>
+POLAR_DEV void rs_op_combine(SclCtx& c, bool isRight)
+{
+    constexpr int NB = RegStage<S>::NB;
+    const uint32_t l = (c.ba >> NB) & RegStage<S>::MASK, r = c.bb[S & 1];
+    const uint32_t out = (l ^ r) | (r << NB);
+    bool toRegs = false;
+    if constexpr (S < 4) toRegs = S + 1 <= c.regTop;
+    if (toRegs) {
+        if constexpr (S < 4) rs_put_bits<S + 1>(c, out, isRight);
+    } else { // the parent stage lives in shared memory (one word: S + 1 <= 5)
+        scl_bits_out(c, (uint32_t)c.gl, S + 1, isRight)[0] = out;
+        if (!isRight) scl_set_own(c.lbPtr, S + 1, c.gl);
+        __syncwarp();
+    }
+}
+
+// After a fork: adopt the parent's lazy-copy vectors, metric and the register blocks that are still live (stages > S).
+template <int S>
+POLAR_DEV void rs_adopt(SclCtx& c, int outMet, int srcPath)
+{
+    const int src = c.fb + srcPath;
+    c.metric = outMet;
+    c.llrPtr = shfl64(c.llrPtr, src);
+    c.lbPtr = shfl64(c.lbPtr, src);
+    c.ba = __shfl_sync(FULL_MASK, c.ba, src);
+#pragma unroll
+    for (int i = RegStage<S>::OFF + RegStage<S>::W; i < 8; ++i) // blocks of the stages above S sit behind it
+        if (i >= (S == 1 ? 1 : 0)) c.r[i] = __shfl_sync(FULL_MASK, c.r[i], src);
+}
+
+template <int L, int S>
+POLAR_DEV void rs_leaf_r0(SclCtx& c, bool isRight) // scl_fip_char.cpp:387-421
+{
+    constexpr int W = RegStage<S>::W, OFF = RegStage<S>::OFF;
+    int acc = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) acc = sum_neg4(c.r[OFF + w] & RegStage<S>::EMASK, acc);
+    c.metric += acc;
+    rs_put_bits<S>(c, 0u, isRight);
+}
+
+template <int L, int S>
+POLAR_DEV void rs_leaf_rep(SclCtx& c, int lgP, bool isRight) // scl_fip_char.cpp:508-581
+{
+    constexpr int lgL = Log2<L>::v, W = RegStage<S>::W, OFF = RegStage<S>::OFF;
+    int neg = 0, pos = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+        const uint32_t x = c.r[OFF + w] & RegStage<S>::EMASK;
+        neg = sum_neg4(x, neg);
+        pos = sum_pos4(x, pos);
+    }
+    const int cand[2] = { c.metric + neg, c.metric - pos };
+    const int lgPo = min(lgL, lgP + 1);
+    int outMet, outIdx;
+    scl_prune<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
+    rs_adopt<S>(c, outMet, (outIdx >> 1) & (L - 1));
+    rs_put_bits<S>(c, (outIdx & 1) ? 0xFFFFFFFFu : 0u, isRight);
+}
+
+// findWeakLlrs (arrayfuncs.h:209-231) on a block held in registers: the K smallest |max(llr,-127)| in the reference's
+// order, with their original positions.  Same emulation as scl_weak_search (only elements 0..3 can be displaced by
+// the swaps), fully unrolled.
+template <int S, int K>
+POLAR_DEV void rs_weak_search(const uint32_t (&x)[RegStage<S>::W], int (&val)[K], int (&idx)[K])
+{
+    constexpr int W = RegStage<S>::W, n = RegStage<S>::NB;
+    uint32_t m[W];
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+        m[w] = uabs4(x[w]);
+        m[w] -= (m[w] >> 7) & 0x01010101u; // |max(x,-127)| per byte
+    }
+    uint32_t tail[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) tail[r] = 0xFFFFFFFFu;
+#pragma unroll
+    for (int w = 1; w < W; ++w) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            uint32_t key = prmt(m[w], (uint32_t)(4 * w + e), 0x7054u | (e << 8)); // (|x_e| << 16) | position
+#pragma unroll
+            for (int r = 0; r < K; ++r) {
+                const uint32_t lo = min(tail[r], key);
+                key = max(tail[r], key);
+                tail[r] = lo;
+            }
+        }
+    }
+    int ha[4], cur[4];
+    bool alive[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        ha[e] = (int)((m[0] >> (8 * e)) & 0xFFu);
+        cur[e] = e;
+        alive[e] = e < n;
+    }
+    int t = 0;
+#pragma unroll
+    for (int i = 0; i < K; ++i) {
+        if (i < n) {
+            uint32_t best = 0xFFFFFFFFu;
+#pragma unroll
+            for (int r = 0; r < K; ++r)
+                if (r == t) best = tail[r];
+            int bw = -1;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const uint32_t key = ((uint32_t)ha[e] << 16) | (uint32_t)cur[e];
+                if (alive[e] && key < best) { best = key; bw = e; }
+            }
+            const int bpos = (int)(best & 0xFFFFu);
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (alive[e] && cur[e] == i) cur[e] = bpos; // the element at position i swaps out
+            if (bw >= 0) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (e == bw) alive[e] = false;
+                idx[i] = bw;
+            } else {
+                idx[i] = bpos;
+                ++t;
+            }
+            val[i] = (int)(best >> 16);
+        } else {
+            idx[i] = 0;
+            val[i] = 0;
+        }
+    }
+}
+
+// RateOne (scl_fip_char.cpp:423-505) and SPC (:583-726) on a register block
+template <int L, int S, bool SPC>
+POLAR_DEV void rs_leaf_flip(SclCtx& c, int lgP, bool isRight)
+{
+    constexpr int lgL = Log2<L>::v, W = RegStage<S>::W, OFF = RegStage<S>::OFF, lgF = SPC ? 3 : 2;
+    uint32_t x[W];
+    uint32_t px = 0, sgn = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+        x[w] = c.r[OFF + w];
+        if (S == 1) x[w] = (x[w] & 0xFFFFu) | 0x7F7F0000u; // the two missing elements never win the search
+        px ^= x[w];
+        sgn |= sign_nibble(x[w]) << (4 * w);
+    }
+    int par = __popc(px & 0x80808080u) & 1;
+    int val[4] = { 0, 0, 0, 0 }, idx[4] = { 0, 0, 0, 0 };
+    if (SPC) {
+        rs_weak_search<S, 4>(x, val, idx);
+    } else {
+        int v2[2], i2[2];
+        rs_weak_search<S, 2>(x, v2, i2);
+        val[0] = v2[0]; val[1] = v2[1];
+        idx[0] = i2[0]; idx[1] = i2[1];
+    }
+    const int a0 = val[0], a1 = val[1], a2 = val[2], a3 = val[3];
+    int m = c.metric, w = 0;
+    int cand[8];
+    if (SPC) {
+        if (par) m -= a0; else w = a0;
+        cand[0] = m;           cand[1] = m - w - a1;  cand[2] = m - w - a2;  cand[3] = m - w - a3;
+        cand[4] = m - a1 - a2; cand[5] = m - a1 - a3; cand[6] = m - a2 - a3; cand[7] = m - w - a1 - a2 - a3;
+    } else {
+        cand[0] = m; cand[1] = m - a0; cand[2] = m - a1; cand[3] = m - a0 - a1;
+        cand[4] = cand[5] = cand[6] = cand[7] = 0;
+    }
+    const int lgPo = min(lgL, lgP + lgF);
+    int outMet, outIdx;
+    scl_prune<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
+    const int srcPath = (outIdx >> lgF) & (L - 1), kind = outIdx & ((1 << lgF) - 1);
+    // what the new path needs from its parent: the four weak positions (4 bits each), the parity and the sign bits
+    const uint32_t mine = (uint32_t)idx[0] | ((uint32_t)idx[1] << 4) | ((uint32_t)idx[2] << 8) | ((uint32_t)idx[3] << 12) |
+                          ((uint32_t)par << 15 << 1) | (sgn << 17);
+    // (sgn has at most 16 bits, but 17 + 16 > 32: a 16-element block sends its top sign bit separately)
+    const uint32_t got = __shfl_sync(FULL_MASK, mine, c.fb + srcPath);
+    uint32_t v = got >> 17;
+    if constexpr (S == 4) v |= (__shfl_sync(FULL_MASK, sgn >> 15, c.fb + srcPath) & 1u) << 15;
+    const int sp = (got >> 16) & 1;
+    // flip sets over (i0,i1,i2,i3), one nibble per candidate kind (scl_fip_char.cpp:641-692; :451-470 for rate 1)
+    const uint32_t table = SPC ? (sp ? 0xEDB78421u : 0xFCA69530u) : 0x3210u;
+    const uint32_t fm = (table >> (4 * kind)) & 15u;
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+        if ((fm >> t) & 1u) v ^= 1u << ((got >> (4 * t)) & 15u);
+    rs_adopt<S>(c, outMet, srcPath);
+    rs_put_bits<S>(c, v, isRight);
+}
+
 // ---------------------------------------------------------------- the kernel
+#ifndef POLAR_SCL_MIN_BLOCKS
+#define POLAR_SCL_MIN_BLOCKS 1
+#endif
 template <int L>
-__global__ void __launch_bounds__(512) scl_i8_kernel(const __grid_constant__ DecodeParams p,
+__global__ void __launch_bounds__(512, POLAR_SCL_MIN_BLOCKS) scl_i8_kernel(const __grid_constant__ DecodeParams p,
                                                      const __grid_constant__ Schedule sched)
 {
     constexpr int lgL = Log2<L>::v, FPW = 32 / L;
@@ -708,6 +1069,11 @@ __global__ void __launch_bounds__(512) scl_i8_kernel(const __grid_constant__ Dec
     c.bitSlotW = p.bitSlotW;
     c.lgN = p.lgN;
     c.smemStages = p.smemStages;
+    c.regTop = p.regStages;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c.r[i] = 0u;
+    c.ba = 0u;
+    c.bb[0] = c.bb[1] = 0u;
 
     // Every warp of a block walks the same schedule, so the block iterates together (same trip count for all
     // its warps); with p.lockstep the warps also meet at a barrier before every step: they then fetch the
@@ -723,23 +1089,43 @@ __global__ void __launch_bounds__(512) scl_i8_kernel(const __grid_constant__ Dec
         c.llrPtr = 0ull;
         c.lbPtr = 0ull;
         int lgPfinal = 0;
+        const uint32_t lockMask = p.lockstep ? (uint32_t)p.lockstep - 1u : 0x7FFFFFFFu;
         for (int pc = 0;; ++pc) {
+            // op word of the list decoders: bits 31..16 hold a dense handler id written by the host (scl_handler_id): one
+            // jump table instead of nested switches on (code, stage)
             const uint32_t op = sched.ops[pc];
-            const uint32_t code = POLAR_OP_CODE(op);
-            if (code == OP_END) break;
+            const uint32_t hid = op >> 16;
+            if (hid == SCL_H_END) break;
             const int s = (int)POLAR_OP_STAGE(op), lgP = (int)POLAR_OP_LGP(op);
             const bool isRight = (POLAR_OP_FLAGS(op) & OPF_RIGHT) != 0;
-            if (p.lockstep && (pc & (p.lockstep - 1)) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
-            switch (code) {
-            case OP_F: scl_op_fg<L, false>(c, s, lgP); break;
-            case OP_G: scl_op_fg<L, true>(c, s, lgP); break;
-            case OP_COMBINE: scl_op_combine<L>(c, s, lgP, isRight); break;
-            case OP_SCL_R0: scl_leaf_r0<L>(c, s, lgP, isRight); lgPfinal = lgP; break;
-            case OP_SCL_REP: scl_leaf_rep<L>(c, s, lgP, isRight); lgPfinal = min(lgL, lgP + 1); break;
-            case OP_SCL_R1: scl_leaf_flip<L>(c, s, lgP, isRight, false); lgPfinal = min(lgL, lgP + 2); break;
-            case OP_SCL_SPC: scl_leaf_flip<L>(c, s, lgP, isRight, true); lgPfinal = min(lgL, lgP + 3); break;
+            if ((pc & lockMask) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
+#define POLAR_RS_CASES(BASE, CALL)                \
+    case BASE + 0: { constexpr int S = 1; CALL; } break; \
+    case BASE + 1: { constexpr int S = 2; CALL; } break; \
+    case BASE + 2: { constexpr int S = 3; CALL; } break; \
+    case BASE + 3: { constexpr int S = 4; CALL; } break;
+            switch (hid) {
+            // register stages: handlers compiled per stage, lane = path
+            POLAR_RS_CASES(SCL_H_RS_F, (rs_op_fg<S, false>(c)))
+            POLAR_RS_CASES(SCL_H_RS_G, (rs_op_fg<S, true>(c)))
+            POLAR_RS_CASES(SCL_H_RS_C, (rs_op_combine<S>(c, isRight)))
+            POLAR_RS_CASES(SCL_H_RS_R0, (rs_leaf_r0<L, S>(c, isRight)); lgPfinal = lgP)
+            POLAR_RS_CASES(SCL_H_RS_REP, (rs_leaf_rep<L, S>(c, lgP, isRight)); lgPfinal = min(lgL, lgP + 1))
+            POLAR_RS_CASES(SCL_H_RS_R1, (rs_leaf_flip<L, S, false>(c, lgP, isRight)); lgPfinal = min(lgL, lgP + 2))
+            case SCL_H_RS_SPC + 1: rs_leaf_flip<L, 2, true>(c, lgP, isRight); lgPfinal = min(lgL, lgP + 3); break; // an SPC leaf has >= 4 elements
+            case SCL_H_RS_SPC + 2: rs_leaf_flip<L, 3, true>(c, lgP, isRight); lgPfinal = min(lgL, lgP + 3); break;
+            case SCL_H_RS_SPC + 3: rs_leaf_flip<L, 4, true>(c, lgP, isRight); lgPfinal = min(lgL, lgP + 3); break;
+            // stages in shared memory / the L2 scratch / the channel row
+            case SCL_H_F: scl_op_fg<L, false>(c, s, lgP); break;
+            case SCL_H_G: scl_op_fg<L, true>(c, s, lgP); break;
+            case SCL_H_C: scl_op_combine<L>(c, s, lgP, isRight); break;
+            case SCL_H_R0: scl_leaf_r0<L>(c, s, lgP, isRight); lgPfinal = lgP; break;
+            case SCL_H_REP: scl_leaf_rep<L>(c, s, lgP, isRight); lgPfinal = min(lgL, lgP + 1); break;
+            case SCL_H_R1: scl_leaf_flip<L>(c, s, lgP, isRight, false); lgPfinal = min(lgL, lgP + 2); break;
+            case SCL_H_SPC: scl_leaf_flip<L>(c, s, lgP, isRight, true); lgPfinal = min(lgL, lgP + 3); break;
             default: break;
             }
+#undef POLAR_RS_CASES
         }
         scl_extract_best_path<L>(p, c, base, scr, lane, live, quad, lgPfinal);
     }

@@ -50,6 +50,8 @@ WORKLOADS = {
                       label="AdaptiveChar (Fast-SSC int8, SCL L=8 on CRC16 failures), N=1024 K=512, 5G frozen set, Eb/N0=2dB"),
     "scl32": dict(N=2048, K=1024, ctype="BB", L=32, crc=32, frames=1 << 16, e2e_frames=1 << 16, parity=1 << 13, cpu_s=4.0,
                   label="SCL L=32 + CRC32, N=2048 K=1024, BB frozen set, int8 LLR, Eb/N0=2dB"),
+    "scl8_n512": dict(N=512, K=256, ctype="BB", L=8, crc=16, frames=1 << 19, e2e_frames=1 << 17, parity=1 << 14, cpu_s=2.0,
+                      label="SCL L=8 + CRC16, N=512 K=256, BB frozen set, int8 LLR, Eb/N0=2dB (occupancy experiments)"),
     # pcbench-style comparability rows (benchmark/main_benchmark.cpp:202-241): iid N(0, 0.5) floats, not codewords, fed to the
     # int8 decoders through decode_vector(const float*), i.e. the quantiser runs inside the timed region
     "pcbench_scl8": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 18, e2e_frames=1 << 17, pcbench=True, parity=1 << 14, cpu_s=3.0,

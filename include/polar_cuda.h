@@ -111,6 +111,27 @@ int polar_cuda_depuncture_batch(polar_puncturer_t p, const void* in, int elemByt
 int polar_cuda_puncture_packed_batch(polar_puncturer_t p, const uint8_t* in, int mem, size_t nFrames, uint8_t* out,
                                      void* stream);
 
+/* On-device link simulator: the worker loop of the reference's pcsim (src/simulation/simulator.cpp:632-672) over batches of
+ * frames, every stage a kernel -- generateData (:850-868), encode (:870-879), BPSK / AWGN / amplifier / quantiser
+ * (:881-931, awgn.cpp:30-43, setChannel :821-841), decode (:919-935), countErrors (:937-964).  Nothing returns to the host
+ * between the stages.  The random streams are Philox4x32-10 keyed by (seed, point) and counted by the ABSOLUTE frame number,
+ * so frame f of a point is the same frame whatever the batch size or the number of GPUs sharing the point.
+ *   decoderKind   : any decoder kind; int8 kinds receive int8 LLRs = quantise(amplification * y), fp32 kinds amplification * y
+ *   amplification : pcsim's default is 10 for the 8-bit decoders (setup.cpp:58) and 4 * 10^(EbN0/10) for float (simulator.cpp:377)
+ *   counters_dev  : DEVICE pointer to 5 x uint64, ADDED to: runs, block errors, bit errors (over all K info bits, CRC
+ *                   included), reported errors (decode() == false), undetected errors (wrong block that passed the detector)
+ * sim_run is asynchronous on `stream`; read the counters after synchronising it.  sim_buffers returns the device buffers of
+ * the LAST batch (llr, sent info, decoded info, verdicts) for subsample checks; its return value is 1 if llr is float. */
+typedef struct polar_sim* polar_sim_t;
+int polar_cuda_sim_create(int device, int N, const uint32_t* frozen, int nFrozen, int decoderKind, int listSize, int systematic,
+                          int crcBits, size_t batchFrames, polar_sim_t* out);
+int polar_cuda_sim_destroy(polar_sim_t sim);
+int polar_cuda_sim_run(polar_sim_t sim, double ebn0_db, double amplification, uint64_t seed, uint32_t point, uint64_t firstFrame,
+                       size_t nFrames, unsigned long long* counters_dev, void* stream);
+int polar_cuda_sim_buffers(polar_sim_t sim, void** llr, uint8_t** sent, uint8_t** decoded, uint8_t** ok, size_t* frames);
+long polar_cuda_sim_launches(polar_sim_t sim, long* decoderLaunches);
+int polar_cuda_test_philox(const uint32_t* ctr, const uint32_t* key, uint32_t* out); /* Philox4x32-10 known-answer hook */
+
 /* Introspection for tests, bench and the roofline. */
 struct polar_code_info {
     int kind, N, K, listSize, systematic, crcBits;

@@ -17,8 +17,11 @@ rep, ksub = sys.argv[1], sys.argv[2]
 so = sys.argv[3] if len(sys.argv) > 3 else os.path.join(os.path.dirname(__file__), "..", "antpolarcodes_b200", "libpolar_cuda.so")
 tmp = tempfile.mkdtemp()
 subprocess.check_call(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, stdout=subprocess.DEVNULL)
-cubin = [f for f in os.listdir(tmp) if f.startswith("polar_cuda.") and f.endswith(".cubin")][0]
-dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
+dis = ""
+for cubin in sorted(f for f in os.listdir(tmp) if f.endswith(".cubin")):  # one cubin per translation unit
+    d = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
+    if ksub in d:
+        dis += d
 addr2line, cur, inside = {}, None, False
 for ln in dis.splitlines():
     if ln.startswith(".text."):
@@ -67,8 +70,8 @@ for k, v in per_line.items():
 stot = sum(samples.values()) or 1
 print("total warp-instructions: %d" % tot)
 print("--- per function (instr %, stall-sample %)")
-for k, v in per_func.most_common(25):
+for k, v in per_func.most_common(60):
     print("%6.2f%%  %6.2f%%  %s" % (100.0 * v / tot, 100.0 * fsamp[k] / stot, k))
 print("--- top lines")
-for k, v in per_line.most_common(40):
+for k, v in per_line.most_common(120):
     print("%6.2f%%  %6.2f%%  %s" % (100.0 * v / tot, 100.0 * samples[k] / stot, k))
