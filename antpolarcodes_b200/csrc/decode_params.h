@@ -29,6 +29,10 @@ struct DecodeParams {
     int smemStages;           // LLR stages [0, smemStages) live in shared memory, [smemStages, lgN) in `spill`
     int spillWarpW;           // words of `spill` per resident warp
     int lockstep;             // warps of a block meet at a barrier before every schedule step
+    int bitsOff, selOff;      // list decoders: word offsets of the bit slots / the select scratch inside a frame
+    int llrBase;              // int8 list decoder: llr_woff of the lowest stage kept in the shared-memory slots
+    int bitBase, bitSpill;    // list decoders: bit_woff of the lowest bit stage in shared memory; first bit stage in the L2 scratch
+    int spA, spB0, spB1;      // word offsets of the spilled bit regions inside the warp's scratch
     int regStages;            // int8 list decoder: stages <= regStages live in registers (min(4, lgN - 2), or -1: none)
     // Fast-SSC (one frame per thread): rows of 32 words
     int llrRows, bitRows, tileRow, outRow, chanRow, nRuns;

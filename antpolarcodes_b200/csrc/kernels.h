@@ -8,7 +8,7 @@ namespace polar {
 
 typedef void (*DecodeKernel)(const DecodeParams, const Schedule);
 
-DecodeKernel scl_i8_kernel_for(int listSize);        // SclFipChar;      nullptr if listSize is not a power of two <= 32
+DecodeKernel scl_i8_kernel_for(int listSize, int maxThreads); // SclFipChar; maxThreads = 512 / 768 / 1024 (register budget 128 / 80 / 64)
 DecodeKernel scl_f32_kernel_for(int listSize);       // SclAvxFloat
 DecodeKernel fastssc_i8_kernel_for(bool wide);       // FastSscFipChar   (wide: 16-warp blocks at 128 registers)
 DecodeKernel fastssc_f32_kernel_for(bool wide);      // FastSscAvxFloat

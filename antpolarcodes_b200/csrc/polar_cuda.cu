@@ -152,6 +152,7 @@ int setup_decoder_geometry(polar_code* c)
     g.lockstep = env_int("POLAR_CUDA_LOCKSTEP", c->kind == POLAR_KIND_FASTSSC_I8 ? 128 : c->kind == POLAR_KIND_SCL_F32 ? 8 : 64);
     if (g.lockstep & (g.lockstep - 1)) g.lockstep = 1; // the kernels test pc & (lockstep - 1)
     g.rootLeaf = 0;
+    g.llrBase = 0; g.bitBase = 0; g.bitSpill = c->lgN + 1; g.spA = g.spB0 = g.spB1 = 0;
     g.regStages = c->kind == POLAR_KIND_SCL_I8 ? std::min(env_int("POLAR_CUDA_REG_STAGES", 4), c->lgN - 2) : -1;
     g.bitB1 = 0;
     g.spillWarpW = 0;
@@ -178,28 +179,49 @@ int setup_decoder_geometry(polar_code* c)
         if (sclF32) // keep a warp's footprint within reach of a few resident warps per SM
             while (nSpill < c->lgN - 5 && (size_t)32 * f32_woff(c->lgN - nSpill) * 4 > 96 * 1024) ++nSpill;
         g.smemStages = c->lgN - nSpill;
-        int slot = sclF32 ? f32_woff(g.smemStages) : llr_woff(g.smemStages);
+        g.rootLeaf = (!c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN) ? 1 : 0;
+        // int8 lists: the stages <= regStages never touch shared memory, so the slots only hold the stages above them
+        const int firstSm = sclF32 ? 0 : std::max(0, g.regStages + 1);
+        g.llrBase = sclF32 ? 0 : llr_woff(firstSm);
+        int slot = sclF32 ? f32_woff(g.smemStages) : std::max(1, llr_woff(g.smemStages) - g.llrBase);
         while (slot % L != 1 % L) ++slot;
         g.slotW = slot;
-        g.rootLeaf = (!c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN) ? 1 : 0;
         const int nW = std::max(1, c->N / 32);
-        const int bitA = bit_woff(c->lgN) + (g.rootLeaf ? nW : 0);
         auto stageWords = [](int s) { return s >= 5 ? 1 << (s - 5) : 1; };
-        const int topEven = (c->lgN - 1) & ~1, topOdd = ((c->lgN - 1) & 1) ? c->lgN - 1 : c->lgN - 2;
+        // partial sums: the two top stages of a long int8 code (each used by one G step and one combine per frame) go to
+        // the L2 scratch next to the spilled LLR stages; with them gone the footprint is set by stages 5 .. lgN-3
+        const int nBitSpill = (sclF32 || g.rootLeaf || !nSpill) ? 0 : std::max(0, std::min(env_int("POLAR_CUDA_BIT_SPILL", c->lgN >= 10 ? 2 : 0), c->lgN - 6));
+        g.bitSpill = nBitSpill ? c->lgN - nBitSpill : c->lgN + 1;
+        const int topSm = std::min(c->lgN - 1, g.bitSpill - 1); // highest bit stage in shared memory
+        g.bitBase = bit_woff(firstSm);
+        const int bitA = bit_woff(topSm + 1) - g.bitBase + (g.rootLeaf ? nW : 0);
+        const int topEven = topSm & ~1, topOdd = (topSm & 1) ? topSm : topSm - 1;
         g.bitBW = bitA;
         g.bitB1 = stageWords(topEven);
         int bslot = bitA + stageWords(topEven) + stageWords(std::max(topOdd, 1));
         while (bslot % L != 1 % L) ++bslot;
         g.bitSlotW = bslot;
+        g.bitsOff = L * g.slotW;
+        g.selOff = L * g.slotW + L * g.bitSlotW;
         int frame = L * g.slotW + L * g.bitSlotW + (sclF32 ? 17 : 9) * L; // + select scratch (candidate keys, swap history)
         while (frame % 32 != L % 32) ++frame;
         g.frameW = frame;
         g.scratchW = 2 * ((c->K + 31) / 32) + nW + 4;
         g.warpW = ((32 / L) * g.frameW + g.scratchW + 3) & ~3;
-        if (nSpill)
-            g.spillWarpW = sclF32 ? 32 * ((1 << c->lgN) - (1 << g.smemStages))
-                                  : 32 * ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
-        c->kernel = sclF32 ? scl_f32_kernel_for(L) : scl_i8_kernel_for(L);
+        if (nSpill) {
+            int words = sclF32 ? ((1 << c->lgN) - (1 << g.smemStages)) : ((1 << (c->lgN - 2)) - (1 << (g.smemStages - 2)));
+            if (nBitSpill) { // region A of the spilled stages, then the even / odd ping-pong buffers of region B
+                const int top = c->lgN - 1, sEven = top & ~1, sOdd = (top & 1) ? top : top - 1;
+                g.spA = words;
+                words += (1 << (c->lgN - 5)) - (1 << (g.bitSpill - 5));
+                g.spB0 = words;
+                words += sEven >= g.bitSpill ? stageWords(sEven) : 0;
+                g.spB1 = words;
+                words += sOdd >= g.bitSpill ? stageWords(sOdd) : 0;
+            }
+            g.spillWarpW = 32 * words;
+        }
+        c->kernel = sclF32 ? scl_f32_kernel_for(L) : scl_i8_kernel_for(L, 512);
         if (!sclF32) // dense handler ids for the kernel's jump table (the fp32 kernel decodes (code, stage) itself)
             for (size_t i = 0; i < c->ops.size(); ++i)
                 c->sched.ops[i] = (c->ops[i] & 0xFFFFu) | (scl_handler_id(c->ops[i], g.regStages) << 16);
@@ -250,6 +272,32 @@ int setup_decoder_geometry(polar_code* c)
     }
     if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
     const size_t perWarp = (size_t)g.warpW * 4;
+    if (c->kind == POLAR_KIND_SCL_I8) {
+        // one block per SM (one lockstep domain), as many warps as the shared memory holds; the kernel exists in three
+        // register budgets (launch bounds 512 / 768 / 1024 threads = 128 / 80 / 64 registers)
+        if (perWarp > (size_t)prop.sharedMemPerBlockOptin)
+            return fail(POLAR_E_UNSUPPORTED, "code does not fit in shared memory (N x listSize too large)");
+        int w = (int)std::min<size_t>(prop.sharedMemPerBlockOptin / perWarp, 32);
+        w = std::min(w, env_int("POLAR_CUDA_SCL_MAX_WARPS", 24)); // 64 registers spill: 24 warps at 80 registers is the widest useful block
+        if (const int forceW = env_int("POLAR_CUDA_WARPS_PER_BLOCK", 0)) w = std::min(w, forceW);
+        const int maxT = w <= 16 ? 512 : w <= 24 ? 768 : 1024;
+        c->kernel = scl_i8_kernel_for(L, maxT);
+        CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)prop.sharedMemPerBlockOptin));
+        int nb = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)c->kernel, w * 32, perWarp * w));
+        if (nb < 1) return fail(POLAR_E_UNSUPPORTED, "kernel cannot be resident with this shared memory footprint");
+        // small codes: several such blocks fit; more than two lockstep domains per SM lose the shared instruction fetch
+        nb = std::min(nb, env_int("POLAR_CUDA_MAX_BLOCKS_PER_SM", w >= 16 ? 1 : 2));
+        c->warpsPerBlock = w;
+        c->blocksPerSM = nb;
+        c->smemPerBlock = perWarp * w;
+        if (g.spillWarpW) {
+            const size_t words = (size_t)g.spillWarpW * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
+            CUDA_TRY(cudaMalloc(&c->dSpill, words * sizeof(uint32_t)));
+        }
+        return POLAR_OK;
+    }
     if (perWarp > (size_t)prop.sharedMemPerBlockOptin)
         return fail(POLAR_E_UNSUPPORTED, "code does not fit in shared memory (N x listSize too large)");
     // The dynamic shared-memory limit belongs to the kernel FUNCTION on the device, not to this handle: it is raised

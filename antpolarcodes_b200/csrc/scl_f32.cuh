@@ -27,17 +27,17 @@ struct FWords {
     POLAR_DEV float operator()(int i) const { return cg ? __ldcg(p + i * stride) : p[i * stride]; }
 };
 
-POLAR_DEV int sclf_spill_woff(const SclCtx& c, int stage) { return ((1 << stage) - (1 << c.smemStages)) << 5; }
+POLAR_DEV int sclf_spill_woff(const SclCtx& c, int stage) { return ((1 << stage) - (1 << c.P.smemStages)) << 5; }
 POLAR_DEV FWords sclf_llr_block(const SclCtx& c, int stage, uint32_t slot)
 {
-    if (stage == c.lgN) return FWords{ reinterpret_cast<const float*>(c.chan), 1, false };
-    if (stage >= c.smemStages) return FWords{ reinterpret_cast<const float*>(c.spill + sclf_spill_woff(c, stage) + slot), 32, true };
-    return FWords{ reinterpret_cast<const float*>(c.llr + slot * c.slotW + f32_woff(stage)), 1, false };
+    if (stage == c.P.lgN) return FWords{ reinterpret_cast<const float*>(c.chan), 1, false };
+    if (stage >= c.P.smemStages) return FWords{ reinterpret_cast<const float*>(c.spill + sclf_spill_woff(c, stage) + slot), 32, true };
+    return FWords{ reinterpret_cast<const float*>(c.llrp() + slot * c.P.slotW + f32_woff(stage)), 1, false };
 }
 POLAR_DEV void sclf_store(const SclCtx& c, int stage, uint32_t slot, int i, float v)
 {
-    if (stage >= c.smemStages) __stcg(reinterpret_cast<float*>(c.spill + sclf_spill_woff(c, stage) + slot) + i * 32, v);
-    else reinterpret_cast<float*>(c.llr + slot * c.slotW + f32_woff(stage))[i] = v;
+    if (stage >= c.P.smemStages) __stcg(reinterpret_cast<float*>(c.spill + sclf_spill_woff(c, stage) + slot) + i * 32, v);
+    else reinterpret_cast<float*>(c.llrp() + slot * c.P.slotW + f32_woff(stage))[i] = v;
 }
 
 // monotone map float -> uint32 (no NaNs; -0.0 is canonicalised by the caller)
@@ -66,9 +66,9 @@ POLAR_DEV void sclf_op_fg(SclCtx& c, int s, int lgP)
 {
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
     const FWords src = sclf_llr_block(c, s + 1, scl_slot_of(c, c.llrPtr, s + 1, q, lgG));
-    const uint32_t* lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
+    const BitBlk lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
     int i = g;
-    if (s + 1 >= c.smemStages) { // parent block in the L2 scratch / global memory: 16 loads in flight
+    if (s + 1 >= c.P.smemStages) { // parent block in the L2 scratch / global memory: 16 loads in flight
         for (; i + 7 * G < n; i += 8 * G) {
             float a[8], b[8], r[8];
 #pragma unroll
@@ -76,7 +76,7 @@ POLAR_DEV void sclf_op_fg(SclCtx& c, int s, int lgP)
 #pragma unroll
             for (int t = 0; t < 8; ++t) {
                 const int it = i + t * G;
-                r[t] = ISG ? g_f32(a[t], b[t], (lb[it >> 5] >> (it & 31)) << 31) : f_f32(a[t], b[t]);
+                r[t] = ISG ? g_f32(a[t], b[t], (lb.ld(it >> 5) >> (it & 31)) << 31) : f_f32(a[t], b[t]);
             }
 #pragma unroll
             for (int t = 0; t < 8; ++t) sclf_store(c, s, (uint32_t)q, i + t * G, r[t]);
@@ -89,14 +89,14 @@ POLAR_DEV void sclf_op_fg(SclCtx& c, int s, int lgP)
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int it = i + t * G;
-            r[t] = ISG ? g_f32(a[t], b[t], (lb[it >> 5] >> (it & 31)) << 31) : f_f32(a[t], b[t]);
+            r[t] = ISG ? g_f32(a[t], b[t], (lb.ld(it >> 5) >> (it & 31)) << 31) : f_f32(a[t], b[t]);
         }
 #pragma unroll
         for (int t = 0; t < 4; ++t) sclf_store(c, s, (uint32_t)q, i + t * G, r[t]);
     }
     for (; i < n; i += G) {
         const float a = src(i), b = src(i + n);
-        sclf_store(c, s, (uint32_t)q, i, ISG ? g_f32(a, b, (lb[i >> 5] >> (i & 31)) << 31) : f_f32(a, b));
+        sclf_store(c, s, (uint32_t)q, i, ISG ? g_f32(a, b, (lb.ld(i >> 5) >> (i & 31)) << 31) : f_f32(a, b));
     }
     scl_set_own(c.llrPtr, s, c.gl);
     __syncwarp();
@@ -193,9 +193,9 @@ template <int L, int FMAX>
 POLAR_DEV void sclf_select(const SclCtx& c, const float (&cand)[FMAX], int lgF, int lgP, int nOut, float& outMet, int& outIdx)
 {
     const int gl = c.gl, F = 1 << lgF;
-    uint32_t* klo = c.sel;
-    uint32_t* khi = c.sel + 8 * L;
-    uint32_t* hs = c.sel + 16 * L;
+    uint32_t* klo = c.selp();
+    uint32_t* khi = c.selp() + 8 * L;
+    uint32_t* hs = c.selp() + 16 * L;
     const int row = gl << lgF;
     const bool act = gl < (1 << lgP);
     unsigned long long lmax = 0ull;
@@ -274,9 +274,9 @@ POLAR_DEV void sclf_leaf_r0(SclCtx& c, int s, int lgP, bool isRight)
     if (g == 0) pun = sclf_lane_reduce(src, n, [](float x) { return x < 0.0f ? x : 0.0f; });
     pun = __shfl_sync(FULL_MASK, pun, c.fb + ((c.gl << lgG) & (L - 1)));
     if (c.gl < (1 << lgP)) c.metric = __float_as_int(__fadd_rn(sclf_metric(c), pun));
-    uint32_t* out = scl_bits_out(c, q, s, isRight);
+    const BitBlk out = scl_bits_out(c, q, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
-    for (int j = g; j < nbw; j += G) out[j] = 0u;
+    for (int j = g; j < nbw; j += G) out.st(j, 0u);
     scl_finish_leaf(c, s, isRight);
 }
 
@@ -304,8 +304,8 @@ POLAR_DEV void sclf_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
     scl_adopt(c, __float_as_int(outMet), (outIdx >> 1) & (L - 1));
     const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
     const int kq = __shfl_sync(FULL_MASK, outIdx & 1, c.fb + qo);
-    uint32_t* out = scl_bits_out(c, qo, s, isRight);
-    if (go == 0) out[0] = kq ? (1u << n) - 1u : 0u;
+    const BitBlk out = scl_bits_out(c, qo, s, isRight);
+    if (go == 0) out.st(0, kq ? (1u << n) - 1u : 0u);
     scl_finish_leaf(c, s, isRight);
 }
 
@@ -371,7 +371,7 @@ POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSp
     const uint32_t fm = __shfl_sync(FULL_MASK, fmask, c.fb + qo);
     const uint32_t p01 = __shfl_sync(FULL_MASK, s01, c.fb + qo), p23 = __shfl_sync(FULL_MASK, s23, c.fb + qo);
     const FWords srcn = sclf_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo, lgGo));
-    uint32_t* out = scl_bits_out(c, qo, s, isRight);
+    const BitBlk out = scl_bits_out(c, qo, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     const uint32_t f[4] = { p01 & 0xFFFFu, p01 >> 16, p23 & 0xFFFFu, p23 >> 16 };
     for (int j = go; j < nbw; j += Go) {
@@ -379,7 +379,7 @@ POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSp
 #pragma unroll
         for (int t = 0; t < 4; ++t)
             if (((fm >> t) & 1u) && (int)f[t] < n && (int)(f[t] >> 5) == j) w ^= 1u << (f[t] & 31u);
-        out[j] = w;
+        out.st(j, w);
     }
     scl_finish_leaf(c, s, isRight);
 }
@@ -394,20 +394,12 @@ __global__ void __launch_bounds__(512) scl_f32_kernel(const __grid_constant__ De
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpsPerBlock = blockDim.x >> 5;
     uint32_t* base = smem + warp * p.warpW;
     uint32_t* scr = base + FPW * p.frameW;
-    SclCtx c;
+    SclCtx c{ p };
     c.gl = lane & (L - 1);
     c.fb = lane & ~(L - 1);
     const int fi = lane >> lgL;
-    c.llr = base + fi * p.frameW;
-    c.bits = c.llr + L * p.slotW;
-    c.sel = c.bits + L * p.bitSlotW;
+    c.frame = base + fi * p.frameW;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + c.fb : nullptr;
-    c.slotW = p.slotW;
-    c.bitBW = p.bitBW;
-    c.bitB1 = p.bitB1;
-    c.bitSlotW = p.bitSlotW;
-    c.lgN = p.lgN;
-    c.smemStages = p.smemStages;
 
     const long long nQuads = (p.nFrames + FPW - 1) / FPW;
     for (long long qb = blockIdx.x; qb * warpsPerBlock < nQuads; qb += gridDim.x) {

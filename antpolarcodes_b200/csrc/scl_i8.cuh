@@ -48,20 +48,22 @@ struct Words {
 };
 
 struct SclCtx {
+    const DecodeParams& P; // geometry is read where it is used: kernel parameters are constant-bank operands, not registers
     const uint32_t* chan; // this lane's frame: channel LLR row (global memory, read only)
-    uint32_t* llr;    // this lane's frame: LLR slots (shared memory)
-    uint32_t* bits;   // this lane's frame: bit slots (shared memory)
+    uint32_t* frame;  // this lane's frame in shared memory: LLR slots, bit slots, select scratch
     uint32_t* spill;  // this lane's frame: first column of the frame in the warp's spill scratch
-    uint32_t* sel;    // this lane's frame: select scratch (9 L words: candidate keys, swap history)
     int gl, fb;       // lane within the frame's group, first lane of the group
-    int slotW, bitBW, bitB1, bitSlotW, lgN, smemStages;
-    int regTop;       // stages <= regTop (= min(4, lgN - 2)) live in the owning lane's registers
     int metric;
     unsigned long long llrPtr, lbPtr;
-    // register stages: LLR blocks of stage 4 / 3 / 2 / 1 in r[4..7] / r[2..3] / r[1] / r[0]; left-child bits of stage
-    // s in bits [2^s, 2^(s+1)) of ba; right-child bits of stage s in bb[s & 1]
+    // register stages (stages <= P.regStages = min(4, lgN - 2) live in the owning lane's registers): LLR blocks of stage
+    // 4 / 3 / 2 / 1 in r[4..7] / r[2..3] / r[1] / r[0]; left-child bits of stage s in bits [2^s, 2^(s+1)) of ba;
+    // right-child bits of stage s in bb[s & 1]
     uint32_t r[8];
     uint32_t ba, bb[2];
+    // LLR slots (only the stages above the register stages: word llr_woff(s) - llrBase of a slot), bit slots, select scratch
+    POLAR_DEV uint32_t* llrp() const { return frame - P.llrBase; }
+    POLAR_DEV uint32_t* bitsp() const { return frame + P.bitsOff; }
+    POLAR_DEV uint32_t* selp() const { return frame + P.selOff; }
 };
 
 POLAR_DEV void scl_set_own(unsigned long long& vec, int stage, int gl)
@@ -83,22 +85,41 @@ POLAR_DEV uint32_t scl_slot_of(const SclCtx& c, unsigned long long vec, int stag
     return __shfl_sync(FULL_MASK, mine, c.fb + path);
 }
 // word offset of a spilled stage inside the warp's scratch ([word][lane] layout, 32 columns)
-POLAR_DEV int scl_spill_woff(const SclCtx& c, int stage) { return ((1 << (stage - 2)) - (1 << (c.smemStages - 2))) << 5; }
+POLAR_DEV int scl_spill_woff(const SclCtx& c, int stage) { return ((1 << (stage - 2)) - (1 << (c.P.smemStages - 2))) << 5; }
 // any LLR block through a generic pointer (leaves; the F/G steps use typed pointers)
 POLAR_DEV Words scl_llr_block(const SclCtx& c, int stage, uint32_t slot)
 {
-    if (stage == c.lgN) return Words{ c.chan, 1, false };
-    if (stage >= c.smemStages) return Words{ c.spill + scl_spill_woff(c, stage) + slot, 32, true };
-    return Words{ c.llr + slot * c.slotW + llr_woff(stage), 1, false };
+    if (stage == c.P.lgN) return Words{ c.chan, 1, false };
+    if (stage >= c.P.smemStages) return Words{ c.spill + scl_spill_woff(c, stage) + slot, 32, true };
+    return Words{ c.llrp() + slot * c.P.slotW + llr_woff(stage), 1, false };
 }
 // bit blocks: region A keeps every stage (left-child results wait there for the combine), region B is a
 // ping-pong pair (a right-child result is consumed by the very next combine)
-POLAR_DEV uint32_t* scl_bits_a(const SclCtx& c, uint32_t slot, int stage) { return c.bits + slot * c.bitSlotW + bit_woff(stage); }
-POLAR_DEV uint32_t* scl_bits_b(const SclCtx& c, uint32_t slot, int stage)
+// A block of packed partial sums: words of a shared-memory slot, or a column of the L2 scratch (stride 32, L2 only).
+struct BitBlk {
+    uint32_t* p;
+    bool g;
+    POLAR_DEV uint32_t ld(int j) const { return g ? __ldcg(p + (j << 5)) : p[j]; }
+    POLAR_DEV void st(int j, uint32_t v) const
+    {
+        if (g) __stcg(p + (j << 5), v);
+        else p[j] = v;
+    }
+};
+// (bits / spill = the frame's bit slots / first scratch column; the epilogue walks the frames of the warp with these)
+POLAR_DEV BitBlk scl_bits_a_at(const SclCtx& c, uint32_t* bits, uint32_t* spill, uint32_t slot, int stage)
 {
-    return c.bits + slot * c.bitSlotW + c.bitBW + ((stage & 1) ? c.bitB1 : 0);
+    if (stage >= c.P.bitSpill) return BitBlk{ spill + ((c.P.spA + (1 << (stage - 5)) - (1 << (c.P.bitSpill - 5))) << 5) + slot, true };
+    return BitBlk{ bits + slot * c.P.bitSlotW + bit_woff(stage) - c.P.bitBase, false };
 }
-POLAR_DEV uint32_t* scl_bits_out(const SclCtx& c, uint32_t slot, int stage, bool isRight)
+POLAR_DEV BitBlk scl_bits_b_at(const SclCtx& c, uint32_t* bits, uint32_t* spill, uint32_t slot, int stage)
+{
+    if (stage >= c.P.bitSpill) return BitBlk{ spill + (((stage & 1) ? c.P.spB1 : c.P.spB0) << 5) + slot, true };
+    return BitBlk{ bits + slot * c.P.bitSlotW + c.P.bitBW + ((stage & 1) ? c.P.bitB1 : 0), false };
+}
+POLAR_DEV BitBlk scl_bits_a(const SclCtx& c, uint32_t slot, int stage) { return scl_bits_a_at(c, c.bitsp(), c.spill, slot, stage); }
+POLAR_DEV BitBlk scl_bits_b(const SclCtx& c, uint32_t slot, int stage) { return scl_bits_b_at(c, c.bitsp(), c.spill, slot, stage); }
+POLAR_DEV BitBlk scl_bits_out(const SclCtx& c, uint32_t slot, int stage, bool isRight)
 {
     return isRight ? scl_bits_b(c, slot, stage) : scl_bits_a(c, slot, stage);
 }
@@ -177,7 +198,7 @@ POLAR_DEV void scl_f_words(const uint32_t* src, int ss, bool chan, uint32_t* dst
 }
 
 template <bool SG, bool DG>
-POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_t* lb, uint32_t* dst, int ds, int s,
+POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const BitBlk& lb, uint32_t* dst, int ds, int s,
                            int g, int G)
 {
     if (s >= 2) {
@@ -187,7 +208,7 @@ POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_
         if (G == 1 && SG) { // parent block in the L2 scratch / global memory: 16 loads in flight
             for (; w + 7 < words; w += 8) {
                 uint32_t a[8], b[8];
-                const uint32_t lw = lb[w >> 3];
+                const uint32_t lw = lb.ld(w >> 3);
 #pragma unroll
                 for (int t = 0; t < 8; ++t) {
                     a[t] = scl_ld<SG>(src + (w + t) * ss, chan);
@@ -200,7 +221,7 @@ POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_
         if (G == 1) { // a lane owns the path: the four words of a batch share one word of left bits
             for (; w + 3 < words; w += 4) {
                 uint32_t a[4], b[4];
-                const uint32_t lw = lb[w >> 3] >> ((w & 4) * 4);
+                const uint32_t lw = lb.ld(w >> 3) >> ((w & 4) * 4);
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
                     a[t] = scl_ld<SG>(src + (w + t) * ss, chan);
@@ -217,18 +238,18 @@ POLAR_DEV void scl_g_words(const uint32_t* src, int ss, bool chan, const uint32_
                 const int wt = w + t * G;
                 a[t] = scl_ld<SG>(src + wt * ss, chan);
                 b[t] = scl_ld<SG>(srcb + wt * ss, chan);
-                n[t] = lb[wt >> 3] >> ((wt & 7) * 4);
+                n[t] = lb.ld(wt >> 3) >> ((wt & 7) * 4);
             }
 #pragma unroll
             for (int t = 0; t < 4; ++t) scl_st<DG>(dst + (w + t * G) * ds, g4(a[t], b[t], nibble_to_msb(n[t])));
         }
         for (; w < words; w += G) {
-            const uint32_t nib = lb[w >> 3] >> ((w & 7) * 4);
+            const uint32_t nib = lb.ld(w >> 3) >> ((w & 7) * 4);
             scl_st<DG>(dst + w * ds, g4(scl_ld<SG>(src + w * ss, chan), scl_ld<SG>(srcb + w * ss, chan), nibble_to_msb(nib)));
         }
     } else if (g == 0) {
         const uint32_t x = scl_ld<SG>(src, chan);
-        scl_st<DG>(dst, g4(x, x >> 16, nibble_to_msb(lb[0] & 3u)));
+        scl_st<DG>(dst, g4(x, x >> 16, nibble_to_msb(lb.ld(0) & 3u)));
     }
 }
 
@@ -238,19 +259,19 @@ POLAR_DEV void scl_op_fg(SclCtx& c, int s, int lgP)
 {
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
     const uint32_t slot = scl_slot_of(c, c.llrPtr, s + 1, q, lgG);
-    const uint32_t* lb = nullptr;
+    BitBlk lb{ nullptr, false };
     if (ISG) lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
-    if (s + 1 < c.smemStages) { // shared -> shared: the bulk of the steps
-        const uint32_t* src = c.llr + slot * c.slotW + llr_woff(s + 1);
-        uint32_t* dst = c.llr + q * c.slotW + llr_woff(s);
+    if (s + 1 < c.P.smemStages) { // shared -> shared: the bulk of the steps
+        const uint32_t* src = c.llrp() + slot * c.P.slotW + llr_woff(s + 1);
+        uint32_t* dst = c.llrp() + q * c.P.slotW + llr_woff(s);
         if (ISG) scl_g_words<false, false>(src, 1, false, lb, dst, 1, s, g, G);
         else scl_f_words<false, false>(src, 1, false, dst, 1, s, g, G);
     } else {
-        const bool chan = (s + 1 == c.lgN);
+        const bool chan = (s + 1 == c.P.lgN);
         const uint32_t* src = chan ? c.chan : c.spill + scl_spill_woff(c, s + 1) + slot;
         const int ss = chan ? 1 : 32;
-        if (s < c.smemStages) {
-            uint32_t* dst = c.llr + q * c.slotW + llr_woff(s);
+        if (s < c.P.smemStages) {
+            uint32_t* dst = c.llrp() + q * c.P.slotW + llr_woff(s);
             if (ISG) scl_g_words<true, false>(src, ss, chan, lb, dst, 1, s, g, G);
             else scl_f_words<true, false>(src, ss, chan, dst, 1, s, g, G);
         } else {
@@ -266,21 +287,21 @@ POLAR_DEV void scl_op_fg(SclCtx& c, int s, int lgP)
 template <int L>
 POLAR_DEV void scl_op_combine(SclCtx& c, int s, int lgP, bool isRight)
 {
-    if (s + 1 == c.lgN) return; // the root is assembled by the epilogue, straight from its two halves
+    if (s + 1 == c.P.lgN) return; // the root is assembled by the epilogue, straight from its two halves
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1);
-    const uint32_t* left = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
-    const uint32_t* right = scl_bits_b(c, q, s);
-    uint32_t* out = scl_bits_out(c, q, s + 1, isRight);
+    const BitBlk left = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
+    const BitBlk right = scl_bits_b(c, q, s);
+    const BitBlk out = scl_bits_out(c, q, s + 1, isRight);
     if (s >= 5) {
         const int hw = 1 << (s - 5);
         for (int j = g; j < hw; j += G) {
-            const uint32_t l = left[j], r = right[j];
-            out[j] = l ^ r;
-            out[j + hw] = r;
+            const uint32_t l = left.ld(j), r = right.ld(j);
+            out.st(j, l ^ r);
+            out.st(j + hw, r);
         }
     } else if (g == 0) {
-        const uint32_t l = left[0], r = right[0];
-        out[0] = (l ^ r) | (r << (1 << s));
+        const uint32_t l = left.ld(0), r = right.ld(0);
+        out.st(0, (l ^ r) | (r << (1 << s)));
     }
     if (!isRight) scl_set_own(c.lbPtr, s + 1, c.gl);
     __syncwarp();
@@ -385,8 +406,8 @@ template <int L, int FMAX>
 POLAR_DEV void scl_select(const SclCtx& c, const int (&cand)[FMAX], int lgF, int lgP, int nOut, int& outMet, int& outIdx)
 {
     const int gl = c.gl, F = 1 << lgF;
-    uint32_t* ks = c.sel;          // L * 8 key words, ks[position]
-    uint32_t* hs = c.sel + 8 * L;  // L history words
+    uint32_t* ks = c.selp();          // L * 8 key words, ks[position]
+    uint32_t* hs = c.selp() + 8 * L;  // L history words
     uint32_t* mine = ks + (gl << lgF);
     constexpr bool V4 = (FMAX >= 4 && L >= 4), V2 = (FMAX == 2 && L >= 2); // the lane's row is 16 / 8 byte aligned
     const bool act = gl < (1 << lgP);
@@ -538,10 +559,10 @@ POLAR_DEV void scl_prune(const SclCtx& c, const int (&cand)[FMAX], int lgF, int 
     if constexpr (L <= 8) {
         uint32_t k;
         if constexpr (FMAX == 2) {
-            k = scl_select_k32<L, 1>(c.sel, c.gl, lgP, nOut, cand[0], cand[1], 0, 0, 0, 0, 0, 0);
+            k = scl_select_k32<L, 1>(c.selp(), c.gl, lgP, nOut, cand[0], cand[1], 0, 0, 0, 0, 0, 0);
         } else {
-            if (lgF == 3) k = scl_select_k32<L, 3>(c.sel, c.gl, lgP, nOut, cand[0], cand[1], cand[2], cand[3], cand[4], cand[5], cand[6], cand[7]);
-            else k = scl_select_k32<L, 2>(c.sel, c.gl, lgP, nOut, cand[0], cand[1], cand[2], cand[3], 0, 0, 0, 0);
+            if (lgF == 3) k = scl_select_k32<L, 3>(c.selp(), c.gl, lgP, nOut, cand[0], cand[1], cand[2], cand[3], cand[4], cand[5], cand[6], cand[7]);
+            else k = scl_select_k32<L, 2>(c.selp(), c.gl, lgP, nOut, cand[0], cand[1], cand[2], cand[3], 0, 0, 0, 0);
         }
         outMet = (int)(k >> 12) - SCL_K32_BIAS;
         outIdx = (int)(k & 63u);
@@ -595,9 +616,9 @@ POLAR_DEV void scl_leaf_r0(SclCtx& c, int s, int lgP, bool isRight)
     acc = group_add(acc, lgG);
     const int pun = lgG ? __shfl_sync(FULL_MASK, acc, c.fb + ((c.gl << lgG) & (L - 1))) : acc;
     if (c.gl < (1 << lgP)) c.metric += pun;
-    uint32_t* out = scl_bits_out(c, q, s, isRight);
+    const BitBlk out = scl_bits_out(c, q, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
-    for (int j = g; j < nbw; j += G) out[j] = 0u;
+    for (int j = g; j < nbw; j += G) out.st(j, 0u);
     scl_finish_leaf(c, s, isRight);
 }
 
@@ -636,10 +657,10 @@ POLAR_DEV void scl_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
     scl_adopt(c, outMet, (outIdx >> 1) & (L - 1));
     const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
     const int kq = lgGo ? __shfl_sync(FULL_MASK, outIdx & 1, c.fb + qo) : (outIdx & 1);
-    uint32_t* out = scl_bits_out(c, qo, s, isRight);
+    const BitBlk out = scl_bits_out(c, qo, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     const uint32_t full = s >= 5 ? 0xFFFFFFFFu : (1u << (1 << s)) - 1u;
-    for (int j = go; j < nbw; j += Go) out[j] = kq ? full : 0u;
+    for (int j = go; j < nbw; j += Go) out.st(j, kq ? full : 0u);
     scl_finish_leaf(c, s, isRight);
 }
 
@@ -656,7 +677,7 @@ POLAR_DEV void scl_write_flipped(SclCtx& c, int s, int lgPo, bool isRight, uint3
         p23 = __shfl_sync(FULL_MASK, p23, c.fb + qo);
     }
     const Words srcn = scl_llr_block(c, s, scl_slot_of(c, c.llrPtr, s, qo, lgGo)); // through the adopted vector
-    uint32_t* out = scl_bits_out(c, qo, s, isRight);
+    const BitBlk out = scl_bits_out(c, qo, s, isRight);
     const int nbw = s >= 5 ? 1 << (s - 5) : 1;
     const uint32_t f[4] = { p01 & 0xFFFFu, p01 >> 16, p23 & 0xFFFFu, p23 >> 16 };
     for (int j = go; j < nbw; j += Go) {
@@ -664,7 +685,7 @@ POLAR_DEV void scl_write_flipped(SclCtx& c, int s, int lgPo, bool isRight, uint3
 #pragma unroll
         for (int t = 0; t < 4; ++t)
             if (((fm >> t) & 1u) && (int)(f[t] >> 5) == j) w ^= 1u << (f[t] & 31u);
-        out[j] = w;
+        out.st(j, w);
     }
     scl_finish_leaf(c, s, isRight);
 }
@@ -744,22 +765,23 @@ POLAR_DEV void scl_extract_best_path(const DecodeParams& p, const SclCtx& c, uin
     for (int f = 0; f < FPW && live; ++f) {
         const long long frame = quad * FPW + f;
         if (frame >= p.nFrames) break;
-        const uint32_t* fbits = base + f * p.frameW + L * p.slotW;
+        uint32_t* fbits = base + f * p.frameW + L * p.slotW;
+        uint32_t* fspill = c.spill - c.fb + f * L; // first scratch column of frame f
         bool okFlag = false;
         for (int path = 0; path < P; ++path) {
             // codeword estimate of this path: the root leaf's bits, or [left ^ right | right] of the two halves
             const uint32_t sa = __shfl_sync(FULL_MASK, slotA, f * L + path);
             if (p.rootLeaf) {
-                const uint32_t* root = fbits + path * p.bitSlotW + bit_woff(p.lgN);
-                for (int w = lane; w < nW; w += 32) cw[w] = root[w];
+                const BitBlk root = scl_bits_a_at(c, fbits, fspill, path, p.lgN);
+                for (int w = lane; w < nW; w += 32) cw[w] = root.ld(w);
             } else {
-                const uint32_t* left = fbits + sa * p.bitSlotW + bit_woff(top);
-                const uint32_t* right = fbits + path * p.bitSlotW + p.bitBW + ((top & 1) ? p.bitB1 : 0);
+                const BitBlk left = scl_bits_a_at(c, fbits, fspill, sa, top);
+                const BitBlk right = scl_bits_b_at(c, fbits, fspill, path, top);
                 if (top >= 5) {
                     const int hw = 1 << (top - 5);
-                    for (int w = lane; w < nW; w += 32) cw[w] = w < hw ? (left[w] ^ right[w]) : right[w - hw];
+                    for (int w = lane; w < nW; w += 32) cw[w] = w < hw ? (left.ld(w) ^ right.ld(w)) : right.ld(w - hw);
                 } else if (lane == 0) {
-                    cw[0] = (left[0] ^ right[0]) | (right[0] << (1 << top));
+                    cw[0] = (left.ld(0) ^ right.ld(0)) | (right.ld(0) << (1 << top));
                 }
             }
             __syncwarp();
@@ -804,7 +826,7 @@ POLAR_DEV void rs_load_parent(const SclCtx& c, uint32_t (&a)[RegStage<S>::W], ui
 {
     constexpr int W = RegStage<S>::W;
     bool inRegs = false;
-    if constexpr (S < 4) inRegs = S + 1 <= c.regTop;
+    if constexpr (S < 4) inRegs = S + 1 <= c.P.regStages;
     if (inRegs) {
         if constexpr (S == 1) {
             a[0] = c.r[1];
@@ -859,11 +881,11 @@ POLAR_DEV void rs_op_combine(SclCtx& c, bool isRight)
     const uint32_t l = (c.ba >> NB) & RegStage<S>::MASK, r = c.bb[S & 1];
     const uint32_t out = (l ^ r) | (r << NB);
     bool toRegs = false;
-    if constexpr (S < 4) toRegs = S + 1 <= c.regTop;
+    if constexpr (S < 4) toRegs = S + 1 <= c.P.regStages;
     if (toRegs) {
         if constexpr (S < 4) rs_put_bits<S + 1>(c, out, isRight);
     } else { // the parent stage lives in shared memory (one word: S + 1 <= 5)
-        scl_bits_out(c, (uint32_t)c.gl, S + 1, isRight)[0] = out;
+        scl_bits_out(c, (uint32_t)c.gl, S + 1, isRight).st(0, out);
         if (!isRight) scl_set_own(c.lbPtr, S + 1, c.gl);
         __syncwarp();
     }
@@ -1043,11 +1065,10 @@ POLAR_DEV void rs_leaf_flip(SclCtx& c, int lgP, bool isRight)
 }
 
 // ---------------------------------------------------------------- the kernel
-#ifndef POLAR_SCL_MIN_BLOCKS
-#define POLAR_SCL_MIN_BLOCKS 1
-#endif
-template <int L>
-__global__ void __launch_bounds__(512, POLAR_SCL_MIN_BLOCKS) scl_i8_kernel(const __grid_constant__ DecodeParams p,
+// MAXT: launch bound = register budget (512 threads: 128 registers, 768: 80, 1024: 64); the host picks the variant that
+// gives the most resident warps for the code's shared-memory footprint
+template <int L, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) scl_i8_kernel(const __grid_constant__ DecodeParams p,
                                                      const __grid_constant__ Schedule sched)
 {
     constexpr int lgL = Log2<L>::v, FPW = 32 / L;
@@ -1055,21 +1076,12 @@ __global__ void __launch_bounds__(512, POLAR_SCL_MIN_BLOCKS) scl_i8_kernel(const
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpsPerBlock = blockDim.x >> 5;
     uint32_t* base = smem + warp * p.warpW;
     uint32_t* scr = base + FPW * p.frameW;
-    SclCtx c;
+    SclCtx c{ p };
     c.gl = lane & (L - 1);
     c.fb = lane & ~(L - 1);
     const int fi = lane >> lgL;
-    c.llr = base + fi * p.frameW;
-    c.bits = c.llr + L * p.slotW;
-    c.sel = c.bits + L * p.bitSlotW;
+    c.frame = base + fi * p.frameW;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + c.fb : nullptr;
-    c.slotW = p.slotW;
-    c.bitBW = p.bitBW;
-    c.bitB1 = p.bitB1;
-    c.bitSlotW = p.bitSlotW;
-    c.lgN = p.lgN;
-    c.smemStages = p.smemStages;
-    c.regTop = p.regStages;
 #pragma unroll
     for (int i = 0; i < 8; ++i) c.r[i] = 0u;
     c.ba = 0u;
