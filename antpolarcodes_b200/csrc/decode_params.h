@@ -8,6 +8,8 @@ struct DecodeParams {
     const void* llr;          // nFrames x N int8 (float inputs are quantised by a pre-pass)
     uint8_t* out;             // nFrames x kb
     uint8_t* ok;              // nFrames
+    uint8_t* cand;            // list decoders, candidate hand-back: nFrames x listSize x kb (all surviving paths in list
+                              // order, no detector on the device; ok[] then holds the number of paths), else null
     const uint16_t* infoPos;  // K code positions of the information bits, ascending
     const uint32_t* crcTab;   // K syndrome contributions (see crc_host.h)
     const uint32_t* runs;     // Fast-SSC: runs of consecutive information positions (pos | len << 16)

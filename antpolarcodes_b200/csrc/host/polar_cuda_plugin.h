@@ -43,30 +43,47 @@ inline void check(int rc)
     throw std::runtime_error(msg);
 }
 
-// CRC width the kernels fuse for this detector: Dummy -> 0, CRC8/16/32 -> 8/16/32.  Anything else (CMAC) has no
-// device implementation.
+// CRC width the kernels fuse for this detector: Dummy -> 0, CRC8/16/32 -> 8/16/32.  Anything else (the reference's cmac,
+// a user's own Detector subclass) returns -1: the decoders then hand all surviving candidates back and the detector
+// runs on the host, in list order, exactly like extractBestPath (scl_fip_char.cpp:816-855).
 inline int fusedCrcBits(ErrorDetection::Detector* d)
 {
     const std::string type = d->getType();
     const unsigned bits = d->getCheckBitCount();
-    if (bits == 0) return 0;
+    if (bits == 0 && type == "DUMMY") return 0;
     if (type == "CRC" && (bits == 8 || bits == 16 || bits == 32)) return (int)bits;
-    throw std::runtime_error("polar_cuda: error detector " + type + "-" + std::to_string(bits) + " is not fused on the GPU");
+    return -1;
 }
+
+// Decoder::getSoftCodeword / getSoftInformation read mBitContainer (decoder.cpp:147-152).  The kernels keep partial sums
+// as packed sign bits and never fill a byte / float container, so a CUDA decoder's bit container refuses instead of
+// returning stale memory.
+template <class Base>
+class NoSoftBits : public Base
+{
+public:
+    using Base::Base;
+    void getSoftBits(void*) override { throw std::logic_error("polar_cuda: soft outputs are not produced by the GPU decoders"); }
+    void getSoftInformation(void*) override { throw std::logic_error("polar_cuda: soft outputs are not produced by the GPU decoders"); }
+};
 
 // A compiled code handle plus the configuration it was compiled for.
 struct Handle {
     polar_code_t code = nullptr;
     int sys = -1, crc = -1;
     ~Handle() { if (code) polar_cuda_code_destroy(code); }
+    bool hostDetector() const { return crc < 0; }
     polar_code_t get(int device, int kind, size_t N, const std::vector<unsigned>& frozen, size_t L, bool systematic,
                      ErrorDetection::Detector* det)
     {
         const int crcBits = fusedCrcBits(det);
         if (code && sys == (int)systematic && crc == crcBits) return code;
         if (code) { polar_cuda_code_destroy(code); code = nullptr; }
+        if (crcBits < 0 && (kind == POLAR_KIND_ENC || kind >= POLAR_KIND_ADAPTIVE_I8))
+            throw std::runtime_error("polar_cuda: error detector " + det->getType() + "-" + std::to_string(det->getCheckBitCount()) +
+                                     " is not fused on the GPU (encoders and adaptive decoders need CRC8/16/32 or none)");
         check(polar_cuda_code_create(device, kind, (int)N, frozen.data(), (int)frozen.size(), (int)L, systematic ? 1 : 0,
-                                     crcBits, &code));
+                                     crcBits < 0 ? 0 : crcBits, &code));
         sys = (int)systematic;
         crc = crcBits;
         return code;
@@ -116,10 +133,10 @@ public:
         delete[] mOutputContainer;
         if (FLOAT) {
             mLlrContainer = new FloatContainer(blockLength);
-            mBitContainer = new FloatContainer(blockLength, mFrozenBits);
+            mBitContainer = new CudaDetail::NoSoftBits<FloatContainer>(blockLength, mFrozenBits);
         } else {
             mLlrContainer = new CharContainer(blockLength);
-            mBitContainer = new CharContainer(blockLength, mFrozenBits);
+            mBitContainer = new CudaDetail::NoSoftBits<CharContainer>(blockLength, mFrozenBits);
         }
         mOutputContainer = new unsigned char[(blockLength - frozenBits.size() + 7) / 8];
         mHandle.sys = -1; // force a rebuild
@@ -127,13 +144,36 @@ public:
 
     size_t getListSize() override { return mListSize; }
 
+    // A detector the kernels do not fuse: all candidates of every frame come back, Detector::check runs here in list
+    // order; the first passing candidate wins, else candidate 0 and verdict false (scl_fip_char.cpp:816-855).
+    void decodeWithHostDetector(const void* llr, int llrType, size_t nFrames, unsigned char* info, unsigned char* ok)
+    {
+        const size_t kb = (mBlockLength - mFrozenBits.size() + 7) / 8, L = mListSize > 1 ? mListSize : 1;
+        std::vector<unsigned char> cand(nFrames * L * kb), count(nFrames);
+        CudaDetail::check(polar_cuda_decode_candidates(code(), llr, llrType, POLAR_MEM_HOST, nFrames, cand.data(), count.data(), nullptr));
+        for (size_t f = 0; f < nFrames; ++f) {
+            unsigned char* c0 = cand.data() + f * L * kb;
+            size_t pick = 0;
+            bool pass = false;
+            for (size_t path = 0; path < count[f] && !pass; ++path)
+                if (mErrorDetector->check(c0 + path * kb, (int)kb)) { pick = path; pass = true; }
+            memcpy(info + f * kb, c0 + pick * kb, kb);
+            if (ok) ok[f] = pass ? 1 : 0;
+        }
+    }
+
     // Decoder::decode(): the frame setSignal() left in mLlrContainer, a batch of one.
     bool decode() override
     {
         uint8_t ok = 0;
         const void* llr = FLOAT ? static_cast<const void*>(static_cast<FloatContainer*>(mLlrContainer)->data())
                                 : static_cast<const void*>(static_cast<CharContainer*>(mLlrContainer)->data());
-        CudaDetail::check(polar_cuda_decode_batch(code(), llr, FLOAT ? POLAR_LLR_F32 : POLAR_LLR_I8, POLAR_MEM_HOST, 1,
+        polar_code_t h = code();
+        if (mHandle.hostDetector()) {
+            decodeWithHostDetector(llr, FLOAT ? POLAR_LLR_F32 : POLAR_LLR_I8, 1, mOutputContainer, &ok);
+            return ok != 0;
+        }
+        CudaDetail::check(polar_cuda_decode_batch(h, llr, FLOAT ? POLAR_LLR_F32 : POLAR_LLR_I8, POLAR_MEM_HOST, 1,
                                                   mOutputContainer, &ok, nullptr));
         return ok != 0;
     }
@@ -147,14 +187,24 @@ public:
                       void* stream = nullptr)
     {
         if (FLOAT) throw std::invalid_argument("a float decoder takes float LLRs");
-        CudaDetail::check(polar_cuda_decode_batch(code(), llr, POLAR_LLR_I8, deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
+        polar_code_t h = code();
+        if (mHandle.hostDetector()) {
+            if (deviceBuffers) throw std::invalid_argument("a host-side detector needs host buffers");
+            return decodeWithHostDetector(llr, POLAR_LLR_I8, nFrames, info, ok);
+        }
+        CudaDetail::check(polar_cuda_decode_batch(h, llr, POLAR_LLR_I8, deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
                                                   nFrames, info, ok, stream));
     }
     // float LLRs into a char decoder are quantised on the device like CharContainer::insertLlr(const float*)
     void decode_batch(const float* llr, size_t nFrames, unsigned char* info, unsigned char* ok, bool deviceBuffers = false,
                       void* stream = nullptr)
     {
-        CudaDetail::check(polar_cuda_decode_batch(code(), llr, POLAR_LLR_F32, deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
+        polar_code_t h = code();
+        if (mHandle.hostDetector()) {
+            if (deviceBuffers) throw std::invalid_argument("a host-side detector needs host buffers");
+            return decodeWithHostDetector(llr, POLAR_LLR_F32, nFrames, info, ok);
+        }
+        CudaDetail::check(polar_cuda_decode_batch(h, llr, POLAR_LLR_F32, deviceBuffers ? POLAR_MEM_DEVICE : POLAR_MEM_HOST,
                                                   nFrames, info, ok, stream));
     }
 };
@@ -222,6 +272,22 @@ inline Decoder* makeCudaDecoder(size_t blockLength, size_t listSize, const std::
     }
     dec->setErrorDetection(new ErrorDetection::CRC8());
     return dec;
+}
+
+// Decoding::create (decoder.cpp:26-48) with the GPU types added: "cuda-char", "cuda-float", "cuda-mixed" select the classes
+// above, every other string goes to the reference's own factory.  This is the function the pybind11 module binds as
+// PolarDecoder's constructor.
+inline Decoder* createWithCuda(size_t blockLength, size_t listSize, const std::vector<unsigned>& frozenBits,
+                               std::string decoderType)
+{
+    if (decoderType.rfind("cuda", 0) != 0) return create(blockLength, listSize, frozenBits, decoderType);
+    int impl;
+    if (decoderType.find("char") != std::string::npos) impl = 0;
+    else if (decoderType.find("float") != std::string::npos) impl = 1;
+    else if (decoderType.find("mixed") != std::string::npos) impl = 2;
+    else throw std::invalid_argument("Unknown PolarDecoder type!");
+    if (listSize < 2) listSize = 1;
+    return makeCudaDecoder(blockLength, listSize, frozenBits, impl);
 }
 
 } // namespace Decoding

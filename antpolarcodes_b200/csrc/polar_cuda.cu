@@ -547,9 +547,10 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
 
 // One batch with DEVICE buffers on stream st: optional quantiser pre-pass + the decoder kernel.
 static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t nFrames, uint8_t* out, uint8_t* ok,
-                            cudaStream_t st)
+                            cudaStream_t st, uint8_t* cand = nullptr)
 {
     DecodeParams p = c->geo;
+    p.cand = cand;
     p.infoPos = c->dInfoPos;
     p.crcTab = c->dSynTab;
     p.crcInit = c->synInit;
@@ -783,6 +784,49 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     } else {
         CUDA_TRY(cudaStreamSynchronize(st));
     }
+    return POLAR_OK;
+}
+
+// Candidate hand-back (a detector the kernels do not fuse is run by the host over all L candidates).
+int polar_cuda_decode_candidates(polar_code_t c, const void* llr, int llrType, int mem, size_t nFrames, uint8_t* cand_out,
+                                 uint8_t* count_out, void* stream)
+{
+    if (!c) return fail(POLAR_E_ARG, "null code handle");
+    if (c->kind == POLAR_KIND_ENC || c->kind >= POLAR_KIND_ADAPTIVE_I8)
+        return fail(POLAR_E_ARG, "candidate hand-back needs a Fast-SSC or list decoder handle");
+    if (c->crcBits) return fail(POLAR_E_ARG, "candidate hand-back: create the handle without a fused CRC");
+    if (nFrames == 0) return POLAR_OK;
+    if (!llr || !cand_out || !count_out) return fail(POLAR_E_ARG, "null buffer");
+    if (llrType != POLAR_LLR_I8 && llrType != POLAR_LLR_F32) return fail(POLAR_E_ARG, "bad llr type");
+    const bool f32Kind = (c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32);
+    if (f32Kind && llrType != POLAR_LLR_F32) return fail(POLAR_E_ARG, "an fp32 decoder takes float LLRs");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool list = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32);
+    const size_t candBytes = nFrames * (size_t)(list ? c->L : 1) * c->kb;
+    if (mem == POLAR_MEM_DEVICE) {
+        if (list) return decode_on_device(c, llr, llrType, nFrames, nullptr, count_out, st, cand_out);
+        int rc = decode_on_device(c, llr, llrType, nFrames, cand_out, count_out, st); // Fast-SSC: one candidate, verdict 1
+        return rc;
+    }
+    const size_t llrBytes = nFrames * (size_t)c->N * (llrType == POLAR_LLR_F32 ? 4 : 1);
+    void* dL = nullptr; uint8_t *dC = nullptr, *dN = nullptr;
+    cudaError_t e;
+    if ((e = cudaMalloc(&dL, llrBytes)) != cudaSuccess || (e = cudaMalloc(&dC, candBytes)) != cudaSuccess ||
+        (e = cudaMalloc(&dN, nFrames)) != cudaSuccess) {
+        cudaFree(dL); cudaFree(dC); cudaFree(dN);
+        cudaGetLastError();
+        return fail(POLAR_E_NOMEM, std::string("candidate staging: ") + cudaGetErrorString(e));
+    }
+    int rc = POLAR_OK;
+    e = cudaMemcpyAsync(dL, llr, llrBytes, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) rc = list ? decode_on_device(c, dL, llrType, nFrames, nullptr, dN, st, dC) : decode_on_device(c, dL, llrType, nFrames, dC, dN, st);
+    if (e == cudaSuccess && !rc) e = cudaMemcpyAsync(cand_out, dC, candBytes, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && !rc) e = cudaMemcpyAsync(count_out, dN, nFrames, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && !rc) e = cudaStreamSynchronize(st);
+    cudaFree(dL); cudaFree(dC); cudaFree(dN);
+    if (rc) return rc;
+    if (e != cudaSuccess) return fail(POLAR_E_CUDA, std::string("candidate hand-back: ") + cudaGetErrorString(e));
     return POLAR_OK;
 }
 

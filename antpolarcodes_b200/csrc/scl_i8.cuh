@@ -768,6 +768,7 @@ POLAR_DEV void scl_extract_best_path(const DecodeParams& p, const SclCtx& c, uin
         uint32_t* fbits = base + f * p.frameW + L * p.slotW;
         uint32_t* fspill = c.spill - c.fb + f * L; // first scratch column of frame f
         bool okFlag = false;
+        const bool handBack = p.cand != nullptr; // every surviving path goes to the host, which owns the detector
         for (int path = 0; path < P; ++path) {
             // codeword estimate of this path: the root leaf's bits, or [left ^ right | right] of the two halves
             const uint32_t sa = __shfl_sync(FULL_MASK, slotA, f * L + path);
@@ -787,6 +788,13 @@ POLAR_DEV void scl_extract_best_path(const DecodeParams& p, const SclCtx& c, uin
             __syncwarp();
             if (!p.systematic) warp_polar_transform(cw, p.N, lane);
             const uint32_t syn = gather_info_and_syndrome(p, cw, outw, lane);
+            if (handBack) {
+                uint8_t* dst = p.cand + ((size_t)frame * L + path) * p.kb;
+                const uint8_t* srcb = reinterpret_cast<const uint8_t*>(outw);
+                for (int i = lane; i < p.kb; i += 32) dst[i] = srcb[i];
+                __syncwarp();
+                continue;
+            }
             if (syn == 0u) { okFlag = true; break; }
             if (!p.crcBits || (path == 0 && P == 1)) break;
             // remember path 0's decision in case nobody passes (scl_fip_char.cpp:848-853)
@@ -797,6 +805,11 @@ POLAR_DEV void scl_extract_best_path(const DecodeParams& p, const SclCtx& c, uin
         if (!okFlag && P > 1 && p.crcBits) { // fall back to the most likely path
             for (int w = lane; w < ((p.K + 31) >> 5); w += 32) outw[w] = cw[nW + w];
             __syncwarp();
+        }
+        if (handBack) {
+            if (lane == 0) p.ok[frame] = (uint8_t)P;
+            __syncwarp();
+            continue;
         }
         store_info(p, frame, outw, lane);
         if (lane == 0) p.ok[frame] = okFlag ? 1 : 0;

@@ -76,6 +76,15 @@ int polar_cuda_code_destroy(polar_code_t code);
 int polar_cuda_decode_batch(polar_code_t code, const void* llr, int llrType, int mem, size_t nFrames,
                             uint8_t* info_out, uint8_t* ok_out, void* stream);
 
+/* Candidate hand-back for detectors the kernels do not fuse (anything but Dummy / CRC8 / CRC16 / CRC32, e.g. the reference's
+ * cmac): the list decoders return the info blocks of ALL surviving paths in list order, so that the host runs
+ * Detector::check over them exactly like extractBestPath does (scl_fip_char.cpp:816-855: first passing path wins, else
+ * path 0 and decode() == false).  The handle must have been created with crcBits = 0 and must not be an adaptive kind.
+ *   cand_out  : nFrames x listSize x ceil(K/8) bytes (Fast-SSC kinds: nFrames x ceil(K/8), one candidate)
+ *   count_out : nFrames bytes, the number of candidates of the frame (paths alive at the end of the tree, <= listSize) */
+int polar_cuda_decode_candidates(polar_code_t code, const void* llr, int llrType, int mem, size_t nFrames, uint8_t* cand_out,
+                                 uint8_t* count_out, void* stream);
+
 /* Encoder::encode_vector over nFrames frames.  info: nFrames x K/8 bytes; like the reference the
  * trailing CRC bytes of every info block are overwritten in place.  code_out: nFrames x N/8. */
 int polar_cuda_encode_batch(polar_code_t code, uint8_t* info, int mem, size_t nFrames, uint8_t* code_out,

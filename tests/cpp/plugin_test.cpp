@@ -153,6 +153,27 @@ static void runCase(const Case& c, bool sys)
         const bool r = refDec->decode_vector(ten.data(), w.data()), g = gpuDec->decode_vector(ten.data(), o.data());
         CHECK(r == g && o == w, "float LLRs into the char decoder N=%d L=%d", c.N, c.L);
     }
+    { // soft outputs are not produced on the GPU: the accessors refuse instead of returning stale container memory
+        std::vector<float> soft(c.N);
+        bool threw = false;
+        try { gpuDec->getSoftCodeword(soft.data()); } catch (const std::logic_error&) { threw = true; }
+        CHECK(threw, "getSoftCodeword on a CUDA decoder must throw");
+        threw = false;
+        try { gpuDec->getSoftInformation(soft.data()); } catch (const std::logic_error&) { threw = true; }
+        CHECK(threw, "getSoftInformation on a CUDA decoder must throw");
+    }
+    if (c.impl == 0 && sys && c.K >= 64 && c.frames >= 32) { // a detector the kernels do not fuse (cmac): candidates come back, the host checks
+        std::unique_ptr<Decoding::Decoder> r2(Decoding::makeDecoder(c.N, c.L, frozen, 0)), g2(Decoding::makeCudaDecoder(c.N, c.L, frozen, 0));
+        r2->setErrorDetection(ErrorDetection::create(32, "cmac"));
+        g2->setErrorDetection(ErrorDetection::create(32, "cmac"));
+        int bad = 0;
+        std::vector<unsigned char> a(kb), b(kb);
+        for (int f = 0; f < 32; ++f) {
+            const bool ra = r2->decode_vector(&ch[(size_t)f * c.N], a.data()), rb = g2->decode_vector(&ch[(size_t)f * c.N], b.data());
+            if (ra != rb || a != b) ++bad;
+        }
+        CHECK(bad == 0, "host-side detector (cmac) N=%d L=%d: %d of 32 frames differ", c.N, c.L, bad);
+    }
     std::printf("case N=%d K=%d L=%d %s crc=%d sys=%d %s: %d frames, %d pass the detector\n", c.N, c.K, c.L,
                 c.impl ? "float" : "char", c.crc, (int)sys, c.ctype, c.frames, okCount);
 }
