@@ -29,6 +29,12 @@ struct ScCtx {
     int bitRow, tileRow, chanRow, smemStages;
     uint32_t* smLane;      // sm + lane
     uint32_t* spillLane;   // spill + lane, rebased so that row llr_woff(s) is the row of spilled stage s
+    // register stages (stages <= regTop = min(4, lgN - 2)): LLR blocks of stage 4 / 3 / 2 / 1 in r[4..7] / r[2..3] / r[1] /
+    // r[0]; the 32-bit word of partial sums the small nodes are working in sits in `bw` (word index curW, -1: none)
+    int regTop;
+    uint32_t r[8];
+    uint32_t bw;
+    int curW;
 };
 
 #define SC_ROW(c, row) (c).sm[((row) << 5) + (c).lane]
@@ -273,6 +279,188 @@ POLAR_DEV bool sc_spc_decide(const uint32_t* src, int s, bool longForm, uint32_t
     return flip;
 }
 
+// ---------------------------------------------------------------- register stages
+// 170 of the 234 steps of the N = 1024 K = 512 program work on blocks of at most 16 elements.  Those blocks live in the
+// thread's registers (a stage-s block is 2^s int8 = at most four words), their partial sums in one cached word of the
+// codeword estimate: the tree is walked left to right, so the small nodes enter a 32-bit word, fill it, and leave it --
+// one load and one store per word.  Every handler is compiled per stage (compile-time word counts and register indices).
+template <int S> struct ScReg {
+    static_assert(S >= 1 && S <= 4, "register stages are 1..4");
+    static constexpr int W = S >= 2 ? 1 << (S - 2) : 1;
+    static constexpr int OFF = S == 4 ? 4 : S == 3 ? 2 : S == 2 ? 1 : 0;
+    static constexpr int NB = 1 << S;
+    static constexpr uint32_t MASK = (1u << NB) - 1u;
+    static constexpr uint32_t EMASK = S == 1 ? 0xFFFFu : 0xFFFFFFFFu;
+};
+
+// write the cached word back (before anything reads the bit rows of shared memory)
+POLAR_DEV void sc_flush_bits(ScCtx& c)
+{
+    if (c.curW >= 0) {
+        SC_ROW(c, c.bitRow + c.curW) = c.bw;
+        c.curW = -1;
+    }
+}
+// make the word of bit position pos the cached one
+POLAR_DEV void sc_enter_word(ScCtx& c, int pos)
+{
+    const int w = pos >> 5;
+    if (w != c.curW) {
+        sc_flush_bits(c);
+        c.curW = w;
+        c.bw = SC_ROW(c, c.bitRow + w);
+    }
+}
+template <int NBITS>
+POLAR_DEV uint32_t sc_get_field(const ScCtx& c, int pos)
+{
+    return (c.bw >> (pos & 31)) & (NBITS >= 32 ? 0xFFFFFFFFu : (1u << NBITS) - 1u);
+}
+template <int NBITS>
+POLAR_DEV void sc_put_field(ScCtx& c, int pos, uint32_t v)
+{
+    if constexpr (NBITS >= 32) {
+        c.bw = v;
+    } else {
+        constexpr uint32_t M = (1u << NBITS) - 1u;
+        const int sh = pos & 31;
+        c.bw = (c.bw & ~(M << sh)) | ((v & M) << sh);
+    }
+}
+
+template <int S>
+POLAR_DEV void scr_load_parent(const ScCtx& c, uint32_t (&a)[ScReg<S>::W], uint32_t (&b)[ScReg<S>::W])
+{
+    constexpr int W = ScReg<S>::W;
+    bool inRegs = false;
+    if constexpr (S < 4) inRegs = S + 1 <= c.regTop;
+    if (inRegs) {
+        if constexpr (S == 1) {
+            a[0] = c.r[1];
+            b[0] = c.r[1] >> 16;
+        } else if constexpr (S < 4) {
+            constexpr int PO = ScReg<S + 1>::OFF;
+#pragma unroll
+            for (int w = 0; w < W; ++w) { a[w] = c.r[PO + w]; b[w] = c.r[PO + W + w]; }
+        }
+    } else {
+        const uint32_t* src = sc_stage(c, S + 1);
+        if constexpr (S == 1) {
+            a[0] = src[0];
+            b[0] = a[0] >> 16;
+        } else {
+#pragma unroll
+            for (int w = 0; w < W; ++w) { a[w] = src[w << 5]; b[w] = src[(w + W) << 5]; }
+        }
+    }
+}
+
+// F / G / G-0R / G-R1 producing (or, for G-R1, consuming) a register block
+template <int S, int CODE>
+POLAR_DEV void scr_op(ScCtx& c, int pos)
+{
+    constexpr int W = ScReg<S>::W, OFF = ScReg<S>::OFF, NB = ScReg<S>::NB;
+    uint32_t a[W], b[W];
+    scr_load_parent<S>(c, a, b);
+    if constexpr (CODE == OP_F) {
+#pragma unroll
+        for (int w = 0; w < W; ++w) c.r[OFF + w] = f4(a[w], b[w]);
+    } else if constexpr (CODE == OP_G_0R) {
+#pragma unroll
+        for (int w = 0; w < W; ++w) c.r[OFF + w] = adds4(a[w], b[w]);
+    } else if constexpr (CODE == OP_G) {
+        const uint32_t lb = sc_get_field<NB>(c, pos);
+#pragma unroll
+        for (int w = 0; w < W; ++w) c.r[OFF + w] = g4(a[w], b[w], nibble_to_msb(lb >> (4 * w)));
+    } else { // OP_G_R1 (ShortROneNode, fastssc_fip_char.cpp:451-474): right bits = sign(g), left bits ^= right bits
+        const uint32_t lb = sc_get_field<NB>(c, pos);
+        uint32_t rb = 0;
+#pragma unroll
+        for (int w = 0; w < W; ++w) rb |= sign_nibble(g4(a[w], b[w], nibble_to_msb(lb >> (4 * w)))) << (4 * w);
+        rb &= ScReg<S>::MASK;
+        sc_put_field<2 * NB>(c, pos, (lb ^ rb) | (rb << NB));
+    }
+}
+
+template <int S, bool ZERO_LEFT>
+POLAR_DEV void scr_combine(ScCtx& c, int pos) // fip_char.h:164-220 on sign bits
+{
+    constexpr int NB = ScReg<S>::NB;
+    const uint32_t l = sc_get_field<NB>(c, pos), r = sc_get_field<NB>(c, pos + NB);
+    sc_put_field<NB>(c, pos, ZERO_LEFT ? r : (l ^ r));
+}
+
+// sign bits of a register block
+template <int S>
+POLAR_DEV uint32_t scr_signs(const uint32_t* x)
+{
+    uint32_t v = 0;
+#pragma unroll
+    for (int w = 0; w < ScReg<S>::W; ++w) v |= sign_nibble(x[w]) << (4 * w);
+    return v & ScReg<S>::MASK;
+}
+
+// short-form SPC decision (fastssc_fip_char.cpp:305-319: first minimum of |x| over the 32-byte vector whose pads are +127):
+// returns the sign bits with the flip applied
+template <int S>
+POLAR_DEV uint32_t scr_spc(const uint32_t* x)
+{
+    constexpr int W = ScReg<S>::W, n = ScReg<S>::NB;
+    uint32_t px = 0, best = 0xFFFFFFFFu, bits = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+        const uint32_t xv = x[w] & ScReg<S>::EMASK;
+        px ^= xv;
+        bits |= sign_nibble(xv) << (4 * w);
+        const uint32_t m = uabs4(xv); // |x| as unsigned, |-128| = 128
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            if (4 * w + e < n) best = min(best, prmt(m, (uint32_t)(4 * w + e), 0x7054u | (e << 8))); // (|x_e| << 16) | index
+    }
+    bits &= ScReg<S>::MASK;
+    const bool odd = (__popc(px & 0x80808080u) & 1) != 0;
+    const uint32_t mv = best >> 16, mi = best & 0xFFFFu;
+    // a +127 pad wins when every |x| exceeds 127 (only -128 does); the negate is void for 0 (and -128)
+    const bool flip = odd && mv != 0u && mv <= 127u;
+    return flip ? bits ^ (1u << mi) : bits;
+}
+
+template <int S, int CODE>
+POLAR_DEV void scr_leaf(ScCtx& c, int pos)
+{
+    constexpr int W = ScReg<S>::W, OFF = ScReg<S>::OFF, NB = ScReg<S>::NB;
+    const uint32_t* x = c.r + OFF;
+    if constexpr (CODE == OP_SC_R0) {
+        sc_put_field<NB>(c, pos, 0u);
+    } else if constexpr (CODE == OP_SC_R1) {
+        sc_put_field<NB>(c, pos, scr_signs<S>(x));
+    } else if constexpr (CODE == OP_SC_REP) { // ShortRepetition (fastssc_fip_char.cpp:265-272): zero pads, 32-lane reduce tree
+        uint32_t a0 = x[0] & ScReg<S>::EMASK, a1 = 0u;
+        if constexpr (W >= 2) a1 = x[1];
+        if constexpr (W == 4) { a0 = adds4(a0, x[2]); a1 = adds4(a1, x[3]); }
+        uint32_t t = W >= 2 ? adds4(a0, a1) : a0;
+        t = adds4(t, t >> 16);
+        t = adds4(t, t >> 8);
+        sc_put_field<NB>(c, pos, (t & 0x80u) ? 0xFFFFFFFFu : 0u);
+    } else if constexpr (CODE == OP_SC_SPC) {
+        sc_put_field<NB>(c, pos, scr_spc<S>(x));
+    } else { // OP_SC_ZERO_SPC (:361-388) / OP_SC_ZERO_ONE (:390-399): y = sat(l + r) over the halves, decided, duplicated
+        static_assert(S >= 2, "a zero-left leaf has at least four elements");
+        constexpr int H = S - 1, HW = ScReg<H>::W, HB = ScReg<H>::NB;
+        uint32_t y[HW];
+        if constexpr (H == 1) {
+            y[0] = adds4(x[0], x[0] >> 16) & 0xFFFFu;
+        } else {
+#pragma unroll
+            for (int w = 0; w < HW; ++w) y[w] = adds4(x[w], x[w + HW]);
+        }
+        uint32_t v;
+        if constexpr (CODE == OP_SC_ZERO_SPC) v = scr_spc<H>(y);
+        else v = scr_signs<H>(y);
+        sc_put_field<NB>(c, pos, v | (v << HB));
+    }
+}
+
 // ---------------------------------------------------------------- the kernel
 // WIDE: blocks of up to 16 warps at 128 registers (the lockstep barrier then spans every resident warp of the
 // SM); otherwise blocks of up to 8 warps with the full register budget.
@@ -294,6 +482,11 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
     c.smemStages = p.smemStages;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW : nullptr;
     c.lastFrame = p.nFrames - 1;
+    c.regTop = p.regStages;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c.r[i] = 0u;
+    c.bw = 0u;
+    c.curW = -1;
     c.smLane = c.sm + lane;
     c.spillLane = c.spill ? c.spill - (llr_woff(p.smemStages) << 5) + lane : c.smLane;
     uint32_t* tileA = c.sm + (p.tileRow << 5);
@@ -320,12 +513,42 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
                 __syncwarp();
             }
         }
+        c.curW = -1;
+        const uint32_t lockMask = p.lockstep ? (uint32_t)p.lockstep - 1u : 0x7FFFFFFFu;
         for (int pc = 0;; ++pc) {
+            // op word of this kernel: the host replaced the op code (bits 5..0) by a dense handler id (sc_handler_id)
             const uint32_t op = sched.ops[pc];
-            const uint32_t code = POLAR_OP_CODE(op);
-            if (code == OP_END) break;
-            if (p.lockstep && (pc & (p.lockstep - 1)) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
+            const uint32_t hid = op & 63u;
+            if (hid == SC_H_END) break;
+            if ((pc & lockMask) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
             const int s = (int)POLAR_OP_STAGE(op), pos = (int)POLAR_OP_POS(op);
+            if (hid < SC_H_GENERIC) { // register stages: handlers compiled per stage
+#define POLAR_SCR_CASES(IDX, FIRST, CALL)                                                   \
+    case 1 + 4 * IDX + 0: if constexpr (FIRST <= 1) { constexpr int S = 1; CALL; } break;      \
+    case 1 + 4 * IDX + 1: if constexpr (FIRST <= 2) { constexpr int S = 2; CALL; } break;      \
+    case 1 + 4 * IDX + 2: if constexpr (FIRST <= 3) { constexpr int S = FIRST <= 3 ? 3 : 4; CALL; } break; \
+    case 1 + 4 * IDX + 3: { constexpr int S = 4; CALL; } break;
+                switch (hid) {
+                POLAR_SCR_CASES(0, 1, (scr_op<S, OP_F>(c, pos)))
+                POLAR_SCR_CASES(1, 1, sc_enter_word(c, pos); (scr_op<S, OP_G>(c, pos)))
+                POLAR_SCR_CASES(2, 1, (scr_op<S, OP_G_0R>(c, pos)))
+                POLAR_SCR_CASES(3, 1, sc_enter_word(c, pos); (scr_op<S, OP_G_R1>(c, pos)))
+                POLAR_SCR_CASES(4, 1, sc_enter_word(c, pos); (scr_combine<S, false>(c, pos)))
+                POLAR_SCR_CASES(5, 1, sc_enter_word(c, pos); (scr_combine<S, true>(c, pos)))
+                POLAR_SCR_CASES(6, 1, sc_enter_word(c, pos); (scr_leaf<S, OP_SC_R0>(c, pos)))
+                POLAR_SCR_CASES(7, 1, sc_enter_word(c, pos); (scr_leaf<S, OP_SC_R1>(c, pos)))
+                POLAR_SCR_CASES(8, 1, sc_enter_word(c, pos); (scr_leaf<S, OP_SC_REP>(c, pos)))
+                POLAR_SCR_CASES(9, 2, sc_enter_word(c, pos); (scr_leaf<S, OP_SC_SPC>(c, pos)))
+                POLAR_SCR_CASES(10, 3, sc_enter_word(c, pos); (scr_leaf<S, OP_SC_ZERO_SPC>(c, pos)))
+                POLAR_SCR_CASES(11, 2, sc_enter_word(c, pos); (scr_leaf<S, OP_SC_ZERO_ONE>(c, pos)))
+                default: break;
+                }
+#undef POLAR_SCR_CASES
+                continue;
+            }
+            // stages in shared memory / the L2 scratch / the channel tiles: the cached bit word goes back first
+            sc_flush_bits(c);
+            const uint32_t code = hid - SC_H_GENERIC + 1u;
             const bool longForm = (POLAR_OP_FLAGS(op) & OPF_LONG) != 0;
             const bool top = (s + 1 == c.lgN) && c.chanRow < 0; // parent block = channel row in global memory
             switch (code) {
@@ -452,6 +675,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
             default: break;
             }
         }
+        sc_flush_bits(c);
         if (live) thread_frame_epilogue(p, c.sm, lane, c.bitRow, c.frame0);
     }
 }

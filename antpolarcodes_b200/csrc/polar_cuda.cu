@@ -269,6 +269,9 @@ int setup_decoder_geometry(polar_code* c)
         if (nSpill) g.spillWarpW = 32 * (llr_woff(c->lgN) - llr_woff(g.smemStages));
         wide = env_int("POLAR_CUDA_SC_WIDE", 1) != 0;
         c->kernel = fastssc_i8_kernel_for(wide);
+        g.regStages = rootLeaf ? -1 : std::min(env_int("POLAR_CUDA_SC_REG_STAGES", 4), c->lgN - 2);
+        for (size_t i = 0; i < c->ops.size(); ++i) // dense handler ids in place of the op codes
+            c->sched.ops[i] = (c->ops[i] & ~63u) | sc_handler_id(c->ops[i], g.regStages);
     }
     if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
     const size_t perWarp = (size_t)g.warpW * 4;
