@@ -162,7 +162,9 @@ def run_sweep(Ns, rate, configs, ebn0s, dtype="char", adaptive=False, constructi
                     if sub is not None:   # a checker's verdict on the first batch (tests/bler_check.py: the CPU reference)
                         rec["subsample"] = sub
                         if "cpu_wilson95" in sub:
-                            rec["ci_ok"] = bool(sub["cpu_wilson95"][0] <= bler <= sub["cpu_wilson95"][1])
+                            rec["ci95_ok"] = bool(sub["cpu_wilson95"][0] <= bler <= sub["cpu_wilson95"][1])
+                            wide = sub.get("cpu_wilson999", sub["cpu_wilson95"])
+                            rec["ci_ok"] = bool(wide[0] <= bler <= wide[1])
                     records.append(rec)
                     if out:
                         with open(out, "a") as f:

@@ -5,7 +5,8 @@ decoded again by the UNMODIFIED reference on the host cores (oracle/_ref).  Per 
 
     subsample: {frames, mismatches (info bytes or verdict differ, must be 0), gpu_errors, cpu_errors (must be equal for the
                 int8 decoders), wilson95 of the CPU subsample}
-    ci_ok:     the BLER of the full run lies inside that 95 % Wilson interval
+    ci95_ok:   the BLER of the full run lies inside that 95 % Wilson interval (1 point in 20 falls outside by construction)
+    ci_ok:     ... inside the 99.9 % interval of the CPU subsample: the gate
 
 (SURVEY.md 8d "parity checks run with every measurement").  The product never imports oracle/: this driver
 lives in tests/ and hands the comparison to the sweep as a callback.
@@ -66,7 +67,9 @@ def main():
             cpu_err = int((ro != h_sent).any(axis=1).sum())
             gpu_err = int((h_dec != h_sent).any(axis=1).sum())
             lo, hi = bler.wilson(cpu_err, n)
+            lo3, hi3 = bler.wilson(cpu_err, n, z=3.2905)
             return {"frames": n, "mismatches": mism, "gpu_errors": gpu_err, "cpu_errors": cpu_err, "cpu_wilson95": [lo, hi],
+                    "cpu_wilson999": [lo3, hi3],
                     "cpu_threads": threads, "cpu_seconds": time.perf_counter() - t0}
         return cb
 
@@ -104,10 +107,14 @@ def main():
                 bad += 0 if ok else 1
             print(json.dumps({k: r[k] for k in ("N", "K", "L", "C", "ebn0_db", "runs", "errors", "bler", "bler_wilson95", "n_gpus",
                                                 "frames_per_second", "stop") if k in r} |
-                             {"subsample": sub, "ci_ok": r.get("ci_ok")}), flush=True)
+                             {"subsample": sub, "ci95_ok": r.get("ci95_ok"), "ci_ok": r.get("ci_ok")}), flush=True)
         if a.csv:
             bler.write_csv(a.csv, records)
-        print(json.dumps({"points": len(records), "points_failing_parity_or_ci": bad}))
+        out95 = sum(1 for r in records if r.get("subsample") and not r.get("ci95_ok", True))
+        # a 95 % interval misses the true value for 1 point in 20 by construction: the gate is the 99.9 % interval, the count
+        # of points outside the 95 % interval is reported next to its expectation
+        print(json.dumps({"points": len(records), "points_failing_parity_or_ci": bad, "points_outside_cpu_wilson95": out95,
+                          "expected_outside_wilson95": round(0.05 * sum(1 for r in records if r.get("subsample")), 1)}))
         return 1 if bad else 0
     return 0
 
