@@ -21,17 +21,16 @@
 namespace polar {
 
 struct ScCtx {
+    const DecodeParams& P; // geometry is read where it is used: kernel parameters are constant-bank operands, not registers
     uint32_t* sm;          // this warp's shared memory
     const uint32_t* chan;  // channel rows (global), N/4 words per frame
     long long frame0, lastFrame;
     uint32_t* spill;       // this warp's rows of the L2-resident scratch (stages >= smemStages), or null
-    int lane, lgN, nw;     // nw = N/4
-    int bitRow, tileRow, chanRow, smemStages;
+    int lane;
     uint32_t* smLane;      // sm + lane
     uint32_t* spillLane;   // spill + lane, rebased so that row llr_woff(s) is the row of spilled stage s
-    // register stages (stages <= regTop = min(4, lgN - 2)): LLR blocks of stage 4 / 3 / 2 / 1 in r[4..7] / r[2..3] / r[1] /
-    // r[0]; the 32-bit word of partial sums the small nodes are working in sits in `bw` (word index curW, -1: none)
-    int regTop;
+    // register stages (stages <= P.regStages = min(4, lgN - 2)): LLR blocks of stage 4 / 3 / 2 / 1 in r[4..7] / r[2..3] /
+    // r[1] / r[0]; the 32-bit word of partial sums the small nodes are working in sits in `bw` (word index curW, -1: none)
     uint32_t r[8];
     uint32_t bw;
     int curW;
@@ -44,8 +43,8 @@ struct ScCtx {
 // channel (degenerate one-leaf codes).
 POLAR_DEV uint32_t* sc_stage(const ScCtx& c, int s)
 {
-    if (s == c.lgN) return c.sm + (c.chanRow << 5) + c.lane;
-    uint32_t* base = s >= c.smemStages ? c.spillLane : c.smLane; // both already offset to the lane's column
+    if (s == c.P.lgN) return c.sm + (c.P.chanRow << 5) + c.lane;
+    uint32_t* base = s >= c.P.smemStages ? c.spillLane : c.smLane; // both already offset to the lane's column
     return base + (llr_woff(s) << 5);
 }
 
@@ -71,14 +70,56 @@ POLAR_DEV void sc_load_tile(const ScCtx& c, uint32_t* tile, int w0, int cw)
     // once; the caller waits (cp_async_wait_all) before the __syncwarp that publishes the tile
     if (c.lane < cw) {
         if (c.frame0 + 31 <= c.lastFrame) {
-            const uint32_t* src = c.chan + c.frame0 * c.nw + w0 + c.lane;
+            const uint32_t* src = c.chan + c.frame0 * (c.P.N >> 2) + w0 + c.lane;
 #pragma unroll 8
-            for (int r = 0; r < 32; ++r) cp_async4(tile + r * 33 + c.lane, src + (long long)r * c.nw);
+            for (int r = 0; r < 32; ++r) cp_async4(tile + r * 33 + c.lane, src + (long long)r * (c.P.N >> 2));
         } else {
             for (int r = 0; r < 32; ++r) {
                 const long long f = min(c.frame0 + r, c.lastFrame);
-                cp_async4(tile + r * 33 + c.lane, c.chan + f * c.nw + w0 + c.lane);
+                cp_async4(tile + r * 33 + c.lane, c.chan + f * (c.P.N >> 2) + w0 + c.lane);
             }
+        }
+    }
+}
+
+// ---- TMA variant of the channel tiles (N >= 256): tile[r * 32 + i] = channel word (w0 + i) of frame (frame0 + r), filled by
+// 32 bulk copies of 128 bytes (lane r copies the row segment of frame r; SASS UBLKCP) that complete on the warp's mbarrier.
+// Rows are 128-byte aligned, so the transposing read is done ROTATED: at step i lane l takes word (i + l) & 31 of its row,
+// which puts the 32 lanes of a step on 32 different banks (a padded row stride would break the 16-byte alignment TMA needs).
+POLAR_DEV void sc_tma_fill(const ScCtx& c, uint32_t* tileA, uint32_t* tileB, int w0, int halfW, uint64_t* bar)
+{
+    fence_proxy_async(); // the tiles alias stage rows written through the generic proxy
+    if (c.lane == 0) mbar_expect_tx(bar, 2u * 32u * 128u);
+    __syncwarp();
+    const long long f = min(c.frame0 + c.lane, c.lastFrame); // tail lanes re-read the last frame
+    const uint32_t* row = c.chan + f * (c.P.N >> 2) + w0;
+    tma_bulk_g2s(tileA + c.lane * 32, row, 128u, bar);
+    tma_bulk_g2s(tileB + c.lane * 32, row + halfW, 128u, bar);
+}
+
+template <int CODE>
+POLAR_DEV void sc_top_rot(ScCtx& c, const uint32_t* tileA, const uint32_t* tileB, uint32_t* dst, int pos, int w0)
+{
+    const uint32_t* ra = tileA + c.lane * 32;
+    const uint32_t* rb = tileB + c.lane * 32;
+    const uint32_t* bits = c.smLane + ((c.P.llrRows + (pos >> 5)) << 5);
+#pragma unroll 1
+    for (int i0 = 0; i0 < 32; i0 += 8) {
+        uint32_t a[8], b[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const int i = (i0 + t + c.lane) & 31;
+            a[t] = ra[i];
+            b[t] = rb[i];
+        }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const int w = w0 + ((i0 + t + c.lane) & 31);
+            uint32_t v;
+            if constexpr (CODE == OP_F) v = f4(a[t], b[t]);
+            else if constexpr (CODE == OP_G_0R) v = adds4(a[t], b[t]);
+            else v = g4(a[t], b[t], nibble_to_msb(bits[(w >> 3) << 5] >> ((w & 7) * 4)));
+            dst[w << 5] = v;
         }
     }
 }
@@ -124,7 +165,7 @@ POLAR_DEV void sc_g_range(ScCtx& c, const Src& src, uint32_t* dst, int pos, int 
     int w = wb;
     if (((we - wb) & 7) == 0 && (pos & 31) == 0) { // whole bit words: one load per 8 LLR words
         for (; w < we; w += 8) {
-            const uint32_t lw = SC_ROW(c, c.bitRow + ((pos + 4 * w) >> 5));
+            const uint32_t lw = SC_ROW(c, c.P.llrRows + ((pos + 4 * w) >> 5));
             uint32_t a[8], b[8];
 #pragma unroll
             for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
@@ -135,7 +176,7 @@ POLAR_DEV void sc_g_range(ScCtx& c, const Src& src, uint32_t* dst, int pos, int 
     }
     for (; w < we; ++w) {
         const int bp = pos + 4 * w;
-        const uint32_t nib = SC_ROW(c, c.bitRow + (bp >> 5)) >> (bp & 31);
+        const uint32_t nib = SC_ROW(c, c.P.llrRows + (bp >> 5)) >> (bp & 31);
         dst[(w) << 5] = g4(src.a(w), src.b(w), nibble_to_msb(nib));
     }
 }
@@ -148,15 +189,15 @@ POLAR_DEV void sc_g_r1_range(ScCtx& c, const Src& src, int s, int pos, int wb, i
     const int hw = 1 << (s - 5);
     for (int w = wb; w < we; w += 8) {
         const int j = w >> 3;
-        const uint32_t lw = SC_ROW(c, c.bitRow + (pos >> 5) + j);
+        const uint32_t lw = SC_ROW(c, c.P.llrRows + (pos >> 5) + j);
         uint32_t a[8], b[8];
 #pragma unroll
         for (int t = 0; t < 8; ++t) { a[t] = src.a(w + t); b[t] = src.b(w + t); }
         uint32_t rw = 0;
 #pragma unroll
         for (int t = 0; t < 8; ++t) rw |= sign_nibble(g4(a[t], b[t], nibble_to_msb(lw >> (4 * t)))) << (4 * t);
-        SC_ROW(c, c.bitRow + (pos >> 5) + hw + j) = rw;
-        SC_ROW(c, c.bitRow + (pos >> 5) + j) = lw ^ rw;
+        SC_ROW(c, c.P.llrRows + (pos >> 5) + hw + j) = rw;
+        SC_ROW(c, c.P.llrRows + (pos >> 5) + j) = lw ^ rw;
     }
 }
 // h < 32: everything inside one bit word
@@ -165,7 +206,7 @@ POLAR_DEV void sc_g_r1_short(ScCtx& c, const Src& src, int s, int pos)
 {
     const int h = 1 << s, sh = pos & 31;
     const uint32_t mask = (1u << h) - 1u;
-    const uint32_t word = SC_ROW(c, c.bitRow + (pos >> 5));
+    const uint32_t word = SC_ROW(c, c.P.llrRows + (pos >> 5));
     const uint32_t lbits = (word >> sh) & mask;
     uint32_t rbits = 0;
     if (s >= 2) {
@@ -178,7 +219,7 @@ POLAR_DEV void sc_g_r1_short(ScCtx& c, const Src& src, int s, int pos)
     }
     const uint32_t both = (lbits ^ rbits) | (rbits << h);
     const uint32_t clr = (mask | (mask << h)) << sh;
-    SC_ROW(c, c.bitRow + (pos >> 5)) = (word & ~clr) | (both << sh);
+    SC_ROW(c, c.P.llrRows + (pos >> 5)) = (word & ~clr) | (both << sh);
 }
 
 // ---- bit helpers (block of n = 2^s bits at absolute position pos, pos % n == 0)
@@ -199,12 +240,12 @@ POLAR_DEV uint32_t sc_sign_word(const uint32_t* src, int s, int j)
 POLAR_DEV void sc_put_bits(ScCtx& c, int s, int pos, int j, uint32_t v)
 {
     if (s >= 5) {
-        SC_ROW(c, c.bitRow + (pos >> 5) + j) = v;
+        SC_ROW(c, c.P.llrRows + (pos >> 5) + j) = v;
     } else {
         const uint32_t mask = (1u << (1 << s)) - 1u;
         const int sh = pos & 31;
-        const uint32_t wd = SC_ROW(c, c.bitRow + (pos >> 5));
-        SC_ROW(c, c.bitRow + (pos >> 5)) = (wd & ~(mask << sh)) | ((v & mask) << sh);
+        const uint32_t wd = SC_ROW(c, c.P.llrRows + (pos >> 5));
+        SC_ROW(c, c.P.llrRows + (pos >> 5)) = (wd & ~(mask << sh)) | ((v & mask) << sh);
     }
 }
 POLAR_DEV void sc_fill_bits(ScCtx& c, int s, int pos, uint32_t pattern)
@@ -297,7 +338,7 @@ template <int S> struct ScReg {
 POLAR_DEV void sc_flush_bits(ScCtx& c)
 {
     if (c.curW >= 0) {
-        SC_ROW(c, c.bitRow + c.curW) = c.bw;
+        SC_ROW(c, c.P.llrRows + c.curW) = c.bw;
         c.curW = -1;
     }
 }
@@ -308,7 +349,7 @@ POLAR_DEV void sc_enter_word(ScCtx& c, int pos)
     if (w != c.curW) {
         sc_flush_bits(c);
         c.curW = w;
-        c.bw = SC_ROW(c, c.bitRow + w);
+        c.bw = SC_ROW(c, c.P.llrRows + w);
     }
 }
 template <int NBITS>
@@ -333,7 +374,7 @@ POLAR_DEV void scr_load_parent(const ScCtx& c, uint32_t (&a)[ScReg<S>::W], uint3
 {
     constexpr int W = ScReg<S>::W;
     bool inRegs = false;
-    if constexpr (S < 4) inRegs = S + 1 <= c.regTop;
+    if constexpr (S < 4) inRegs = S + 1 <= c.P.regStages;
     if (inRegs) {
         if constexpr (S == 1) {
             a[0] = c.r[1];
@@ -461,6 +502,49 @@ POLAR_DEV void scr_leaf(ScCtx& c, int pos)
     }
 }
 
+// ---------------------------------------------------------------- inner steps of the stages 5 .. lgN-2, compiled per stage
+// (compile-time trip counts and row offsets; the parent block sits in the thread's rows of shared memory or of the L2
+// scratch, never in the channel tiles: the top-level steps keep the generic path)
+template <int S>
+POLAR_DEV uint32_t* sc_stage_t(const ScCtx& c)
+{
+    return (S >= c.P.smemStages ? c.spillLane : c.smLane) + (llr_woff(S) << 5);
+}
+
+template <int S, int CODE>
+POLAR_DEV void scb_fg(ScCtx& c, int pos)
+{
+    static_assert(S >= 5, "whole bit words");
+    constexpr int words = 1 << (S - 2), hw = 1 << (S - 5);
+    const uint32_t* src = sc_stage_t<S + 1>(c);
+    uint32_t* dst = sc_stage_t<S>(c);
+    uint32_t* bits = c.smLane + ((c.P.llrRows + (pos >> 5)) << 5); // the block's first bit row
+#pragma unroll 2
+    for (int w = 0; w < words; w += 8) {
+        uint32_t a[8], b[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) { a[t] = src[(w + t) << 5]; b[t] = src[(w + t + words) << 5]; }
+        if constexpr (CODE == OP_F) {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) dst[(w + t) << 5] = f4(a[t], b[t]);
+        } else if constexpr (CODE == OP_G_0R) {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) dst[(w + t) << 5] = adds4(a[t], b[t]);
+        } else if constexpr (CODE == OP_G) {
+            const uint32_t lw = bits[(w >> 3) << 5];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) dst[(w + t) << 5] = g4(a[t], b[t], nibble_to_msb(lw >> (4 * t)));
+        } else { // OP_G_R1 (ROneNode, fastssc_fip_char.cpp:427-449)
+            const uint32_t lw = bits[(w >> 3) << 5];
+            uint32_t rw = 0;
+#pragma unroll
+            for (int t = 0; t < 8; ++t) rw |= sign_nibble(g4(a[t], b[t], nibble_to_msb(lw >> (4 * t)))) << (4 * t);
+            bits[((w >> 3) + hw) << 5] = rw;
+            bits[(w >> 3) << 5] = lw ^ rw;
+        }
+    }
+}
+
 // ---------------------------------------------------------------- the kernel
 // WIDE: blocks of up to 16 warps at 128 registers (the lockstep barrier then spans every resident warp of the
 // SM); otherwise blocks of up to 8 warps with the full register budget.
@@ -470,19 +554,12 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
 {
     extern __shared__ __align__(16) uint32_t smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warpsPerBlock = blockDim.x >> 5;
-    ScCtx c;
+    ScCtx c{ p };
     c.sm = smem + warp * p.warpW;
     c.chan = static_cast<const uint32_t*>(p.llr);
     c.lane = lane;
-    c.lgN = p.lgN;
-    c.nw = p.N >> 2;
-    c.bitRow = p.llrRows;
-    c.tileRow = p.tileRow;
-    c.chanRow = p.chanRow;
-    c.smemStages = p.smemStages;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW : nullptr;
     c.lastFrame = p.nFrames - 1;
-    c.regTop = p.regStages;
 #pragma unroll
     for (int i = 0; i < 8; ++i) c.r[i] = 0u;
     c.bw = 0u;
@@ -494,6 +571,13 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
     const uint32_t* myA = tileA + lane * 33;
     const uint32_t* myB = tileB + lane * 33;
     const int halfW = p.N >> 3, cw = min(32, halfW); // words per half of the channel row, chunk width
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(c.sm + (p.mbarRow << 5));
+    unsigned mbarPhase = 0u;
+    if (p.useTma) {
+        if (lane == 0) mbar_init(mbar, 1);
+        fence_proxy_async();
+        __syncwarp();
+    }
 
     const long long totalWarps = (long long)gridDim.x * warpsPerBlock;
     const long long nGroups = (p.nFrames + 31) >> 5;
@@ -503,13 +587,13 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
         const bool live = g0 + warp < nGroups; // a spare warp redoes the last group and drops it
         const long long grp = live ? g0 + warp : nGroups - 1;
         c.frame0 = grp << 5;
-        if (c.chanRow >= 0) { // one-leaf codes: stage the channel rows (transposed) once
-            for (int w0 = 0; w0 < c.nw; w0 += 32) {
-                const int n = min(32, c.nw - w0);
+        if (c.P.chanRow >= 0) { // one-leaf codes: stage the channel rows (transposed) once
+            for (int w0 = 0; w0 < (c.P.N >> 2); w0 += 32) {
+                const int n = min(32, (c.P.N >> 2) - w0);
                 sc_load_tile(c, tileA, w0, n);
                 cp_async_wait_all();
                 __syncwarp();
-                for (int i = 0; i < n; ++i) SC_ROW(c, c.chanRow + w0 + i) = myA[i];
+                for (int i = 0; i < n; ++i) SC_ROW(c, c.P.chanRow + w0 + i) = myA[i];
                 __syncwarp();
             }
         }
@@ -518,7 +602,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
         for (int pc = 0;; ++pc) {
             // op word of this kernel: the host replaced the op code (bits 5..0) by a dense handler id (sc_handler_id)
             const uint32_t op = sched.ops[pc];
-            const uint32_t hid = op & 63u;
+            const uint32_t hid = (op & 63u) | ((op >> 4) & 64u);
             if (hid == SC_H_END) break;
             if ((pc & lockMask) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
             const int s = (int)POLAR_OP_STAGE(op), pos = (int)POLAR_OP_POS(op);
@@ -548,9 +632,22 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
             }
             // stages in shared memory / the L2 scratch / the channel tiles: the cached bit word goes back first
             sc_flush_bits(c);
+            if (hid >= SC_H_BIG) { // F / G / G-0R / G-R1 of the stages 5 .. lgN-2, compiled per stage
+#define POLAR_SCB_CASES(S)                                                          \
+    case SC_H_BIG + 4 * (S - 5) + 0: scb_fg<S, OP_F>(c, pos); break;                  \
+    case SC_H_BIG + 4 * (S - 5) + 1: scb_fg<S, OP_G>(c, pos); break;                  \
+    case SC_H_BIG + 4 * (S - 5) + 2: scb_fg<S, OP_G_0R>(c, pos); break;               \
+    case SC_H_BIG + 4 * (S - 5) + 3: scb_fg<S, OP_G_R1>(c, pos); break;
+                switch (hid) {
+                POLAR_SCB_CASES(5) POLAR_SCB_CASES(6) POLAR_SCB_CASES(7) POLAR_SCB_CASES(8) POLAR_SCB_CASES(9) POLAR_SCB_CASES(10)
+                default: break;
+                }
+#undef POLAR_SCB_CASES
+                continue;
+            }
             const uint32_t code = hid - SC_H_GENERIC + 1u;
             const bool longForm = (POLAR_OP_FLAGS(op) & OPF_LONG) != 0;
-            const bool top = (s + 1 == c.lgN) && c.chanRow < 0; // parent block = channel row in global memory
+            const bool top = (s + 1 == c.P.lgN) && c.P.chanRow < 0; // parent block = channel row in global memory
             switch (code) {
             case OP_F:      // fip_char.h:76-91
             case OP_G:      // fip_char.h:93-110
@@ -563,7 +660,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
                     if (code == OP_F) dst[0] = f4(x, x >> 16);
                     else if (code == OP_G_0R) dst[0] = adds4(x, x >> 16);
                     else if (code == OP_G) {
-                        const uint32_t nib = (SC_ROW(c, c.bitRow + (pos >> 5)) >> (pos & 31)) & 3u;
+                        const uint32_t nib = (SC_ROW(c, c.P.llrRows + (pos >> 5)) >> (pos & 31)) & 3u;
                         dst[0] = g4(x, x >> 16, nibble_to_msb(nib));
                     } else sc_g_r1_short(c, src, s, pos);
                     break;
@@ -576,6 +673,16 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
                     else if (code == OP_G) sc_g_range(c, src, dst, pos, 0, words);
                     else if (s >= 5) sc_g_r1_range(c, src, s, pos, 0, words);
                     else sc_g_r1_short(c, src, s, pos);
+                } else if (p.useTma && code != OP_G_R1) { // words == halfW >= 32: TMA-filled tiles, rotated transposing read
+                    for (int w0 = 0; w0 < halfW; w0 += 32) {
+                        sc_tma_fill(c, tileA, tileB, w0, halfW, mbar);
+                        mbar_wait(mbar, mbarPhase);
+                        mbarPhase ^= 1u;
+                        if (code == OP_F) sc_top_rot<OP_F>(c, tileA, tileB, dst, pos, w0);
+                        else if (code == OP_G_0R) sc_top_rot<OP_G_0R>(c, tileA, tileB, dst, pos, w0);
+                        else sc_top_rot<OP_G>(c, tileA, tileB, dst, pos, w0);
+                        __syncwarp();
+                    }
                 } else { // words == halfW
                     for (int w0 = 0; w0 < halfW; w0 += cw) {
                         sc_load_tile(c, tileA, w0, cw);
@@ -595,26 +702,26 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
             }
             case OP_COMBINE: { // fip_char.h:164-207
                 if (s >= 5) {
-                    const int hw = 1 << (s - 5), r0 = c.bitRow + (pos >> 5);
+                    const int hw = 1 << (s - 5), r0 = c.P.llrRows + (pos >> 5);
                     for (int j = 0; j < hw; ++j) SC_ROW(c, r0 + j) ^= SC_ROW(c, r0 + hw + j);
                 } else {
                     const int h = 1 << s, sh = pos & 31;
-                    uint32_t wd = SC_ROW(c, c.bitRow + (pos >> 5));
+                    uint32_t wd = SC_ROW(c, c.P.llrRows + (pos >> 5));
                     wd ^= ((wd >> (sh + h)) & ((1u << h) - 1u)) << sh;
-                    SC_ROW(c, c.bitRow + (pos >> 5)) = wd;
+                    SC_ROW(c, c.P.llrRows + (pos >> 5)) = wd;
                 }
                 break;
             }
             case OP_COMBINE_0R: { // fip_char.h:209-220
                 if (s >= 5) {
-                    const int hw = 1 << (s - 5), r0 = c.bitRow + (pos >> 5);
+                    const int hw = 1 << (s - 5), r0 = c.P.llrRows + (pos >> 5);
                     for (int j = 0; j < hw; ++j) SC_ROW(c, r0 + j) = SC_ROW(c, r0 + hw + j);
                 } else {
                     const int h = 1 << s, sh = pos & 31;
                     const uint32_t mask = (1u << h) - 1u;
-                    uint32_t wd = SC_ROW(c, c.bitRow + (pos >> 5));
+                    uint32_t wd = SC_ROW(c, c.P.llrRows + (pos >> 5));
                     wd = (wd & ~(mask << sh)) | (((wd >> (sh + h)) & mask) << sh);
-                    SC_ROW(c, c.bitRow + (pos >> 5)) = wd;
+                    SC_ROW(c, c.P.llrRows + (pos >> 5)) = wd;
                 }
                 break;
             }
@@ -657,7 +764,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
             case OP_SC_ZERO_ONE: { // fastssc_fip_char.cpp:390-399
                 // y = sat(l + r) goes to the (free) child stage, or to row 0 when that stage is spilled
                 const int hs = s - 1;
-                uint32_t* y = hs < c.smemStages ? sc_stage(c, hs) : c.sm + c.lane;
+                uint32_t* y = hs < c.P.smemStages ? sc_stage(c, hs) : c.sm + c.lane;
                 const uint32_t* src = sc_stage(c, s);
                 if (hs >= 2) {
                     const int words = 1 << (hs - 2);
@@ -676,7 +783,7 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
             }
         }
         sc_flush_bits(c);
-        if (live) thread_frame_epilogue(p, c.sm, lane, c.bitRow, c.frame0);
+        if (live) thread_frame_epilogue(p, c.sm, lane, c.P.llrRows, c.frame0);
     }
 }
 

@@ -265,13 +265,23 @@ int setup_decoder_geometry(polar_code* c)
         else { g.tileRow = rows; rows += tileRows; }
         if (rootLeaf) { g.chanRow = rows; rows += c->N / 4; }
         g.outRow = 0;
+        // TMA bulk copies for the channel tiles (rows of whole 128-byte segments, N >= 256; one more row holds the mbarrier).
+        // Measured on B200 (N=1024 K=512, 2^20 frames): 32 per-lane 128-byte cp.async.bulk copies per tile (UBLKCP takes
+        // uniform operands, so the warp issues them one lane after the other) 146.9 Gbit/s against 181.7 for the 4-byte
+        // cp.async tiles below -- off by default, POLAR_CUDA_TMA=1 selects it (profiles/r2_s17_tma_ab.txt).
+        g.useTma = (!rootLeaf && c->N >= 256 && env_int("POLAR_CUDA_TMA", 0)) ? 1 : 0;
+        g.mbarRow = rows;
+        if (g.useTma) rows += 1;
         g.warpW = rows * 32;
         if (nSpill) g.spillWarpW = 32 * (llr_woff(c->lgN) - llr_woff(g.smemStages));
         wide = env_int("POLAR_CUDA_SC_WIDE", 1) != 0;
         c->kernel = fastssc_i8_kernel_for(wide);
         g.regStages = rootLeaf ? -1 : std::min(env_int("POLAR_CUDA_SC_REG_STAGES", 4), c->lgN - 2);
         for (size_t i = 0; i < c->ops.size(); ++i) // dense handler ids in place of the op codes
-            c->sched.ops[i] = (c->ops[i] & ~63u) | sc_handler_id(c->ops[i], g.regStages);
+        {
+            const uint32_t h = sc_handler_id(c->ops[i], g.regStages, c->lgN);
+            c->sched.ops[i] = (c->ops[i] & ~(63u | (1u << 10))) | (h & 63u) | ((h & 64u) << 4);
+        }
     }
     if (!c->kernel) return fail(POLAR_E_UNSUPPORTED, "no kernel for this list size");
     const size_t perWarp = (size_t)g.warpW * 4;
@@ -581,6 +591,7 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
         CUDA_TRY(cudaGetLastError());
         p.llr = c->dQuant;
     }
+    if (p.useTma && ((uintptr_t)p.llr & 15u)) p.useTma = 0; // bulk copies need 16-byte aligned rows: 4-byte cp.async tiles instead
     const int framesPerWarp = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32) ? 32 / c->L : 32;
     const long long warpsNeeded = ((long long)nFrames + framesPerWarp - 1) / framesPerWarp;
     const long long blocksNeeded = (warpsNeeded + c->warpsPerBlock - 1) / c->warpsPerBlock;

@@ -108,6 +108,40 @@ POLAR_DEV void cp_async4(uint32_t* smemDst, const uint32_t* globalSrc)
 }
 POLAR_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// ---- TMA bulk copies (cp.async.bulk, SASS UBLKCP) completing on a shared-memory mbarrier
+POLAR_DEV void mbar_init(uint64_t* bar, int count)
+{
+    const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(count) : "memory");
+}
+POLAR_DEV void mbar_expect_tx(uint64_t* bar, unsigned bytes) // one arrival + the byte count the copies will complete
+{
+    const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(a), "r"(bytes) : "memory");
+}
+POLAR_DEV void mbar_wait(uint64_t* bar, unsigned parity)
+{
+    const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(a), "r"(parity) : "memory");
+}
+// bytes: multiple of 16; both addresses 16-byte aligned
+POLAR_DEV void tma_bulk_g2s(void* smemDst, const void* globalSrc, unsigned bytes, uint64_t* bar)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst), b = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(d), "l"(globalSrc),
+                 "r"(bytes), "r"(b) : "memory");
+}
+// order earlier generic-proxy accesses to shared memory before the async-proxy writes that follow
+POLAR_DEV void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 POLAR_DEV int sat8i(int v) { return min(max(v, -128), 127); }
 
 } // namespace polar

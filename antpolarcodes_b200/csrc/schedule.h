@@ -73,11 +73,17 @@ inline uint32_t scl_handler_id(uint32_t op, int regTop)
 // Fast-SSC int8 kernel: the host replaces the op code (bits 5..0) by a dense handler id.  1 + 4 * idx + (stage - 1) for the
 // steps on register stages (idx: F, G, G-0R, G-R1, combine, combine-0R, R0, R1, REP, SPC, 0-SPC, 0-1), SC_H_GENERIC + code - 1
 // for everything else.
-enum ScHandler : uint32_t { SC_H_END = 0, SC_H_GENERIC = 49 };
-inline uint32_t sc_handler_id(uint32_t op, int regTop)
+// SC_H_BIG + 4 * (stage - 5) + {F, G, G-0R, G-R1} for the inner steps of the stages 5 .. lgN-2 (7-bit ids: bit 6 travels
+// in bit 10 of the op word, a list-decoder field).
+enum ScHandler : uint32_t { SC_H_END = 0, SC_H_GENERIC = 49, SC_H_BIG = 64 };
+inline uint32_t sc_handler_id(uint32_t op, int regTop, int lgN)
 {
     const uint32_t code = op & 63u, stage = (op >> 6) & 15u;
     if (code == OP_END) return SC_H_END;
+    if ((int)stage >= 5 && (int)stage > regTop && (int)stage <= lgN - 2 && (int)stage <= 10 && regTop >= 0) {
+        const int k = code == OP_F ? 0 : code == OP_G ? 1 : code == OP_G_0R ? 2 : code == OP_G_R1 ? 3 : -1;
+        if (k >= 0) return SC_H_BIG + 4u * (stage - 5u) + (uint32_t)k;
+    }
     static const int idx[16] = { -1, 0, 1, 4, 3, 2, 5, 6, 7, 8, -1, 9, 10, 11, -1, -1 }; // by OpCode (REP2 has >= 32 elements)
     const int k = code < 16 ? idx[code] : -1;
     if ((int)stage <= regTop && stage >= 1 && k >= 0) return 1u + 4u * (uint32_t)k + (stage - 1u);
