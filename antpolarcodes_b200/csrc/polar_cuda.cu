@@ -759,15 +759,33 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     }
     // HOST buffers: chunks of whole grid waves, double buffered over two internal streams, so that the H2D copy
     // of chunk k+1 and the D2H copy of chunk k-1 run under the kernel of chunk k.  The kernels themselves are
-    // chained by events (they share the spill / quantiser scratch of the handle).
+    // chained by events (they share the spill / quantiser scratch of the handle).  A launch costs a fixed ~60 us
+    // (measured: one-wave launches run at 13.0 Gbit/s, 16-wave launches at 14.6), a large first chunk leaves its copy
+    // exposed: the chunks therefore GROW -- 1, 2, 4, ... waves up to POLAR_CUDA_CHUNK_MB -- so the pipeline fills
+    // after one wave and runs on large launches from then on.
     const int framesPerWarp = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32) ? 32 / c->L : 32;
     const size_t wave = (size_t)framesPerWarp * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
-    const size_t targetBytes = (size_t)env_int("POLAR_CUDA_CHUNK_MB", 32) << 20;
-    size_t chunk = std::max<size_t>(1, targetBytes / ((size_t)c->N * eb) / wave) * wave;
-    if (chunk * 2 > nFrames || !env_int("POLAR_CUDA_PIPELINE", 1)) chunk = nFrames; // too small to split
-    const size_t nChunks = (nFrames + chunk - 1) / chunk;
+    const size_t rowBytes = (size_t)c->N * eb;
+    const size_t maxChunk = std::max<size_t>(1, (((size_t)env_int("POLAR_CUDA_CHUNK_MB", 128) << 20) / rowBytes) / wave) * wave;
+    const size_t firstChunk = std::max<size_t>(1, (((size_t)env_int("POLAR_CUDA_FIRST_CHUNK_MB", 8) << 20) / rowBytes) / wave) * wave;
+    std::vector<std::pair<size_t, size_t>> chunks; // (first frame, frames)
+    if (std::min(firstChunk, maxChunk) * 2 > nFrames || !env_int("POLAR_CUDA_PIPELINE", 1)) {
+        chunks.emplace_back(0, nFrames); // too small to split
+    } else {
+        size_t f0 = 0, sz = std::min(firstChunk, maxChunk);
+        while (f0 < nFrames) {
+            size_t n = std::min(sz, nFrames - f0);
+            if (nFrames - f0 - n < wave / 2) n = nFrames - f0; // do not leave a sliver for the last launch
+            chunks.emplace_back(f0, n);
+            f0 += n;
+            sz = std::min(sz * 2, maxChunk);
+        }
+    }
+    size_t largest = 0;
+    for (auto& ch : chunks) largest = std::max(largest, ch.second);
+    const size_t nChunks = chunks.size();
     const int depth = nChunks > 1 ? 2 : 1;
-    int rc = ensure_staging(c, chunk * depth, eb);
+    int rc = ensure_staging(c, largest * depth, eb);
     if (rc) return rc;
     if (depth == 2 && !c->pipe[0]) {
         for (int i = 0; i < 2; ++i) {
@@ -778,13 +796,13 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     CUDA_TRY(cudaStreamSynchronize(st)); // work queued before this call on the caller's stream comes first
     const uint8_t* src = static_cast<const uint8_t*>(llr);
     for (size_t k = 0; k < nChunks; ++k) {
-        const size_t f0 = k * chunk, n = std::min(chunk, nFrames - f0);
+        const size_t f0 = chunks[k].first, n = chunks[k].second;
         const int h = depth == 2 ? (int)(k & 1) : 0;
         cudaStream_t s = depth == 2 ? c->pipe[h] : st;
-        uint8_t* dL = static_cast<uint8_t*>(c->dLlr) + (size_t)h * chunk * c->N * eb;
-        uint8_t* dO = c->dOut + (size_t)h * chunk * c->kb;
-        uint8_t* dK = c->dOk + (size_t)h * chunk;
-        CUDA_TRY(cudaMemcpyAsync(dL, src + f0 * c->N * eb, n * c->N * (size_t)eb, cudaMemcpyHostToDevice, s));
+        uint8_t* dL = static_cast<uint8_t*>(c->dLlr) + (size_t)h * largest * rowBytes;
+        uint8_t* dO = c->dOut + (size_t)h * largest * c->kb;
+        uint8_t* dK = c->dOk + (size_t)h * largest;
+        CUDA_TRY(cudaMemcpyAsync(dL, src + f0 * rowBytes, n * rowBytes, cudaMemcpyHostToDevice, s));
         if (depth == 2 && k > 0) CUDA_TRY(cudaStreamWaitEvent(s, c->pipeDone[h ^ 1], 0)); // kernel k-1 has finished
         rc = decode_on_device(c, dL, llrType, n, dO, dK, s);
         if (rc) return rc;

@@ -36,7 +36,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 WORKLOADS = {
     # frames = frames per step per GPU; parity = frames of the timed batch re-decoded by the reference; cpu_s = CPU baseline seconds
-    "scl8": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 19, e2e_frames=1 << 18, parity=1 << 16, cpu_s=8.0,
+    "scl8": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 19, e2e_frames=1 << 19, parity=1 << 16, cpu_s=8.0,
                  label="SCL L=8 + CRC16, N=1024 K=512, 5G frozen set, int8 LLR, Eb/N0=2dB"),
     "fastssc": dict(N=1024, K=512, ctype="BB", L=1, crc=0, frames=1 << 20, e2e_frames=1 << 19, parity=1 << 18, cpu_s=3.0,
                     label="Fast-SSC int8, N=1024 K=512, BB frozen set, Eb/N0=2dB"),
@@ -59,7 +59,7 @@ WORKLOADS = {
     "pcbench_fastssc": dict(N=1024, K=512, ctype="BB", L=1, crc=0, frames=1 << 19, e2e_frames=1 << 18, pcbench=True, parity=1 << 17, cpu_s=3.0,
                             label="pcbench-style: Fast-SSC int8 decoder fed iid N(0,0.5) float inputs, N=1024 K=512, BB frozen set"),
 }
-ALSO = ["fastssc", "fastssc_f32", "encode", "scl32", "pcbench_scl8", "pcbench_fastssc"]
+ALSO = ["fastssc", "fastssc_f32", "encode", "scl32", "scl8_f32", "pcbench_scl8", "pcbench_fastssc"]
 METRIC = "info-bit Gbps (N=1024 K=512, SCL L=8+CRC16)"
 EBN0_DB = 2.0
 

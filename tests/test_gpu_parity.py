@@ -147,6 +147,7 @@ def test_host_buffer_pipeline(gpu, monkeypatch, N, K, L, n):
     o0, k0 = dec.decode_batch(llr)
     monkeypatch.setenv("POLAR_CUDA_PIPELINE", "1")
     monkeypatch.setenv("POLAR_CUDA_CHUNK_MB", "1")
+    monkeypatch.setenv("POLAR_CUDA_FIRST_CHUNK_MB", "1")
     launches = dec._get().launches()
     o1, k1 = dec.decode_batch(llr)
     assert dec._get().launches() - launches >= 2, "the batch was not split"
