@@ -30,7 +30,7 @@ EXPORTS = [
     "polar_cuda_puncturer_destroy", "polar_cuda_puncturer_parent_length", "polar_cuda_puncture_batch",
     "polar_cuda_depuncture_batch", "polar_cuda_puncture_packed_batch",
     "polar_cuda_sim_create", "polar_cuda_sim_destroy", "polar_cuda_sim_run", "polar_cuda_sim_buffers", "polar_cuda_sim_launches",
-    "polar_cuda_test_philox", "polar_cuda_decode_candidates",
+    "polar_cuda_test_philox", "polar_cuda_decode_candidates", "polar_cuda_decode_batch_noalloc",
 ]
 
 
@@ -60,6 +60,7 @@ def lib():
         l.polar_cuda_decode_batch.argtypes = [vp, vp, i, i, sz, vp, vp, vp]
         l.polar_cuda_encode_batch.argtypes = [vp, vp, i, sz, vp, vp]
         l.polar_cuda_decode_candidates.argtypes = [vp, vp, i, i, sz, vp, vp, vp]
+        l.polar_cuda_decode_batch_noalloc.argtypes = [vp, vp, i, sz, vp, vp, vp]
         l.polar_cuda_crc_generate.argtypes = [i, vp, i]
         l.polar_cuda_crc_check.argtypes = [i, vp, i]
         l.polar_cuda_frozen_bits.argtypes = [i, i, _c.c_float, _c.c_char_p, vp]

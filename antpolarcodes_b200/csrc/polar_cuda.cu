@@ -76,6 +76,40 @@ bool compile_schedule_cached(TreeKind tk, int N, const std::vector<uint32_t>& fr
 
 } // namespace
 
+// ---------------------------------------------------------------- scratch of the allocation-free entry point
+// polar_cuda_decode_batch_noalloc (end of the decode section) serves callers that may not allocate device memory: code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.  Its kernels take the scratch that
+// holds the top LLR / partial-sum stages from this file-scope array instead of the handle's cudaMalloc'ed buffer.
+// Every GPU that loads the library holds the array until the process exits; every call on a device shares it.
+// In HOST code the name below is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device, with that device current, by cudaGetSymbolAddress (noalloc_scratch_for) and that pointer goes to the kernels.
+static __device__ __align__(256) unsigned char g_noallocScratch[POLAR_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+std::mutex g_noallocMu;
+constexpr int kNoallocMaxDevices = 64;
+void* g_noallocPtr[kNoallocMaxDevices] = {};
+cudaError_t g_noallocErr[kNoallocMaxDevices] = {};
+
+// Device address of g_noallocScratch on `device` (which must be the current device).  Looked up at set-up time
+// (polar_cuda_code_create) so that the entry point itself only reads the cache.
+int noalloc_scratch_for(int device, void** ptr)
+{
+    if (device < 0 || device >= kNoallocMaxDevices) return fail(POLAR_E_ARG, "no-alloc scratch: device index out of range");
+    std::lock_guard<std::mutex> lk(g_noallocMu);
+    if (!g_noallocPtr[device] && g_noallocErr[device] == cudaSuccess) {
+        void* d = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&d, g_noallocScratch);
+        if (e != cudaSuccess) { g_noallocErr[device] = e; cudaGetLastError(); }
+        else g_noallocPtr[device] = d;
+    }
+    if (!g_noallocPtr[device])
+        return fail(POLAR_E_CUDA, std::string("cudaGetSymbolAddress(no-alloc scratch): ") + cudaGetErrorString(g_noallocErr[device]));
+    *ptr = g_noallocPtr[device];
+    return POLAR_OK;
+}
+} // namespace
+
 struct polar_code {
     int device = 0, kind = 0, N = 0, lgN = 0, K = 0, kb = 0, L = 1, systematic = 1, crcBits = 0;
     std::vector<uint32_t> frozen;
@@ -554,6 +588,12 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
         }
     } while (0);
     if (rc) { polar_cuda_code_destroy(c); return rc; }
+    if (kind != POLAR_KIND_ENC) { // set-up for polar_cuda_decode_batch_noalloc: the per-device address of its static scratch
+        void* unused = nullptr;   // (a failure is kept and reported by that entry point; the other paths do not need it)
+        const std::string keep = g_lastError;
+        noalloc_scratch_for(device, &unused);
+        g_lastError = keep;
+    }
     *out = c;
     return POLAR_OK;
 }
@@ -859,6 +899,53 @@ int polar_cuda_decode_candidates(polar_code_t c, const void* llr, int llrType, i
     cudaFree(dL); cudaFree(dC); cudaFree(dN);
     if (rc) return rc;
     if (e != cudaSuccess) return fail(POLAR_E_CUDA, std::string("candidate hand-back: ") + cudaGetErrorString(e));
+    return POLAR_OK;
+}
+
+// Decoder::decode_vector over a batch WITHOUT any allocation (see g_noallocScratch above).  Same kernels and launch
+// geometry as polar_cuda_decode_batch with DEVICE buffers; only the scratch pointer differs.  Nothing here calls
+// cudaMalloc / cudaFree / an allocating routine: no staging, no quantiser copy, no event creation.
+int polar_cuda_decode_batch_noalloc(polar_code_t c, const void* llr, int llrType, size_t nFrames, uint8_t* info_out,
+                                    uint8_t* ok_out, void* stream)
+{
+    if (!c) return fail(POLAR_E_ARG, "null code handle");
+    if (c->kind != POLAR_KIND_FASTSSC_I8 && c->kind != POLAR_KIND_FASTSSC_F32 && c->kind != POLAR_KIND_SCL_I8 &&
+        c->kind != POLAR_KIND_SCL_F32)
+        return fail(POLAR_E_ARG, "no-alloc decode: the handle must be a Fast-SSC or list decoder (not an encoder or an adaptive kind)");
+    if (nFrames == 0) return POLAR_OK;
+    if (!llr || !info_out || !ok_out) return fail(POLAR_E_ARG, "no-alloc decode: llr, info_out and ok_out must be DEVICE buffers (none may be null)");
+    const bool f32Kind = (c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32);
+    if (llrType != (f32Kind ? POLAR_LLR_F32 : POLAR_LLR_I8))
+        return fail(POLAR_E_ARG, "no-alloc decode: LLRs must have the decoder's own type (float LLRs into an int8 decoder need the "
+                                 "quantiser's scratch copy: use polar_cuda_decode_batch)");
+    // scratch this handle's full grid needs: one spillWarpW-word region per resident warp
+    const size_t need = (size_t)c->geo.spillWarpW * sizeof(uint32_t) * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
+    if (need > (size_t)POLAR_NOALLOC_SCRATCH_BYTES)
+        return fail(POLAR_E_UNSUPPORTED, "no-alloc decode: this code needs " + std::to_string(need) + " bytes of scratch, the static array holds " +
+                                             std::to_string((size_t)POLAR_NOALLOC_SCRATCH_BYTES) + " (POLAR_NOALLOC_SCRATCH_BYTES): use polar_cuda_decode_batch");
+    CUDA_TRY(cudaSetDevice(c->device));
+    void* scratch = nullptr;
+    int rc = noalloc_scratch_for(c->device, &scratch); // cached by polar_cuda_code_create
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    DecodeParams p = c->geo;
+    p.cand = nullptr;
+    p.infoPos = c->dInfoPos;
+    p.crcTab = c->dSynTab;
+    p.crcInit = c->synInit;
+    p.nFrames = (long long)nFrames;
+    p.llr = llr; p.out = info_out; p.ok = ok_out;
+    p.spill = c->geo.spillWarpW ? static_cast<uint32_t*>(scratch) : nullptr; // every word is written before it is read: nothing to clear
+    p.runs = c->dRuns;
+    p.nRuns = c->nRuns;
+    if (p.useTma && ((uintptr_t)p.llr & 15u)) p.useTma = 0;
+    const int framesPerWarp = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32) ? 32 / c->L : 32;
+    const long long warpsNeeded = ((long long)nFrames + framesPerWarp - 1) / framesPerWarp;
+    const long long blocksNeeded = (warpsNeeded + c->warpsPerBlock - 1) / c->warpsPerBlock;
+    const int grid = (int)std::min<long long>(blocksNeeded, (long long)c->blocksPerSM * c->numSMs);
+    c->kernel<<<grid, c->warpsPerBlock * 32, c->smemPerBlock, st>>>(p, c->sched);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
     return POLAR_OK;
 }
 

@@ -85,6 +85,24 @@ int polar_cuda_decode_batch(polar_code_t code, const void* llr, int llrType, int
 int polar_cuda_decode_candidates(polar_code_t code, const void* llr, int llrType, int mem, size_t nFrames, uint8_t* cand_out,
                                  uint8_t* count_out, void* stream);
 
+/* Allocation-free decode.  NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and results as
+ * polar_cuda_decode_batch with DEVICE buffers, but the kernel's scratch (the top LLR / partial-sum stages it keeps in L2)
+ * lives in a file-scope static __device__ array of POLAR_NOALLOC_SCRATCH_BYTES instead of a cudaMalloc'ed buffer, and the
+ * call allocates nothing: no cudaMalloc, cudaFree, staging copy or event creation.
+ *   code     : a FASTSSC_I8 / FASTSSC_F32 / SCL_I8 / SCL_F32 handle (creating it is the set-up step and does allocate)
+ *   llr      : DEVICE, nFrames x N, the decoder's own type (int8 for the int8 kinds, float for the fp32 kinds)
+ *   info_out : DEVICE, nFrames x ceil(K/8);  ok_out : DEVICE, nFrames (required);  asynchronous on `stream`
+ * Limit: the handle's launch geometry must need at most POLAR_NOALLOC_SCRATCH_BYTES of scratch (spill words per resident
+ * warp x resident warps: e.g. Fast-SSC int8 N <= 1024 and SCL int8 L = 8 N <= 512 fit on a 148-SM B200, SCL L = 8 N = 1024
+ * does not); larger codes are rejected with POLAR_E_UNSUPPORTED and a message that states both sizes.
+ * Every GPU that loads the library holds the array until exit.  ALL calls on a device share it -- whatever the handle or the
+ * stream -- and it keeps the last call's contents (the kernels write every scratch word before they read it, so nothing
+ * has to be cleared): calls that overlap on the GPU race.  Serialise them (one stream, or events between streams). */
+#define POLAR_NOALLOC_SCRATCH_BYTES (64u << 20)
+int polar_cuda_decode_batch_noalloc(polar_code_t code, const void* llr, int llrType, size_t nFrames, uint8_t* info_out,
+                                    uint8_t* ok_out, void* stream);
+
 /* Encoder::encode_vector over nFrames frames.  info: nFrames x K/8 bytes; like the reference the
  * trailing CRC bytes of every info block are overwritten in place.  code_out: nFrames x N/8. */
 int polar_cuda_encode_batch(polar_code_t code, uint8_t* info, int mem, size_t nFrames, uint8_t* code_out,
