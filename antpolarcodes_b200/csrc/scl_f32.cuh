@@ -386,7 +386,7 @@ POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSp
 
 // ---------------------------------------------------------------- the kernel
 template <int L>
-__global__ void __launch_bounds__(512) scl_f32_kernel(const __grid_constant__ DecodeParams p,
+__global__ void __launch_bounds__(512, 1) scl_f32_kernel(const __grid_constant__ DecodeParams p,
                                                       const __grid_constant__ Schedule sched)
 {
     constexpr int lgL = Log2<L>::v, FPW = 32 / L;

@@ -1,14 +1,17 @@
 """GPU parity: the CUDA path, called through the C ABI, against the CPU oracle (and against the compiled
 reference where oracle/_ref is present) on the same seeded inputs.  Bit-exact: info bytes and verdicts."""
+import os
+
 import numpy as np
 import pytest
 
 import antpolarcodes_b200 as ap
 from polar_testlib import (KIND_FASTSSC_F32, KIND_FASTSSC_I8, KIND_SCL_F32, KIND_SCL_I8, awgn_llrs, have_ref,
-                           oracle_decode, oracle_encode, pcbench_llrs, ref_decode, ref_decode_fresh, ref_encode,
+                           oracle_decode, oracle_encode, pcbench_llrs, ref_decode, ref_decode_ex, ref_decode_fresh, ref_encode,
                            stress_llrs, workload)
 
 pytestmark = pytest.mark.gpu
+THREADS = os.cpu_count() or 1
 
 
 def _workloads(N, frozen, n, crc):
@@ -24,11 +27,8 @@ def _compare(dec, kind, N, frozen, L, sysm, crc, llr, tag):
     bad = np.where((out != eo).any(axis=1) | (ok != ek))[0]
     assert len(bad) == 0, "%s: %d/%d frames differ from the oracle, first %s" % (tag, len(bad), len(llr), bad[:5])
     if have_ref() and (sysm or N >= 256):
-        if kind == KIND_SCL_F32:  # the reference's fp32 list decoder depends on its history: fresh object per frame
-            ro, rk = ref_decode_fresh(kind, N, frozen, llr[:16], L, sysm, crc)
-            out, ok = out[:16], ok[:16]
-        else:
-            ro, rk, _ = ref_decode(kind, N, frozen, llr, L, sysm, crc)
+        # the reference's fp32 list decoder depends on its history: fresh object per frame; all host threads
+        ro, rk, _ = ref_decode_ex(kind, N, frozen, llr, L, sysm, crc, THREADS, 1, fresh=(kind == KIND_SCL_F32))
         bad = np.where((out != ro).any(axis=1) | (ok != rk))[0]
         assert len(bad) == 0, "%s: %d frames differ from the reference, first %s" % (tag, len(bad), bad[:5])
 
@@ -248,3 +248,32 @@ def test_empty_and_ragged_batches(gpu):
         assert np.array_equal(big[n - 1], big[(n - 1) % 512]) and bigk[n - 1] == bigk[(n - 1) % 512]
     p = ap.Puncturer(200, fz)
     assert p.depuncture_batch(np.zeros((0, 200), np.int8)).shape == (0, N)
+
+
+# Many distinct frames against the COMPILED REFERENCE (not the oracle restatement), all host threads: tie-break differences at
+# the 1-in-10^4 level would show here (96 / 12 / 16 frames were too few).
+MANY = [
+    # kind, N, K, construction, L, crc, frames per workload
+    (KIND_SCL_I8, 1024, 512, "5G", 8, 16, 32768),     # the headline code
+    (KIND_SCL_I8, 2048, 1024, "BB", 32, 32, 1024),    # C4
+    (KIND_SCL_F32, 1024, 512, "5G", 8, 16, 512),      # fp32 list decoder, fresh reference object per frame
+    (KIND_FASTSSC_I8, 1024, 512, "BB", 1, 0, 65536),  # C1
+    (KIND_FASTSSC_F32, 256, 128, "BB", 1, 0, 65536),  # C2
+]
+
+
+@pytest.mark.parametrize("kind,N,K,ctype,L,crc,n", MANY)
+def test_many_frames_against_the_compiled_reference(gpu, kind, N, K, ctype, L, crc, n):
+    if not have_ref():
+        pytest.skip("oracle/_ref not built")
+    frozen = ap.frozen_bits(N, K, 0.0, ctype)
+    f32 = kind in (KIND_FASTSSC_F32, KIND_SCL_F32)
+    dec = ap.PolarDecoder(N, L, frozen, "float" if f32 else "char")
+    dec._kind = kind
+    dec.setErrorDetection(crc)
+    for name in ("awgn", "awgn0", "pcbench", "stress"):
+        llr = workload(name, kind, N, frozen, n, crc, seed=1000 + len(name))
+        out, ok = dec.decode_batch(llr)
+        ro, rk, _ = ref_decode_ex(kind, N, frozen, llr, L, 1, crc, THREADS, 1, fresh=(kind == KIND_SCL_F32))
+        bad = np.where((out != ro).any(axis=1) | (ok != rk))[0]
+        assert len(bad) == 0, "%s: %d/%d frames differ from the reference, first %s" % (name, len(bad), n, bad[:5])
