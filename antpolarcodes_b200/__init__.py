@@ -31,6 +31,7 @@ EXPORTS = [
     "polar_cuda_depuncture_batch", "polar_cuda_puncture_packed_batch",
     "polar_cuda_sim_create", "polar_cuda_sim_destroy", "polar_cuda_sim_run", "polar_cuda_sim_buffers", "polar_cuda_sim_launches",
     "polar_cuda_test_philox", "polar_cuda_decode_candidates", "polar_cuda_decode_batch_noalloc",
+    "polar_cuda_decode_soft_batch",
 ]
 
 
@@ -61,6 +62,7 @@ def lib():
         l.polar_cuda_encode_batch.argtypes = [vp, vp, i, sz, vp, vp]
         l.polar_cuda_decode_candidates.argtypes = [vp, vp, i, i, sz, vp, vp, vp]
         l.polar_cuda_decode_batch_noalloc.argtypes = [vp, vp, i, sz, vp, vp, vp]
+        l.polar_cuda_decode_soft_batch.argtypes = [vp, vp, i, sz, vp, vp, vp]
         l.polar_cuda_crc_generate.argtypes = [i, vp, i]
         l.polar_cuda_crc_check.argtypes = [i, vp, i]
         l.polar_cuda_frozen_bits.argtypes = [i, i, _c.c_float, _c.c_char_p, vp]
@@ -334,6 +336,30 @@ class PolarDecoder:
     def fallbacks(self):
         """adaptive decoders: frames redone by the list decoder so far"""
         return self._get().fallbacks()
+
+    def soft_batch(self, llr, want_info=True):
+        """Decoder::getSoftCodeword / getSoftInformation over a batch (int8 Fast-SSC only): [nFrames, N] int8 LLRs ->
+        ([nFrames, N] int8 soft codeword, [nFrames, K] int8 soft information or None)."""
+        if llr.ndim != 2 or llr.shape[1] != self._N:
+            raise RuntimeError("Input vector size mismatch!")
+        n, K = llr.shape[0], self.infoLength()
+        if _is_torch(llr):
+            import torch
+            if llr.dtype != torch.int8:
+                raise RuntimeError("soft outputs take int8 LLRs")
+            soft = torch.empty((n, self._N), dtype=torch.int8, device=llr.device)
+            info = torch.empty((n, K), dtype=torch.int8, device=llr.device) if want_info else None
+        else:
+            if llr.dtype != _np.int8:
+                raise RuntimeError("soft outputs take int8 LLRs")
+            llr = _np.ascontiguousarray(llr)
+            soft = _np.empty((n, self._N), _np.int8)
+            info = _np.empty((n, K), _np.int8) if want_info else None
+        lp, mem = _buf(llr)
+        sp, _ = _buf(soft)
+        ip = _buf(info)[0] if info is not None else None
+        _check(lib().polar_cuda_decode_soft_batch(self._get()._h, lp, mem, n, sp, ip, 0))
+        return soft, info
 
     def decode_vector(self, llr):
         """float32[N] or int8[N] -> uint8[K/8]; the detector verdict is dropped, as in decoder_python.cc."""

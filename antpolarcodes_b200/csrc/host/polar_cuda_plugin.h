@@ -27,6 +27,7 @@
 #include <polarcode/errordetection/errordetector.h>
 #include <polarcode/puncturer.h>
 #include <cstring>
+#include <functional>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -58,6 +59,24 @@ inline int fusedCrcBits(ErrorDetection::Detector* d)
 // Decoder::getSoftCodeword / getSoftInformation read mBitContainer (decoder.cpp:147-152).  The kernels keep partial sums
 // as packed sign bits and never fill a byte / float container, so a CUDA decoder's bit container refuses instead of
 // returning stale memory.
+// int8 Fast-SSC: the byte soft bits are produced on demand by polar_cuda_decode_soft_batch for the frame decode() saw last
+// (the decoder hands its LLR snapshot over through `fill`), then served by the CharContainer accessors as usual.
+class SoftOnDemandChar : public CharContainer
+{
+public:
+    std::function<void(CharContainer&)> fill;
+    bool stale = false;
+    SoftOnDemandChar(size_t size, const std::vector<unsigned>& frozen) : CharContainer(size, frozen) {}
+    void refresh()
+    {
+        if (stale && fill) { fill(*this); stale = false; }
+    }
+    void getSoftBits(void* pData) override { refresh(); CharContainer::getSoftBits(pData); }
+    void getSoftInformation(void* pData) override { refresh(); CharContainer::getSoftInformation(pData); }
+    void getPackedBits(void* pData) override { refresh(); CharContainer::getPackedBits(pData); }
+    void getPackedInformationBits(void* pData) override { refresh(); CharContainer::getPackedInformationBits(pData); }
+};
+
 template <class Base>
 class NoSoftBits : public Base
 {
@@ -104,6 +123,7 @@ class CudaDecoder : public Decoder
     size_t mListSize;
     int mDevice;
     int mAdaptiveKind; // POLAR_KIND_ADAPTIVE_* or -1
+    std::vector<char> mLastLlr; // int8 Fast-SSC: the frame decode() saw last (soft outputs are computed from it on demand)
 
     int kind() const
     {
@@ -134,6 +154,16 @@ public:
         if (FLOAT) {
             mLlrContainer = new FloatContainer(blockLength);
             mBitContainer = new CudaDetail::NoSoftBits<FloatContainer>(blockLength, mFrozenBits);
+        } else if (mListSize == 1 && mAdaptiveKind < 0) { // FastSscCudaChar: getSoftCodeword / getSoftInformation work
+            mLlrContainer = new CharContainer(blockLength);
+            auto* soft = new CudaDetail::SoftOnDemandChar(blockLength, mFrozenBits);
+            soft->fill = [this](CharContainer& dst) {
+                std::vector<char> bytes(mBlockLength);
+                CudaDetail::check(polar_cuda_decode_soft_batch(code(), reinterpret_cast<const int8_t*>(mLastLlr.data()), POLAR_MEM_HOST, 1,
+                                                               reinterpret_cast<int8_t*>(bytes.data()), nullptr, nullptr));
+                dst.insertLlr(bytes.data()); // N raw bytes into the container's data
+            };
+            mBitContainer = soft;
         } else {
             mLlrContainer = new CharContainer(blockLength);
             mBitContainer = new CudaDetail::NoSoftBits<CharContainer>(blockLength, mFrozenBits);
@@ -169,6 +199,10 @@ public:
         const void* llr = FLOAT ? static_cast<const void*>(static_cast<FloatContainer*>(mLlrContainer)->data())
                                 : static_cast<const void*>(static_cast<CharContainer*>(mLlrContainer)->data());
         polar_code_t h = code();
+        if (auto* soft = dynamic_cast<CudaDetail::SoftOnDemandChar*>(mBitContainer)) {
+            mLastLlr.assign(static_cast<const char*>(llr), static_cast<const char*>(llr) + mBlockLength);
+            soft->stale = true;
+        }
         if (mHandle.hostDetector()) {
             decodeWithHostDetector(llr, FLOAT ? POLAR_LLR_F32 : POLAR_LLR_I8, 1, mOutputContainer, &ok);
             return ok != 0;

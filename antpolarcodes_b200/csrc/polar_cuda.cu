@@ -6,6 +6,7 @@
 #include "batch_kernels.cuh"
 #include "decode_params.h"
 #include "encode.cuh"
+#include "fastssc_i8_soft.cuh"
 #include "kernels.h"
 #include "puncture.cuh"
 #include "schedule.h"
@@ -146,6 +147,8 @@ struct polar_code {
     cudaEvent_t scratchFree = nullptr;
     cudaStream_t scratchStream = nullptr;
     bool scratchBusy = false;
+    uint32_t* dSoftScratch = nullptr; // soft-output kernel: LLR stages + byte partial sums per resident warp
+    size_t softScratchWords = 0;
     // adaptive kinds: the two decoders and the compaction scratch
     polar_code* fast = nullptr;
     polar_code* list = nullptr;
@@ -424,7 +427,7 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaSetDevice(c->device);
     cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab);
     cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
-    cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns);
+    cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns); cudaFree(c->dSoftScratch);
     cudaFree(c->dFailIdx); cudaFree(c->dFailCount); cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
     if (c->hFailCount) cudaFreeHost(c->hFailCount);
     if (c->scratchFree) cudaEventDestroy(c->scratchFree);
@@ -899,6 +902,67 @@ int polar_cuda_decode_candidates(polar_code_t c, const void* llr, int llrType, i
     cudaFree(dL); cudaFree(dC); cudaFree(dN);
     if (rc) return rc;
     if (e != cudaSuccess) return fail(POLAR_E_CUDA, std::string("candidate hand-back: ") + cudaGetErrorString(e));
+    return POLAR_OK;
+}
+
+// Decoder::getSoftCodeword / getSoftInformation after FastSscFipChar::decode (decoder.cpp:147-152) over a batch.
+int polar_cuda_decode_soft_batch(polar_code_t c, const int8_t* llr, int mem, size_t nFrames, int8_t* soft_out,
+                                 int8_t* soft_info_out, void* stream)
+{
+    if (!c) return fail(POLAR_E_ARG, "null code handle");
+    if (c->kind != POLAR_KIND_FASTSSC_I8) return fail(POLAR_E_UNSUPPORTED, "soft outputs exist for the int8 Fast-SSC decoder only");
+    if (nFrames == 0) return POLAR_OK;
+    if (!llr || !soft_out) return fail(POLAR_E_ARG, "null buffer");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    SoftParams p{};
+    p.N = c->N; p.lgN = c->lgN; p.K = c->K;
+    p.bitsOff = llr_woff(c->lgN + 1);
+    p.warpW = 32 * (p.bitsOff + std::max(1, c->N / 4));
+    p.infoPos = c->dInfoPos;
+    p.nFrames = (long long)nFrames;
+    const int warpsPerBlock = 8;
+    const long long groups = ((long long)nFrames + 31) / 32;
+    const int grid = (int)std::min<long long>((groups + warpsPerBlock - 1) / warpsPerBlock, (long long)c->numSMs * (c->N >= 2048 ? 1 : 2));
+    const size_t words = (size_t)p.warpW * warpsPerBlock * grid;
+    if (words > c->softScratchWords) {
+        cudaFree(c->dSoftScratch);
+        c->dSoftScratch = nullptr; c->softScratchWords = 0;
+        CUDA_TRY(cudaMalloc(&c->dSoftScratch, words * sizeof(uint32_t)));
+        c->softScratchWords = words;
+    }
+    p.scratch = c->dSoftScratch;
+    Schedule sched; // the node program with its op codes (c->sched carries the throughput kernel's handler ids instead)
+    memset(&sched, 0, sizeof(sched));
+    memcpy(sched.ops, c->ops.data(), c->ops.size() * sizeof(uint32_t));
+    const size_t llrBytes = nFrames * (size_t)c->N, infoBytes = nFrames * (size_t)c->K;
+    int8_t *dL = nullptr, *dS = nullptr, *dI = nullptr;
+    if (mem == POLAR_MEM_HOST) {
+        cudaError_t e;
+        if ((e = cudaMalloc(&dL, llrBytes)) != cudaSuccess || (e = cudaMalloc(&dS, llrBytes)) != cudaSuccess ||
+            (soft_info_out && (e = cudaMalloc(&dI, infoBytes)) != cudaSuccess)) {
+            cudaFree(dL); cudaFree(dS); cudaFree(dI);
+            cudaGetLastError();
+            return fail(POLAR_E_NOMEM, std::string("soft-output staging: ") + cudaGetErrorString(e));
+        }
+        p.llr = dL; p.soft = dS; p.softInfo = soft_info_out ? dI : nullptr;
+    } else {
+        p.llr = llr; p.soft = soft_out; p.softInfo = soft_info_out;
+    }
+    cudaError_t e = cudaSuccess;
+    if (mem == POLAR_MEM_HOST) e = cudaMemcpyAsync(dL, llr, llrBytes, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        fastssc_i8_soft_kernel<<<grid, warpsPerBlock * 32, 0, st>>>(p, sched);
+        c->launches++;
+        e = cudaGetLastError();
+    }
+    if (mem == POLAR_MEM_HOST) {
+        if (e == cudaSuccess) e = cudaMemcpyAsync(soft_out, dS, llrBytes, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess && soft_info_out) e = cudaMemcpyAsync(soft_info_out, dI, infoBytes, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        cudaFree(dL); cudaFree(dS); cudaFree(dI);
+    }
+    if (e != cudaSuccess) return fail(POLAR_E_CUDA, std::string("soft-output decode: ") + cudaGetErrorString(e));
     return POLAR_OK;
 }
 

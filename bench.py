@@ -52,6 +52,8 @@ WORKLOADS = {
                   label="SCL L=32 + CRC32, N=2048 K=1024, BB frozen set, int8 LLR, Eb/N0=2dB"),
     "scl8_n512": dict(N=512, K=256, ctype="BB", L=8, crc=16, frames=1 << 19, e2e_frames=1 << 17, parity=1 << 14, cpu_s=2.0,
                       label="SCL L=8 + CRC16, N=512 K=256, BB frozen set, int8 LLR, Eb/N0=2dB (occupancy experiments)"),
+    "fastssc_soft": dict(N=1024, K=512, ctype="BB", L=1, crc=0, frames=1 << 18, e2e_frames=1 << 17, soft=True, parity=1 << 14, cpu_s=2.0,
+                         label="Fast-SSC int8 soft outputs (getSoftCodeword + getSoftInformation), N=1024 K=512, BB frozen set, Eb/N0=2dB"),
     # pcbench-style comparability rows (benchmark/main_benchmark.cpp:202-241): iid N(0, 0.5) floats, not codewords, fed to the
     # int8 decoders through decode_vector(const float*), i.e. the quantiser runs inside the timed region
     "pcbench_scl8": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 18, e2e_frames=1 << 17, pcbench=True, parity=1 << 14, cpu_s=3.0,
@@ -59,7 +61,7 @@ WORKLOADS = {
     "pcbench_fastssc": dict(N=1024, K=512, ctype="BB", L=1, crc=0, frames=1 << 19, e2e_frames=1 << 18, pcbench=True, parity=1 << 17, cpu_s=3.0,
                             label="pcbench-style: Fast-SSC int8 decoder fed iid N(0,0.5) float inputs, N=1024 K=512, BB frozen set"),
 }
-ALSO = ["fastssc", "fastssc_f32", "encode", "scl32", "scl8_f32", "pcbench_scl8", "pcbench_fastssc"]
+ALSO = ["fastssc", "fastssc_f32", "encode", "scl32", "scl8_f32", "fastssc_soft", "pcbench_scl8", "pcbench_fastssc"]
 METRIC = "info-bit Gbps (N=1024 K=512, SCL L=8+CRC16)"
 EBN0_DB = 2.0
 
@@ -540,9 +542,101 @@ def measure_encoder(ctx, args, name, wl, steps, warmup, with_cpu=True):
             "check": check}
 
 
+def measure_soft(ctx, args, name, wl, steps, warmup, with_cpu=True):
+    """Decoder::getSoftCodeword / getSoftInformation over a batch (SURVEY.md 8f-4): N int8 LLRs -> N soft bytes + K soft info bytes."""
+    import antpolarcodes_b200 as ap
+    torch, device, world, rank = ctx.torch, ctx.device, ctx.world, ctx.rank
+    N, K = wl["N"], wl["K"]
+    frames = args.frames or wl["frames"]
+    e2e_frames = min(args.e2e_frames or wl["e2e_frames"], frames)
+    frozen = ap.frozen_bits(N, K, 0.0, wl["ctype"])
+    dec = ap.PolarDecoder(N, 1, frozen, "char", device=ctx.local)
+    dec.setErrorDetection(0)
+    llr, _ = make_llrs_on_device(ctx, ap, wl, frozen, frames, 0x50F7 + rank)
+    soft = torch.empty((frames, N), dtype=torch.int8, device=device)
+    info = torch.empty((frames, K), dtype=torch.int8, device=device)
+    h = dec._get()._h
+    L_ = ap.lib()
+
+    def step(l=llr, s_=soft, i_=info, mem=ap.MEM_DEVICE):
+        rc = L_.polar_cuda_decode_soft_batch(h, l.data_ptr(), mem, l.shape[0], s_.data_ptr(), i_.data_ptr(), ctx.sp)
+        assert rc == 0, L_.polar_cuda_last_error()
+    for _ in range(warmup):
+        step()
+    ctx.barrier()
+    sampler = ClockSampler(ctx.local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    l0 = dec._get().launches()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    ctx.barrier()
+    ev[0].record(ctx.stream)
+    for s_i in range(steps):
+        step()
+        ev[s_i + 1].record(ctx.stream)
+    ctx.barrier()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    k_ms = float(np.mean([ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]))
+    launches = dec._get().launches() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    h_llr = torch.empty((e2e_frames, N), dtype=torch.int8).pin_memory()
+    h_llr.copy_(llr[:e2e_frames])
+    h_soft = torch.empty((e2e_frames, N), dtype=torch.int8).pin_memory()
+    h_info = torch.empty((e2e_frames, K), dtype=torch.int8).pin_memory()
+    step(h_llr, h_soft, h_info, ap.MEM_HOST)
+    ctx.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ctx.stream)
+    for _ in range(steps):
+        step(h_llr, h_soft, h_info, ap.MEM_HOST)
+    e1.record(ctx.stream)
+    ctx.barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    e2e_match = bool((h_soft == soft[:e2e_frames].cpu()).all().item())
+    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        ctx.dist.all_reduce(t, op=ctx.dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(t[0].item()), float(t[1].item())
+    if rank != 0:
+        return None
+    hbm_peak, _, which = peaks()
+    value = world * frames * steps * K / (total_ms * 1e-3) / 1e9
+    e2e_val = world * e2e_frames * steps * K / (e2e_ms * 1e-3) / 1e9
+    bpf = 2 * N + K
+    hbm = frames * bpf / (k_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "achieved": hbm, "peak": hbm_peak, "unit": "GB/s", "frac": hbm / hbm_peak, "traffic": None,
+            "peak_source": which + " hbm copy", "algorithmic_bytes": bpf * frames, "kernel_ms": k_ms, "frames_per_launch": frames}
+    check = {"frames": frames}
+    cpu = None
+    try:
+        from polar_testlib import KIND_FASTSSC_I8, have_ref, ref_soft
+        if have_ref():
+            npar = min(args.parity if args.parity >= 0 else wl["parity"], frames)
+            hl = np.ascontiguousarray(llr[:npar].cpu().numpy())
+            t0 = time.perf_counter()
+            rs, ri = ref_soft(KIND_FASTSSC_I8, N, frozen, hl)
+            tt = time.perf_counter() - t0
+            bad = int(((rs != soft[:npar].cpu().numpy()).any(axis=1) | (ri != info[:npar].cpu().numpy()).any(axis=1)).sum())
+            check.update({"parity_frames": npar, "parity_mismatches": bad, "parity_against": "unmodified reference (oracle/_ref): getSoftCodeword + getSoftInformation"})
+            if with_cpu:
+                cpu = {"value": npar * K / tt / 1e9, "unit": "Gbit/s", "cores": 1, "kind": "reference",
+                       "sample": "%d frames: FastSscFipChar decode_vector + getSoftCodeword + getSoftInformation, one thread, %.2f s" % (npar, tt)}
+    except Exception as e:
+        cpu = {"value": None, "unit": "Gbit/s", "cores": 0, "kind": "reference", "sample": "failed: %r" % (e,)}
+    return {"metric": wl["label"], "value": value, "unit": "Gbit/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": total_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": wl["label"], "frames_per_step_per_gpu": frames, "e2e_frames_per_step_per_gpu": e2e_frames,
+                       "cache": "inputs larger than L2 (%d MiB in+out per step)" % (frames * bpf >> 20), "parallelism": "frames sharded x%d" % world},
+            "e2e": {"value": e2e_val, "unit": "Gbit/s", "h2d_bytes_per_step": e2e_frames * N, "d2h_bytes_per_step": e2e_frames * (N + K),
+                    "matches_device_run": e2e_match},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+            "speedup_e2e_vs_cpu_baseline": (e2e_val / cpu["value"]) if cpu and cpu.get("value") else None, "check": check}
+
+
 def measure(ctx, args, name, steps, warmup, with_cpu=True):
     wl = WORKLOADS[name]
-    fn = measure_encoder if wl.get("encoder") else measure_decoder
+    fn = measure_encoder if wl.get("encoder") else measure_soft if wl.get("soft") else measure_decoder
     rec = fn(ctx, args, name, wl, steps, warmup, with_cpu)
     ctx.torch.cuda.empty_cache()
     return rec

@@ -85,6 +85,15 @@ int polar_cuda_decode_batch(polar_code_t code, const void* llr, int llrType, int
 int polar_cuda_decode_candidates(polar_code_t code, const void* llr, int llrType, int mem, size_t nFrames, uint8_t* cand_out,
                                  uint8_t* count_out, void* stream);
 
+/* Decoder::getSoftCodeword / getSoftInformation (src/polarcode/decoding/decoder.cpp:147-152) after FastSscFipChar::decode, over
+ * nFrames frames: the N byte partial sums ("soft bits", include/polarcode/decoding/fip_char.h:164-220) the root node leaves in
+ * the decoder's bit container, byte for byte what the reference returns (sign = hard decision; R0 127, R1 the LLR, REP the
+ * saturating sum, SPC the LLR with one byte negated, inner nodes the raw byte XOR of their halves), and the same bytes
+ * gathered at the K information positions.  int8 Fast-SSC handles only (POLAR_E_UNSUPPORTED otherwise).
+ *   llr : nFrames x N int8;  soft_out : nFrames x N int8;  soft_info_out : nFrames x K int8 or NULL;  mem as in decode_batch */
+int polar_cuda_decode_soft_batch(polar_code_t code, const int8_t* llr, int mem, size_t nFrames, int8_t* soft_out,
+                                 int8_t* soft_info_out, void* stream);
+
 /* Allocation-free decode.  NO COUNTERPART IN THE REFERENCE: added for callers that cannot
  * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and results as
  * polar_cuda_decode_batch with DEVICE buffers, but the kernel's scratch (the top LLR / partial-sum stages it keeps in L2)

@@ -4,6 +4,7 @@
 
 namespace oracle {
 int fastssc_i8_decode(int N, const uint8_t* fm, int systematic, int crcBits, const int8_t* llr, uint8_t* out);
+void fastssc_i8_soft(int N, const uint8_t* fm, const int8_t* llr, int8_t* soft);
 void fastssc_i8_stats(int N, const uint8_t* fm, long* counts, long* sizes);
 int scl_i8_decode(int N, int L, const uint8_t* fm, int systematic, int crcBits, const int8_t* llr, uint8_t* out);
 void scl_i8_stats(int N, const uint8_t* fm, long* counts, long* sizes);
@@ -50,5 +51,13 @@ extern "C" int oracle_tree_stats(int kind, int N, const uint32_t* frozen, int nF
     if (kind == ORACLE_FASTSSC_I8) fastssc_i8_stats(N, fm.data(), counts, sizes);
     else if (kind == ORACLE_SCL_I8) scl_i8_stats(N, fm.data(), counts, sizes);
     else return -2;
+    return 0;
+}
+
+// Soft codeword of the int8 Fast-SSC decoder (Decoder::getSoftCodeword, decoder.cpp:147): nFrames x N bytes
+extern "C" int oracle_fastssc_i8_soft(int N, const uint32_t* frozen, int nFrozen, const int8_t* llr, long nFrames, int8_t* soft)
+{
+    std::vector<uint8_t> fm = frozen_mask(N, frozen, nFrozen);
+    for (long f = 0; f < nFrames; ++f) fastssc_i8_soft(N, fm.data(), llr + f * N, soft + f * N);
     return 0;
 }

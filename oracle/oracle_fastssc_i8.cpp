@@ -148,7 +148,16 @@ static void decode_node(const int8_t* llr, int8_t* bits, const uint8_t* fm, int 
     for (int i = 0; i < h; ++i) child[i] = g_i8(llr[i], llr[i + h], bits[i]);
     decode_node(child.data(), bits + h, fm + h, h, st);
     tally(st, ORACLE_NODE_COMBINE, h);
-    for (int i = 0; i < h; ++i) bits[i] = (int8_t)(bits[i] ^ bits[i + h]);
+    if (n <= VEC) { // ShortRateRNode -> CombineBitsShort (fip_char.h:185-205): both halves are clamped to -127 first.  Only
+                    // the byte values change (soft outputs), never a sign.
+        for (int i = 0; i < h; ++i) {
+            const int8_t l = bits[i] < -127 ? -127 : bits[i], r = bits[i + h] < -127 ? -127 : bits[i + h];
+            bits[i] = (int8_t)(l ^ r);
+            bits[i + h] = r;
+        }
+    } else { // RateRNode -> CombineInPlace (fip_char.h:164-171): raw byte XOR, right half untouched
+        for (int i = 0; i < h; ++i) bits[i] = (int8_t)(bits[i] ^ bits[i + h]);
+    }
 }
 
 int fastssc_i8_decode(int N, const uint8_t* fm, int systematic, int crcBits, const int8_t* llr,
@@ -161,6 +170,14 @@ int fastssc_i8_decode(int N, const uint8_t* fm, int systematic, int crcBits, con
     extract_info(hard.data(), fm, N, systematic, out);
     int K = N - count_frozen(fm, N);
     return crc_check(crcBits, out, (K + 7) / 8); // fastssc_fip_char.cpp:627-628
+}
+
+// Decoder::getSoftCodeword after FastSscFipChar::decode (decoder.cpp:147, bitcontainer.cpp:566-569): the N byte "soft bits"
+// the root node left in mBitContainer -- R0: 127, R1: the LLR, REP: the saturating sum, SPC: the LLR with one byte negated,
+// inner nodes: raw byte XOR of the halves (sign = bit value, lower bits carry no meaning but are reproducible).
+void fastssc_i8_soft(int N, const uint8_t* fm, const int8_t* llr, int8_t* soft)
+{
+    decode_node(llr, soft, fm, N, nullptr);
 }
 
 void fastssc_i8_stats(int N, const uint8_t* fm, long* counts, long* sizes)

@@ -280,6 +280,30 @@ int polar_ref_puncturer(int blockLength, const uint32_t* frozen, int nFrozen, in
     }
 }
 
+// Decoder::getSoftCodeword / getSoftInformation (decoder.cpp:147-152) after decode_vector, for any decoder kind that
+// takes the given LLR type.  soft: nFrames x N elements, softInfo: nFrames x K elements (int8 for the char decoders,
+// float for the float decoders); either may be null.
+int polar_ref_soft(void* h, const void* llr, long nFrames, void* soft, void* softInfo)
+{
+    RefCode* c = static_cast<RefCode*>(h);
+    const bool isFloat = (c->kind == KIND_FASTSSC_F32 || c->kind == KIND_SCL_F32);
+    const size_t es = isFloat ? 4 : 1, kb = (c->K + 7) / 8;
+    try {
+        Decoding::Decoder* d = make_decoder(*c);
+        std::vector<uint8_t> out(kb);
+        for (long f = 0; f < nFrames; ++f) {
+            if (isFloat) d->decode_vector(static_cast<const float*>(llr) + f * c->N, out.data());
+            else d->decode_vector(static_cast<const char*>(llr) + f * c->N, out.data());
+            if (soft) d->getSoftCodeword(static_cast<char*>(soft) + f * c->N * es);
+            if (softInfo) d->getSoftInformation(static_cast<char*>(softInfo) + f * c->K * es);
+        }
+        delete d;
+        return 0;
+    } catch (...) {
+        return -1;
+    }
+}
+
 int polar_ref_hw_threads() { return (int)std::thread::hardware_concurrency(); }
 
 } // extern "C"

@@ -150,6 +150,35 @@ def ref_decode_fresh(kind, N, frozen, llr, L=1, systematic=1, crc=0):
     return np.concatenate(outs), np.concatenate(oks)
 
 
+def ref_soft(kind, N, frozen, llr, L=1, systematic=1, crc=0):
+    """(soft codeword [nF, N], soft information [nF, K]) of the reference decoder: Decoder::getSoftCodeword /
+    getSoftInformation (decoder.cpp:147-152) after decode_vector."""
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    llr = np.ascontiguousarray(llr)
+    nF, K = llr.shape[0], N - len(frozen)
+    soft, info = np.zeros((nF, N), llr.dtype), np.zeros((nF, K), llr.dtype)
+    fn = ref().polar_ref_soft
+    fn.argtypes = [_vp, _vp, _l, _vp, _vp]
+    fn.restype = _i
+    h = ref().polar_ref_code_create(kind, N, _ptr(frozen), len(frozen), L, systematic, crc)
+    rc = fn(h, _ptr(llr), nF, _ptr(soft), _ptr(info))
+    ref().polar_ref_code_destroy(h)
+    if rc:
+        raise RuntimeError("reference soft output threw")
+    return soft, info
+
+
+def oracle_fastssc_i8_soft(N, frozen, llr):
+    """soft codeword of the int8 Fast-SSC oracle, [nF, N] int8"""
+    frozen = np.ascontiguousarray(frozen, np.uint32)
+    llr = np.ascontiguousarray(llr, np.int8)
+    soft = np.zeros(llr.shape, np.int8)
+    fn = oracle().oracle_fastssc_i8_soft
+    fn.argtypes = [_i, _vp, _i, _vp, _l, _vp]
+    assert fn(N, _ptr(frozen), len(frozen), _ptr(llr), llr.shape[0], _ptr(soft)) == 0
+    return soft
+
+
 def is_float_kind(kind):
     return kind in (KIND_FASTSSC_F32, KIND_SCL_F32, KIND_ADAPTIVE_F32, KIND_ADAPTIVE_MIXED)
 
