@@ -23,6 +23,8 @@ struct EncodeParams {
     uint32_t genInit;
     long long nFrames;
     int N, lgN, K, kb, nb, crcBits, systematic;
+    int vecIn;              // info rows are 16-byte aligned (encode_reg_kernel: 128-bit loads)
+    int byteOut;            // codeword rows are not 4-byte aligned (encode_kernel: byte stores)
 };
 
 POLAR_DEV uint32_t inword_transform(uint32_t v)
@@ -129,8 +131,10 @@ __global__ void __launch_bounds__(256) encode_kernel(const __grid_constant__ Enc
 #pragma unroll
             for (int j = 0; j < WPL; ++j) {
                 const uint32_t o = __byte_perm(__brev(word[j]), 0u, 0x0123u);
-                if (p.N >= 32) {
+                if (p.N >= 32 && !p.byteOut) {
                     reinterpret_cast<uint32_t*>(gcode)[j * 32 + g] = o;
+                } else if (p.N >= 32) {
+                    for (int i = 0; i < 4; ++i) gcode[4 * (j * 32 + g) + i] = (uint8_t)(o >> (8 * i));
                 } else {
                     for (int i = 0; i < p.nb; ++i) gcode[i] = (uint8_t)(o >> (8 * i));
                 }
@@ -216,6 +220,127 @@ __global__ void __launch_bounds__(128) encode_thread_kernel(const __grid_constan
     }
 }
 
+// ---------------------------------------------------------------- one frame per thread, no shared staging of the codeword
+// (N = 32 W <= 1024, kb % 4 == 0).  Second generation of the kernel above:
+//   * words are kept BIT-REVERSED (code position i of a word = bit 31 - i), the order of the MSB-first bytes on both sides:
+//     the info words are the big-endian loads themselves, a codeword word is one byte permutation away from memory order, the
+//     in-word butterflies shift left (v ^= (v << s) & m);
+//   * the scatter program sits in the constant bank (kernel parameter): run r of code word j is one funnel shift of two
+//     neighbouring info words and one masked OR -- indices, shift and mask are uniform-datapath values, the thread spends
+//     two shared loads, SHF.L.W and LOP3;
+//   * a thread loads its own info row (128- or 256-bit loads, rows of one warp are contiguous) and stores its own codeword
+//     (STG.256 where the codeword has eight words or more): no block-wide synchronisation at all.
+static constexpr int ENC_MAX_RUNS = 512; // 16 runs per word x 32 words: every frozen set of N <= 1024 fits
+struct EncodeProgram {
+    uint32_t maskRev[32];             // info positions of code word j, bit-reversed
+    uint16_t first[34];               // runs of word j: first[j] .. first[j+1]-1
+    uint4 run[ENC_MAX_RUNS];          // x = byte offset of the row of the HIGH source word (row = info word index + 1; row 0 and
+};                                    // row kbw+1 are zero pads), y = funnel shift, z = mask of the destination field (reversed)
+
+POLAR_DEV uint32_t inword_transform_rev(uint32_t v)
+{
+    v ^= (v << 1) & 0xAAAAAAAAu;
+    v ^= (v << 2) & 0xCCCCCCCCu;
+    v ^= (v << 4) & 0xF0F0F0F0u;
+    v ^= (v << 8) & 0xFF00FF00u;
+    v ^= (v << 16) & 0xFFFF0000u;
+    return v;
+}
+
+POLAR_DEV void stg256(uint32_t* dst, const uint32_t* v)
+{
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]),
+                 "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+}
+
+static constexpr int ENC_REG_THREADS = 128;
+template <int W>
+__global__ void __launch_bounds__(ENC_REG_THREADS) encode_reg_kernel(const __grid_constant__ EncodeParams p, const __grid_constant__ EncodeProgram prog)
+{
+    extern __shared__ __align__(16) uint32_t esm[]; // row r of thread t at esm[r * 128 + t]: conflict free for any uniform r
+    const int tid = threadIdx.x, kbw = p.kb >> 2;
+    uint32_t* mine = esm + tid;
+    mine[0] = 0u;
+    mine[(kbw + 1) * ENC_REG_THREADS] = 0u;
+    const long long stride = (long long)gridDim.x * ENC_REG_THREADS;
+    for (long long frame = (long long)blockIdx.x * ENC_REG_THREADS + tid; frame < p.nFrames; frame += stride) {
+        uint32_t* ginfo = reinterpret_cast<uint32_t*>(p.info + frame * p.kb);
+        if (p.vecIn) {
+            for (int i = 0; i < kbw; i += 4) {
+                const uint4 q = *reinterpret_cast<const uint4*>(ginfo + i);
+                mine[(i + 1) * ENC_REG_THREADS] = __byte_perm(q.x, 0u, 0x0123u);
+                mine[(i + 2) * ENC_REG_THREADS] = __byte_perm(q.y, 0u, 0x0123u);
+                mine[(i + 3) * ENC_REG_THREADS] = __byte_perm(q.z, 0u, 0x0123u);
+                mine[(i + 4) * ENC_REG_THREADS] = __byte_perm(q.w, 0u, 0x0123u);
+            }
+        } else {
+            for (int i = 0; i < kbw; ++i) mine[(i + 1) * ENC_REG_THREADS] = __byte_perm(ginfo[i], 0u, 0x0123u);
+        }
+        if (p.crcBits) { // Detector::generate: the checksum is linear in the info bits (crc_host.h); trailer bits weigh 0
+            uint32_t crc = p.genInit;
+            for (int i = 0; i < kbw; ++i) {
+                const uint32_t w = mine[(i + 1) * ENC_REG_THREADS];
+#pragma unroll 8
+                for (int b = 0; b < 32; ++b) crc ^= __ldg(p.genTab + 32 * i + b) & (0u - ((w >> (31 - b)) & 1u));
+            }
+            uint32_t last = mine[kbw * ENC_REG_THREADS];
+            if (p.crcBits == 8) last = (last & ~0xFFu) | (crc & 0xFFu);
+            else if (p.crcBits == 16) last = (last & ~0xFFFFu) | (crc & 0xFFFFu);   // big-endian trailer: crc16.cpp:35-43
+            else last = __byte_perm(crc, 0u, 0x0123u);                             // native little-endian u32: crc32.cpp:55-66
+            mine[kbw * ENC_REG_THREADS] = last;
+            ginfo[kbw - 1] = __byte_perm(last, 0u, 0x0123u);
+        }
+        uint32_t word[W];
+#pragma unroll
+        for (int j = 0; j < W; ++j) {
+            uint32_t v = 0;
+            const int r1 = prog.first[j + 1];
+            for (int r = prog.first[j]; r < r1; ++r) { // uniform: every thread of the grid walks the same runs
+                const uint4 e = prog.run[r];
+                const uint32_t* hi = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(mine) + e.x);
+                v |= __funnelshift_l(hi[ENC_REG_THREADS], hi[0], e.y) & e.z;
+            }
+            word[j] = v;
+        }
+        for (int pass = 0; pass < (p.systematic ? 2 : 1); ++pass) {
+#pragma unroll
+            for (int j = 0; j < W; ++j) {
+                if (pass) word[j] &= prog.maskRev[j];
+                word[j] = inword_transform_rev(word[j]);
+            }
+#pragma unroll
+            for (int d = 1; d < W; d <<= 1)
+#pragma unroll
+                for (int j = 0; j < W; ++j)
+                    if (!(j & d)) word[j] ^= word[j + d];
+        }
+#pragma unroll
+        for (int j = 0; j < W; ++j) word[j] = __byte_perm(word[j], 0u, 0x0123u);
+        uint32_t* gcode = reinterpret_cast<uint32_t*>(p.code + frame * p.nb);
+        if constexpr (W >= 8) {
+#pragma unroll
+            for (int j = 0; j < W; j += 8) stg256(gcode + j, word + j);
+        } else if constexpr (W == 4) {
+            *reinterpret_cast<uint4*>(gcode) = make_uint4(word[0], word[1], word[2], word[3]);
+        } else if constexpr (W == 2) {
+            *reinterpret_cast<uint2*>(gcode) = make_uint2(word[0], word[1]);
+        } else {
+            gcode[0] = word[0];
+        }
+    }
+}
+
+template <int W>
+inline int launch_encode_reg(const EncodeParams& p, const EncodeProgram& prog, int numSMs, cudaStream_t st)
+{
+    const int kbw = p.kb >> 2;
+    const size_t smem = (size_t)ENC_REG_THREADS * (kbw + 2) * 4;
+    const long long nBlocks = (p.nFrames + ENC_REG_THREADS - 1) / ENC_REG_THREADS;
+    const int grid = (int)std::min<long long>(nBlocks, (long long)numSMs * 16);
+    encode_reg_kernel<W><<<grid, ENC_REG_THREADS, smem, st>>>(p, prog);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
 template <int W>
 inline int launch_encode_thread(const EncodeParams& p, int numSMs, cudaStream_t st)
 {
@@ -231,11 +356,26 @@ inline int launch_encode_thread(const EncodeParams& p, int numSMs, cudaStream_t 
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
-inline int launch_encode(const EncodeParams& p, int numSMs, cudaStream_t st)
+inline int launch_encode(const EncodeParams& p0, const EncodeProgram* prog, int numSMs, cudaStream_t st)
 {
+    EncodeParams p = p0;
     const int W = p.N >= 32 ? p.N >> 5 : 1;
-    // one frame per thread whenever the codeword fits the registers and the info block is whole words
-    if (p.N >= 32 && p.N <= 1024 && (p.kb & 3) == 0 && p.kb >= 4) {
+    // second-generation kernel: needs the scatter program and codeword rows aligned for its widest store
+    if (prog && p.N >= 32 && p.N <= 1024 && (p.kb & 3) == 0 && p.kb >= 4 && ((uintptr_t)p.code & (size_t)(std::min(p.nb, 32) - 1)) == 0 &&
+        ((uintptr_t)p.info & 3u) == 0) {
+        p.vecIn = ((p.kb & 15) == 0 && ((uintptr_t)p.info & 15u) == 0) ? 1 : 0;
+        switch (W) {
+        case 1: return launch_encode_reg<1>(p, *prog, numSMs, st);
+        case 2: return launch_encode_reg<2>(p, *prog, numSMs, st);
+        case 4: return launch_encode_reg<4>(p, *prog, numSMs, st);
+        case 8: return launch_encode_reg<8>(p, *prog, numSMs, st);
+        case 16: return launch_encode_reg<16>(p, *prog, numSMs, st);
+        case 32: return launch_encode_reg<32>(p, *prog, numSMs, st);
+        }
+    }
+    // one frame per thread whenever the codeword fits the registers and the info block is whole (aligned) words
+    p.byteOut = ((uintptr_t)p.code & 3u) ? 1 : 0;
+    if (p.N >= 32 && p.N <= 1024 && (p.kb & 3) == 0 && p.kb >= 4 && (((uintptr_t)p.info | (uintptr_t)p.code) & 3u) == 0) {
         switch (W) {
         case 1: return launch_encode_thread<1>(p, numSMs, st);
         case 2: return launch_encode_thread<2>(p, numSMs, st);

@@ -130,6 +130,7 @@ struct polar_code {
     size_t smemPerBlock = 0;
     uint32_t* dRuns = nullptr;     // Fast-SSC: runs of consecutive information positions
     int nRuns = 0;
+    polar::EncodeProgram* encProg = nullptr; // encoder, 32 <= N <= 1024: the scatter program of encode_reg_kernel (kernel parameter)
     uint32_t* dSpill = nullptr;    // list decoders: L2-resident scratch for the top LLR stage
     int8_t* dQuant = nullptr;      // int8 copy of fp32 LLRs (quantiser pre-pass)
     size_t quantBytes = 0;
@@ -431,6 +432,7 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaFree(c->dFailIdx); cudaFree(c->dFailCount); cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
     if (c->hFailCount) cudaFreeHost(c->hFailCount);
     if (c->scratchFree) cudaEventDestroy(c->scratchFree);
+    delete c->encProg;
     polar_cuda_code_destroy(c->fast);
     polar_cuda_code_destroy(c->list);
     for (int i = 0; i < 2; ++i) {
@@ -574,6 +576,26 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
                 }
             }
             tab[nWords] = (uint32_t)runs.size();
+            if (N >= 32 && N <= 1024 && (int)runs.size() <= ENC_MAX_RUNS && !env_int("POLAR_CUDA_ENC_V1", 0)) {
+                // the same runs for the bit-reversed words of encode_reg_kernel: source row, funnel shift, destination mask
+                EncodeProgram* g = new EncodeProgram();
+                memset(g, 0, sizeof(*g));
+                for (int w = 0; w < nWords; ++w) {
+                    g->first[w] = (uint16_t)tab[w];
+                    uint32_t rev = 0;
+                    for (int i = 0; i < 32; ++i) rev |= ((wordTab[w].x >> i) & 1u) << (31 - i);
+                    g->maskRev[w] = rev;
+                }
+                for (int w = nWords; w < 34; ++w) g->first[w] = (uint16_t)runs.size();
+                for (size_t r = 0; r < runs.size(); ++r) {
+                    const int b = runs[r] & 31u, len = (runs[r] >> 5) & 63u, k = runs[r] >> 11, s = k & 31, wi = k >> 5;
+                    const uint32_t hiRow = s >= b ? wi + 1 : wi, sh = s >= b ? s - b : 32 - (b - s);
+                    g->run[r].x = hiRow * (uint32_t)(ENC_REG_THREADS * 4);
+                    g->run[r].y = sh;
+                    g->run[r].z = (len == 32 ? 0xFFFFFFFFu : ((1u << len) - 1u)) << (32 - b - len);
+                }
+                c->encProg = g;
+            }
             tab.insert(tab.end(), runs.begin(), runs.end());
             c->nRuns = nWords + 1; // offset of the run entries inside the table
             if ((e = cudaMalloc(&c->dRuns, tab.size() * sizeof(uint32_t))) != cudaSuccess ||
@@ -1035,7 +1057,7 @@ int polar_cuda_encode_batch(polar_code_t c, uint8_t* info, int mem, size_t nFram
     } else {
         p.info = info; p.code = code_out;
     }
-    int rc = launch_encode(p, c->numSMs, st);
+    int rc = launch_encode(p, c->encProg, c->numSMs, st);
     c->launches++;
     if (rc) return fail(POLAR_E_CUDA, std::string("encode launch: ") + cudaGetErrorString(cudaGetLastError()));
     if (mem == POLAR_MEM_HOST) {

@@ -73,13 +73,14 @@ def test_round_logic_world2_gloo(tmp_path):
         "r, w = dist.get_rank(), dist.get_world_size()\n"
         "sim = Fake()\n"
         "tot, rounds, sub = simulate_point(sim, 2.0, 1, 0, r, w, 'cpu', 100, 10**6, 128)\n"
-        "print(json.dumps({'rank': r, 'tot': tot, 'ranges': sim.ranges, 'rounds': len(rounds)}))\n"
-        "dist.destroy_process_group()\n" % ROOT)
+        "open(os.path.join(%r, 'rank%%d.json' %% r), 'w').write(json.dumps({'rank': r, 'tot': tot, 'ranges': sim.ranges, 'rounds': len(rounds)}))\n"
+        "dist.destroy_process_group()\n" % (ROOT, str(tmp_path)))
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", "29741", str(script)],
                          capture_output=True, text=True, timeout=240)
     assert out.returncode == 0, out.stderr[-2000:]
-    recs = sorted((json.loads(l) for l in out.stdout.splitlines() if l.startswith("{")), key=lambda d: d["rank"])
+    recs = [json.loads((tmp_path / ("rank%d.json" % r)).read_text()) for r in range(2)]   # one file per rank: two ranks printing
+    # to one pipe can interleave their lines
     assert len(recs) == 2 and recs[0]["tot"] == recs[1]["tot"] and recs[0]["rounds"] == recs[1]["rounds"]
     nr = recs[0]["rounds"]
     frames = nr * 2 * 128

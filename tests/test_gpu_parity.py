@@ -202,6 +202,33 @@ def test_encoder_parity(gpu, N, K, ctype, sysm, crc):
         assert np.array_equal(code, rcode) and np.array_equal(mine, rinfo)
 
 
+@pytest.mark.parametrize("N,K,ctype", [(256, 128, "BB"), (1024, 512, "5G"), (1024, 992, "BB"), (512, 96, "BE"), (64, 32, "BB"), (1024, 44 * 8, "5G")])
+@pytest.mark.parametrize("crc", [0, 16])
+def test_encoder_device_buffers_aligned_and_not(gpu, N, K, ctype, crc):
+    """DEVICE buffers: the one-frame-per-thread kernel with 128/256-bit accesses when the rows are aligned, the staged kernel when the
+    caller's pointers are not (an offset view of a larger allocation); several thousand frames so that the grid-stride loop
+    wraps.  Both against the oracle."""
+    import torch
+    frozen = ap.frozen_bits(N, K, 0.0, ctype)
+    kb, nb, n = K // 8, N // 8, 40000 + 77
+    rng = np.random.default_rng(N * 3 + K + crc)
+    info = rng.integers(0, 256, (n, kb), dtype=np.uint8)
+    ecode, einfo = oracle_encode(N, frozen, info, 1, crc)
+    enc = ap.PolarEncoder(N, frozen)
+    enc.setErrorDetection(crc)
+    for off_in, off_out in ((0, 0), (4, 0), (0, 4), (1, 3)):
+        raw_in = torch.zeros(n * kb + 64, dtype=torch.uint8, device="cuda")
+        raw_out = torch.zeros(n * nb + 64, dtype=torch.uint8, device="cuda")
+        d_info = raw_in[off_in:off_in + n * kb].view(n, kb)
+        d_info.copy_(torch.from_numpy(info))
+        d_code = raw_out[off_out:off_out + n * nb].view(n, nb)
+        enc.encode_batch(d_info, out=d_code)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_code.cpu().numpy(), ecode), (off_in, off_out)
+        assert np.array_equal(d_info.cpu().numpy(), einfo), (off_in, off_out)
+        assert int(raw_out[:off_out].sum()) == 0 and int(raw_out[off_out + n * nb:].sum()) == 0   # nothing outside the rows
+
+
 def test_primitives_exhaustive(gpu):
     """F and G over all 256 x 256 int8 pairs, both bit values (superset of decodingtest.cpp:504-737)."""
     from polar_testlib import oracle
