@@ -18,6 +18,7 @@ struct EncodeParams {
     uint8_t* code;          // nFrames x nb
     const uint2* wordTab;   // per code word: x = mask of info positions, y = number of info bits before it
     const uint32_t* genTab; // per info bit: CRC contribution
+    const uint32_t* genNib; // encode_reg_kernel: per info nibble (4 stream bits, MSB first) and value: 16 contributions
     const uint32_t* runTab; // [0..W]: first run of each code word; then the runs: b | len << 5 | first info bit << 11
     int runBase;            // offset of the run entries inside runTab
     uint32_t genInit;
@@ -254,78 +255,116 @@ POLAR_DEV void stg256(uint32_t* dst, const uint32_t* v)
 }
 
 static constexpr int ENC_REG_THREADS = 128;
+#ifndef POLAR_ENC_FPT
+#define POLAR_ENC_FPT 2
+#endif
+static constexpr int ENC_FPT = POLAR_ENC_FPT; // frames per thread: the run entry, its address arithmetic and the loop control serve both
+static constexpr int ENC_ROW_WORDS = ENC_REG_THREADS * ENC_FPT; // words between two rows of a thread
 template <int W>
 __global__ void __launch_bounds__(ENC_REG_THREADS) encode_reg_kernel(const __grid_constant__ EncodeParams p, const __grid_constant__ EncodeProgram prog)
 {
-    extern __shared__ __align__(16) uint32_t esm[]; // row r of thread t at esm[r * 128 + t]: conflict free for any uniform r
+    extern __shared__ __align__(16) uint32_t esm[]; // row r of frame f of thread t at esm[(r * FPT + f) * 128 + t]: no conflicts
     const int tid = threadIdx.x, kbw = p.kb >> 2;
     uint32_t* mine = esm + tid;
-    mine[0] = 0u;
-    mine[(kbw + 1) * ENC_REG_THREADS] = 0u;
-    const long long stride = (long long)gridDim.x * ENC_REG_THREADS;
-    for (long long frame = (long long)blockIdx.x * ENC_REG_THREADS + tid; frame < p.nFrames; frame += stride) {
-        uint32_t* ginfo = reinterpret_cast<uint32_t*>(p.info + frame * p.kb);
-        if (p.vecIn) {
-            for (int i = 0; i < kbw; i += 4) {
-                const uint4 q = *reinterpret_cast<const uint4*>(ginfo + i);
-                mine[(i + 1) * ENC_REG_THREADS] = __byte_perm(q.x, 0u, 0x0123u);
-                mine[(i + 2) * ENC_REG_THREADS] = __byte_perm(q.y, 0u, 0x0123u);
-                mine[(i + 3) * ENC_REG_THREADS] = __byte_perm(q.z, 0u, 0x0123u);
-                mine[(i + 4) * ENC_REG_THREADS] = __byte_perm(q.w, 0u, 0x0123u);
+#pragma unroll
+    for (int f = 0; f < ENC_FPT; ++f) {
+        mine[f * ENC_REG_THREADS] = 0u;
+        mine[(kbw + 1) * ENC_ROW_WORDS + f * ENC_REG_THREADS] = 0u;
+    }
+    // CRC generate as a table walk: the checksum is linear in the info bits (crc_host.h), so it is the XOR of one entry per
+    // info nibble.  16 consecutive words per nibble: the 32 lanes of a load hit at most 16 different banks, equal values
+    // broadcast -- no conflicts.  kb * 128 bytes of shared memory, copied once per block.
+    const uint32_t* nibTab = esm + (kbw + 2) * ENC_ROW_WORDS;
+    if (p.crcBits) {
+        uint32_t* t = esm + (kbw + 2) * ENC_ROW_WORDS;
+        for (int i = tid; i < kbw * 128; i += ENC_REG_THREADS) t[i] = __ldg(p.genNib + i);
+        __syncthreads();
+    }
+    const long long stride = (long long)gridDim.x * ENC_ROW_WORDS;
+    for (long long frame0 = (long long)blockIdx.x * ENC_ROW_WORDS + tid; frame0 < p.nFrames; frame0 += stride) {
+        bool live[ENC_FPT];
+#pragma unroll
+        for (int f = 0; f < ENC_FPT; ++f) {
+            const long long frame = frame0 + f * ENC_REG_THREADS;
+            live[f] = frame < p.nFrames;
+            if (!live[f]) continue;
+            uint32_t* row = mine + f * ENC_REG_THREADS;
+            uint32_t* ginfo = reinterpret_cast<uint32_t*>(p.info + frame * p.kb);
+            if (p.vecIn) {
+                for (int i = 0; i < kbw; i += 4) {
+                    const uint4 q = *reinterpret_cast<const uint4*>(ginfo + i);
+                    row[(i + 1) * ENC_ROW_WORDS] = __byte_perm(q.x, 0u, 0x0123u);
+                    row[(i + 2) * ENC_ROW_WORDS] = __byte_perm(q.y, 0u, 0x0123u);
+                    row[(i + 3) * ENC_ROW_WORDS] = __byte_perm(q.z, 0u, 0x0123u);
+                    row[(i + 4) * ENC_ROW_WORDS] = __byte_perm(q.w, 0u, 0x0123u);
+                }
+            } else {
+                for (int i = 0; i < kbw; ++i) row[(i + 1) * ENC_ROW_WORDS] = __byte_perm(ginfo[i], 0u, 0x0123u);
             }
-        } else {
-            for (int i = 0; i < kbw; ++i) mine[(i + 1) * ENC_REG_THREADS] = __byte_perm(ginfo[i], 0u, 0x0123u);
-        }
-        if (p.crcBits) { // Detector::generate: the checksum is linear in the info bits (crc_host.h); trailer bits weigh 0
-            uint32_t crc = p.genInit;
-            for (int i = 0; i < kbw; ++i) {
-                const uint32_t w = mine[(i + 1) * ENC_REG_THREADS];
-#pragma unroll 8
-                for (int b = 0; b < 32; ++b) crc ^= __ldg(p.genTab + 32 * i + b) & (0u - ((w >> (31 - b)) & 1u));
+            if (p.crcBits) { // Detector::generate: the checksum is linear in the info bits (crc_host.h); trailer bits weigh 0
+                uint32_t crc = p.genInit;
+                for (int i = 0; i < kbw; ++i) {
+                    const uint32_t w = row[(i + 1) * ENC_ROW_WORDS];
+                    const char* t = reinterpret_cast<const char*>(nibTab + i * 128);
+#pragma unroll
+                    for (int n = 0; n < 8; ++n) { // nibble n = stream bits 4n .. 4n+3 of the word = bits 31-4n .. 28-4n
+                        const uint32_t off = n == 7 ? (w << 2) & 0x3Cu : (w >> (26 - 4 * n)) & 0x3Cu;
+                        crc ^= *reinterpret_cast<const uint32_t*>(t + n * 64 + off);
+                    }
+                }
+                uint32_t last = row[kbw * ENC_ROW_WORDS];
+                if (p.crcBits == 8) last = (last & ~0xFFu) | (crc & 0xFFu);
+                else if (p.crcBits == 16) last = (last & ~0xFFFFu) | (crc & 0xFFFFu);   // big-endian trailer: crc16.cpp:35-43
+                else last = __byte_perm(crc, 0u, 0x0123u);                             // native little-endian u32: crc32.cpp:55-66
+                row[kbw * ENC_ROW_WORDS] = last;
+                ginfo[kbw - 1] = __byte_perm(last, 0u, 0x0123u);
             }
-            uint32_t last = mine[kbw * ENC_REG_THREADS];
-            if (p.crcBits == 8) last = (last & ~0xFFu) | (crc & 0xFFu);
-            else if (p.crcBits == 16) last = (last & ~0xFFFFu) | (crc & 0xFFFFu);   // big-endian trailer: crc16.cpp:35-43
-            else last = __byte_perm(crc, 0u, 0x0123u);                             // native little-endian u32: crc32.cpp:55-66
-            mine[kbw * ENC_REG_THREADS] = last;
-            ginfo[kbw - 1] = __byte_perm(last, 0u, 0x0123u);
         }
-        uint32_t word[W];
+        uint32_t word[ENC_FPT][W];
 #pragma unroll
         for (int j = 0; j < W; ++j) {
-            uint32_t v = 0;
+            uint32_t v[ENC_FPT];
+#pragma unroll
+            for (int f = 0; f < ENC_FPT; ++f) v[f] = 0u;
             const int r1 = prog.first[j + 1];
             for (int r = prog.first[j]; r < r1; ++r) { // uniform: every thread of the grid walks the same runs
                 const uint4 e = prog.run[r];
                 const uint32_t* hi = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(mine) + e.x);
-                v |= __funnelshift_l(hi[ENC_REG_THREADS], hi[0], e.y) & e.z;
-            }
-            word[j] = v;
-        }
-        for (int pass = 0; pass < (p.systematic ? 2 : 1); ++pass) {
 #pragma unroll
-            for (int j = 0; j < W; ++j) {
-                if (pass) word[j] &= prog.maskRev[j];
-                word[j] = inword_transform_rev(word[j]);
+                for (int f = 0; f < ENC_FPT; ++f)
+                    v[f] |= __funnelshift_l(hi[ENC_ROW_WORDS + f * ENC_REG_THREADS], hi[f * ENC_REG_THREADS], e.y) & e.z;
             }
 #pragma unroll
-            for (int d = 1; d < W; d <<= 1)
-#pragma unroll
-                for (int j = 0; j < W; ++j)
-                    if (!(j & d)) word[j] ^= word[j + d];
+            for (int f = 0; f < ENC_FPT; ++f) word[f][j] = v[f];
         }
 #pragma unroll
-        for (int j = 0; j < W; ++j) word[j] = __byte_perm(word[j], 0u, 0x0123u);
-        uint32_t* gcode = reinterpret_cast<uint32_t*>(p.code + frame * p.nb);
-        if constexpr (W >= 8) {
+        for (int f = 0; f < ENC_FPT; ++f) {
+            for (int pass = 0; pass < (p.systematic ? 2 : 1); ++pass) {
 #pragma unroll
-            for (int j = 0; j < W; j += 8) stg256(gcode + j, word + j);
-        } else if constexpr (W == 4) {
-            *reinterpret_cast<uint4*>(gcode) = make_uint4(word[0], word[1], word[2], word[3]);
-        } else if constexpr (W == 2) {
-            *reinterpret_cast<uint2*>(gcode) = make_uint2(word[0], word[1]);
-        } else {
-            gcode[0] = word[0];
+                for (int j = 0; j < W; ++j) {
+                    if (pass) word[f][j] &= prog.maskRev[j];
+                    word[f][j] = inword_transform_rev(word[f][j]);
+                }
+#pragma unroll
+                for (int d = 1; d < W; d <<= 1)
+#pragma unroll
+                    for (int j = 0; j < W; ++j)
+                        if (!(j & d)) word[f][j] ^= word[f][j + d];
+            }
+            if (!live[f]) continue;
+#pragma unroll
+            for (int j = 0; j < W; ++j) word[f][j] = __byte_perm(word[f][j], 0u, 0x0123u);
+            uint32_t* gcode = reinterpret_cast<uint32_t*>(p.code + (frame0 + f * ENC_REG_THREADS) * p.nb);
+            if constexpr (W >= 8) {
+#pragma unroll
+                for (int j = 0; j < W; j += 8) stg256(gcode + j, word[f] + j);
+            } else if constexpr (W == 4) {
+                *reinterpret_cast<uint4*>(gcode) = make_uint4(word[f][0], word[f][1], word[f][2], word[f][3]);
+            } else if constexpr (W == 2) {
+                *reinterpret_cast<uint2*>(gcode) = make_uint2(word[f][0], word[f][1]);
+            } else {
+                gcode[0] = word[f][0];
+            }
         }
     }
 }
@@ -334,8 +373,11 @@ template <int W>
 inline int launch_encode_reg(const EncodeParams& p, const EncodeProgram& prog, int numSMs, cudaStream_t st)
 {
     const int kbw = p.kb >> 2;
-    const size_t smem = (size_t)ENC_REG_THREADS * (kbw + 2) * 4;
-    const long long nBlocks = (p.nFrames + ENC_REG_THREADS - 1) / ENC_REG_THREADS;
+    const size_t smem = (size_t)ENC_ROW_WORDS * (kbw + 2) * 4 + (p.crcBits ? (size_t)kbw * 512 : 0);
+    if (smem > 48 * 1024 &&
+        cudaFuncSetAttribute((const void*)encode_reg_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return -1;
+    const long long nBlocks = (p.nFrames + ENC_ROW_WORDS - 1) / ENC_ROW_WORDS;
     const int grid = (int)std::min<long long>(nBlocks, (long long)numSMs * 16);
     encode_reg_kernel<W><<<grid, ENC_REG_THREADS, smem, st>>>(p, prog);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;

@@ -321,6 +321,10 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_f32_kernel(const 
         const bool live = g0 + warp < nGroups; // a spare warp redoes the last group and drops it
         const long long grp = live ? g0 + warp : nGroups - 1;
         c.frame0 = grp << 5;
+        if (p.prefetchNext && g0 + totalWarps + warp < nGroups) { // the next group of this warp: its channel rows into L2
+            const long long nf0 = (g0 + totalWarps + warp) << 5;
+            warp_prefetch_l2(static_cast<const float*>(p.llr) + nf0 * p.N, min(32LL, p.nFrames - nf0) * p.N * 4, lane);
+        }
         if (c.chanRow >= 0) { // one-leaf codes: stage the channel rows (transposed) once
             for (int w0 = 0; w0 < c.nw; w0 += 32) {
                 const int n = min(32, c.nw - w0);

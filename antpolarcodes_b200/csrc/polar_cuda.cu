@@ -122,6 +122,7 @@ struct polar_code {
     uint2* dWordTab = nullptr;     // per code word: info-position mask, info bits before it (encoder)
     uint32_t* dSynTab = nullptr;   // K
     uint32_t* dGenTab = nullptr;   // K
+    uint32_t* dGenNib = nullptr;   // encoder with a CRC, kb % 4 == 0: kb * 2 nibbles x 16 values (encode_reg_kernel)
     uint32_t synInit = 0, genInit = 0;
     // launch geometry
     DecodeKernel kernel = nullptr;
@@ -189,6 +190,7 @@ int setup_decoder_geometry(polar_code* c)
     // SCL fp32 1 -> 8: 4.11 -> 4.19; without any barrier the kernels stall on instruction fetch)
     g.lockstep = env_int("POLAR_CUDA_LOCKSTEP", c->kind == POLAR_KIND_FASTSSC_I8 ? 128 : c->kind == POLAR_KIND_SCL_F32 ? 8 : 64);
     if (g.lockstep & (g.lockstep - 1)) g.lockstep = 1; // the kernels test pc & (lockstep - 1)
+    g.prefetchNext = env_int("POLAR_CUDA_PREFETCH", 0);
     g.rootLeaf = 0;
     g.llrBase = 0; g.bitBase = 0; g.bitSpill = c->lgN + 1; g.spA = g.spB0 = g.spB1 = 0;
     g.regStages = c->kind == POLAR_KIND_SCL_I8 ? std::min(env_int("POLAR_CUDA_REG_STAGES", 4), c->lgN - 2) : -1;
@@ -426,7 +428,7 @@ int polar_cuda_code_destroy(polar_code_t c)
 {
     if (!c) return POLAR_OK;
     cudaSetDevice(c->device);
-    cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab);
+    cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab); cudaFree(c->dGenNib);
     cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
     cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns); cudaFree(c->dSoftScratch);
     cudaFree(c->dFailIdx); cudaFree(c->dFailCount); cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
@@ -558,6 +560,22 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
                 break;
             }
         }
+        if (kind == POLAR_KIND_ENC && crcBits && (c->kb & 3) == 0) {
+            // checksum contribution of every value of every info nibble (stream bits 4n .. 4n+3, first bit = value bit 3)
+            std::vector<uint32_t> nib((size_t)c->kb * 2 * 16, 0u);
+            for (int n = 0; n < c->kb * 2; ++n)
+                for (int v = 1; v < 16; ++v) {
+                    uint32_t x = 0;
+                    for (int b = 0; b < 4; ++b)
+                        if (((v >> (3 - b)) & 1) && 4 * n + b < K) x ^= t.gen[4 * n + b];
+                    nib[(size_t)n * 16 + v] = x;
+                }
+            if ((e = cudaMalloc(&c->dGenNib, nib.size() * sizeof(uint32_t))) != cudaSuccess ||
+                (e = cudaMemcpy(c->dGenNib, nib.data(), nib.size() * sizeof(uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
+                rc = fail(POLAR_E_CUDA, std::string("CRC nibble table upload: ") + cudaGetErrorString(e));
+                break;
+            }
+        }
         if (kind == POLAR_KIND_ENC) {
             // encoder: per code word the runs of consecutive information positions (b | len << 5 | first info bit << 11)
             // behind a table of run offsets per word
@@ -590,7 +608,7 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
                 for (size_t r = 0; r < runs.size(); ++r) {
                     const int b = runs[r] & 31u, len = (runs[r] >> 5) & 63u, k = runs[r] >> 11, s = k & 31, wi = k >> 5;
                     const uint32_t hiRow = s >= b ? wi + 1 : wi, sh = s >= b ? s - b : 32 - (b - s);
-                    g->run[r].x = hiRow * (uint32_t)(ENC_REG_THREADS * 4);
+                    g->run[r].x = hiRow * (uint32_t)(ENC_ROW_WORDS * 4);
                     g->run[r].y = sh;
                     g->run[r].z = (len == 32 ? 0xFFFFFFFFu : ((1u << len) - 1u)) << (32 - b - len);
                 }
@@ -1046,7 +1064,7 @@ int polar_cuda_encode_batch(polar_code_t c, uint8_t* info, int mem, size_t nFram
     EncodeParams p{};
     p.N = c->N; p.lgN = c->lgN; p.K = c->K; p.kb = c->kb; p.nb = std::max(1, c->N / 8);
     p.crcBits = c->crcBits; p.systematic = c->systematic;
-    p.wordTab = c->dWordTab; p.genTab = c->dGenTab; p.genInit = c->genInit;
+    p.wordTab = c->dWordTab; p.genTab = c->dGenTab; p.genNib = c->dGenNib; p.genInit = c->genInit;
     p.runTab = c->dRuns; p.runBase = c->nRuns;
     p.nFrames = (long long)nFrames;
     if (mem == POLAR_MEM_HOST) {

@@ -108,6 +108,15 @@ POLAR_DEV void cp_async4(uint32_t* smemDst, const uint32_t* globalSrc)
 }
 POLAR_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// ---- L2 prefetch of a contiguous byte range by one warp (the next frame group's channel rows: the top-level steps of the
+// group then find them in L2 instead of waiting for HBM)
+POLAR_DEV void warp_prefetch_l2(const void* base, long long bytes, int lane)
+{
+    const char* p = reinterpret_cast<const char*>(reinterpret_cast<uintptr_t>(base) & ~(uintptr_t)127);
+    const long long span = bytes + (long long)(reinterpret_cast<uintptr_t>(base) & 127u);
+    for (long long off = (long long)lane * 128; off < span; off += 32 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + off));
+}
+
 // ---- TMA bulk copies (cp.async.bulk, SASS UBLKCP) completing on a shared-memory mbarrier
 POLAR_DEV void mbar_init(uint64_t* bar, int count)
 {

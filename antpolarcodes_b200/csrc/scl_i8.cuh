@@ -142,6 +142,12 @@ template <int L>
 POLAR_DEV uint32_t list_max(uint32_t v)
 {
     if (L == 32) return __reduce_max_sync(FULL_MASK, v);
+#ifdef POLAR_SCL_REDUX_GROUPS // one REDUX per list group instead of log2(L) shuffle + max pairs (A/B: profiles/r2_experiments.txt)
+    if (L >= POLAR_SCL_REDUX_GROUPS) {
+        const uint32_t lane = threadIdx.x & 31u;
+        return __reduce_max_sync((L == 32 ? 0xFFFFFFFFu : ((1u << L) - 1u)) << (lane & ~(uint32_t)(L - 1)), v);
+    }
+#endif
 #pragma unroll
     for (int d = 1; d < L; d <<= 1) v = max(v, __shfl_xor_sync(FULL_MASK, v, d));
     return v;

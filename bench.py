@@ -46,6 +46,8 @@ WORKLOADS = {
                      label="SCL fp32 L=8 + CRC16, N=1024 K=512, 5G frozen set, Eb/N0=2dB"),
     "encode": dict(N=256, K=128, ctype="BB", L=1, crc=0, frames=1 << 22, e2e_frames=1 << 21, encoder=True, parity=1 << 18, cpu_s=3.0,
                    label="packed butterfly encoder, systematic, N=256 K=128, BB frozen set"),
+    "encode_n1024": dict(N=1024, K=512, ctype="5G", L=1, crc=16, frames=1 << 21, e2e_frames=1 << 20, encoder=True, parity=1 << 17, cpu_s=3.0,
+                         label="packed butterfly encoder + CRC16 generate, systematic, N=1024 K=512, 5G frozen set"),
     "adaptive8": dict(N=1024, K=512, ctype="5G", L=8, crc=16, frames=1 << 20, e2e_frames=1 << 19, adaptive=True, parity=1 << 16, cpu_s=4.0,
                       label="AdaptiveChar (Fast-SSC int8, SCL L=8 on CRC16 failures), N=1024 K=512, 5G frozen set, Eb/N0=2dB"),
     "scl32": dict(N=2048, K=1024, ctype="BB", L=32, crc=32, frames=1 << 16, e2e_frames=1 << 16, parity=1 << 13, cpu_s=4.0,
