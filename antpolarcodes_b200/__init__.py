@@ -166,7 +166,11 @@ class _Code:
             lib().polar_cuda_code_destroy(self._h)
             self._h = _c.c_void_p()
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:   # interpreter shutdown: the module globals may already be gone, the process frees the device memory
+            pass
 
     def info(self):
         ci = CodeInfo()
@@ -440,7 +444,11 @@ class Puncturer:
             lib().polar_cuda_puncturer_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:   # interpreter shutdown: the module globals may already be gone
+            pass
 
     def blockLength(self):
         return self._M
@@ -539,7 +547,11 @@ class LinkSimulator:
             lib().polar_cuda_sim_destroy(self._h)
             self._h = _c.c_void_p()
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:   # interpreter shutdown: the module globals may already be gone
+            pass
 
     def default_amplification(self, ebn0_db):
         """pcsim's defaults: 10 ahead of the 8-bit quantiser (setup.cpp:58), 4 * 10^(Eb/N0 / 10) for float (simulator.cpp:377)"""

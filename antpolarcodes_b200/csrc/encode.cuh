@@ -10,6 +10,7 @@
 #pragma once
 #include "primitives.cuh"
 #include <algorithm>
+#include <cstring>
 
 namespace polar {
 
@@ -232,11 +233,14 @@ __global__ void __launch_bounds__(128) encode_thread_kernel(const __grid_constan
 //   * a thread loads its own info row (128- or 256-bit loads, rows of one warp are contiguous) and stores its own codeword
 //     (STG.256 where the codeword has eight words or more): no block-wide synchronisation at all.
 static constexpr int ENC_MAX_RUNS = 512; // 16 runs per word x 32 words: every frozen set of N <= 1024 fits
-struct EncodeProgram {
+static constexpr int ENC_FEW_RUNS = 96;  // the usual case (N=1024 K=512: 55 - 63 runs): a 1.7 KB kernel parameter instead of 8.4 KB
+template <int CAP>                       // (parameters above 4 KB take a slower launch path: +6 us per launch measured)
+struct EncodeProgramT {
     uint32_t maskRev[32];             // info positions of code word j, bit-reversed
     uint16_t first[34];               // runs of word j: first[j] .. first[j+1]-1
-    uint4 run[ENC_MAX_RUNS];          // x = byte offset of the row of the HIGH source word (row = info word index + 1; row 0 and
+    uint4 run[CAP];                   // x = byte offset of the row of the HIGH source word (row = info word index + 1; row 0 and
 };                                    // row kbw+1 are zero pads), y = funnel shift, z = mask of the destination field (reversed)
+using EncodeProgram = EncodeProgramT<ENC_MAX_RUNS>;
 
 POLAR_DEV uint32_t inword_transform_rev(uint32_t v)
 {
@@ -255,14 +259,12 @@ POLAR_DEV void stg256(uint32_t* dst, const uint32_t* v)
 }
 
 static constexpr int ENC_REG_THREADS = 128;
-#ifndef POLAR_ENC_FPT
-#define POLAR_ENC_FPT 2
-#endif
-static constexpr int ENC_FPT = POLAR_ENC_FPT; // frames per thread: the run entry, its address arithmetic and the loop control serve both
-static constexpr int ENC_ROW_WORDS = ENC_REG_THREADS * ENC_FPT; // words between two rows of a thread
-template <int W>
-__global__ void __launch_bounds__(ENC_REG_THREADS) encode_reg_kernel(const __grid_constant__ EncodeParams p, const __grid_constant__ EncodeProgram prog)
+// ENC_FPT frames per thread: the run entry, its address arithmetic and the loop control serve all of them (measured: 2 frames
+// 5775, 3 -> 5501, 4 -> 5629 Gbit/s at N=256); batches too small to fill the GPU with two frames per thread take one
+template <int W, int ENC_FPT, int CAP>
+__global__ void __launch_bounds__(ENC_REG_THREADS) encode_reg_kernel(const __grid_constant__ EncodeParams p, const __grid_constant__ EncodeProgramT<CAP> prog)
 {
+    constexpr int ENC_ROW_WORDS = ENC_REG_THREADS * ENC_FPT; // words between two rows of a thread
     extern __shared__ __align__(16) uint32_t esm[]; // row r of frame f of thread t at esm[(r * FPT + f) * 128 + t]: no conflicts
     const int tid = threadIdx.x, kbw = p.kb >> 2;
     uint32_t* mine = esm + tid;
@@ -369,18 +371,40 @@ __global__ void __launch_bounds__(ENC_REG_THREADS) encode_reg_kernel(const __gri
     }
 }
 
-template <int W>
-inline int launch_encode_reg(const EncodeParams& p, const EncodeProgram& prog, int numSMs, cudaStream_t st)
+template <int W, int FPT, int CAP>
+inline int launch_encode_reg_cap(const EncodeParams& p, const EncodeProgramT<CAP>& prog, int numSMs, cudaStream_t st)
 {
+    constexpr int rowWords = ENC_REG_THREADS * FPT;
     const int kbw = p.kb >> 2;
-    const size_t smem = (size_t)ENC_ROW_WORDS * (kbw + 2) * 4 + (p.crcBits ? (size_t)kbw * 512 : 0);
+    const size_t smem = (size_t)rowWords * (kbw + 2) * 4 + (p.crcBits ? (size_t)kbw * 512 : 0);
     if (smem > 48 * 1024 &&
-        cudaFuncSetAttribute((const void*)encode_reg_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        cudaFuncSetAttribute((const void*)encode_reg_kernel<W, FPT, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return -1;
-    const long long nBlocks = (p.nFrames + ENC_ROW_WORDS - 1) / ENC_ROW_WORDS;
+    const long long nBlocks = (p.nFrames + rowWords - 1) / rowWords;
     const int grid = (int)std::min<long long>(nBlocks, (long long)numSMs * 16);
-    encode_reg_kernel<W><<<grid, ENC_REG_THREADS, smem, st>>>(p, prog);
+    encode_reg_kernel<W, FPT, CAP><<<grid, ENC_REG_THREADS, smem, st>>>(p, prog);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+template <int W, int FPT>
+inline int launch_encode_reg_fpt(const EncodeParams& p, const EncodeProgram& prog, int numSMs, cudaStream_t st)
+{
+    if (prog.first[33] <= ENC_FEW_RUNS) { // first[33] = number of runs
+        EncodeProgramT<ENC_FEW_RUNS> few;
+        memcpy(few.maskRev, prog.maskRev, sizeof(few.maskRev));
+        memcpy(few.first, prog.first, sizeof(few.first));
+        memcpy(few.run, prog.run, sizeof(few.run));
+        return launch_encode_reg_cap<W, FPT, ENC_FEW_RUNS>(p, few, numSMs, st);
+    }
+    return launch_encode_reg_cap<W, FPT, ENC_MAX_RUNS>(p, prog, numSMs, st);
+}
+
+// prog[0]: row offsets for one frame per thread, prog[1]: for two
+template <int W>
+inline int launch_encode_reg(const EncodeParams& p, const EncodeProgram* prog, int numSMs, cudaStream_t st)
+{
+    const bool two = p.nFrames >= (long long)numSMs * 8 * ENC_REG_THREADS * 2; // eight blocks per SM even at two frames per thread
+    return two ? launch_encode_reg_fpt<W, 2>(p, prog[1], numSMs, st) : launch_encode_reg_fpt<W, 1>(p, prog[0], numSMs, st);
 }
 
 template <int W>
@@ -398,7 +422,7 @@ inline int launch_encode_thread(const EncodeParams& p, int numSMs, cudaStream_t 
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
-inline int launch_encode(const EncodeParams& p0, const EncodeProgram* prog, int numSMs, cudaStream_t st)
+inline int launch_encode(const EncodeParams& p0, const EncodeProgram* prog /* [2] or null */, int numSMs, cudaStream_t st)
 {
     EncodeParams p = p0;
     const int W = p.N >= 32 ? p.N >> 5 : 1;
@@ -407,12 +431,12 @@ inline int launch_encode(const EncodeParams& p0, const EncodeProgram* prog, int 
         ((uintptr_t)p.info & 3u) == 0) {
         p.vecIn = ((p.kb & 15) == 0 && ((uintptr_t)p.info & 15u) == 0) ? 1 : 0;
         switch (W) {
-        case 1: return launch_encode_reg<1>(p, *prog, numSMs, st);
-        case 2: return launch_encode_reg<2>(p, *prog, numSMs, st);
-        case 4: return launch_encode_reg<4>(p, *prog, numSMs, st);
-        case 8: return launch_encode_reg<8>(p, *prog, numSMs, st);
-        case 16: return launch_encode_reg<16>(p, *prog, numSMs, st);
-        case 32: return launch_encode_reg<32>(p, *prog, numSMs, st);
+        case 1: return launch_encode_reg<1>(p, prog, numSMs, st);
+        case 2: return launch_encode_reg<2>(p, prog, numSMs, st);
+        case 4: return launch_encode_reg<4>(p, prog, numSMs, st);
+        case 8: return launch_encode_reg<8>(p, prog, numSMs, st);
+        case 16: return launch_encode_reg<16>(p, prog, numSMs, st);
+        case 32: return launch_encode_reg<32>(p, prog, numSMs, st);
         }
     }
     // one frame per thread whenever the codeword fits the registers and the info block is whole (aligned) words

@@ -4,6 +4,11 @@
 #include "decode_params.h"
 #include "schedule.h"
 
+// launch bound of the middle register budget of scl_i8_kernel (768 threads = 80 registers; A/B builds override it)
+#ifndef POLAR_SCL_MID_THREADS
+#define POLAR_SCL_MID_THREADS 768
+#endif
+
 namespace polar {
 
 typedef void (*DecodeKernel)(const DecodeParams, const Schedule);

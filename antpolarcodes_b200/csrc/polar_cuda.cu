@@ -17,6 +17,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <list>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -133,6 +134,8 @@ struct polar_code {
     int nRuns = 0;
     polar::EncodeProgram* encProg = nullptr; // encoder, 32 <= N <= 1024: the scatter program of encode_reg_kernel (kernel parameter)
     uint32_t* dSpill = nullptr;    // list decoders: L2-resident scratch for the top LLR stage
+    size_t spillBytes = 0, l2WindowBytes = 0;
+    float l2Persist = 0.f;         // > 0: the scratch is launched as a persisting L2 access-policy window with this hit ratio
     int8_t* dQuant = nullptr;      // int8 copy of fp32 LLRs (quantiser pre-pass)
     size_t quantBytes = 0;
     // staging buffers for HOST-memory calls
@@ -171,6 +174,33 @@ int env_int(const char* name, int dflt)
 {
     const char* v = getenv(name);
     return v && *v ? atoi(v) : dflt;
+}
+
+// The scratch of the spilled stages as a persisting L2 access-policy window (launch attribute of the decoder kernel): the
+// input that streams through the cache no longer evicts it.  Measured on B200 (profiles/r2_experiments.txt t12): Fast-SSC int8
+// N=1024 (57 MB of scratch) 181.6 -> 190.6 Gbit/s; the list decoders, whose scratch (124 - 250 MB) exceeds what the device can
+// set aside, lose 2 - 10 %.  So: on when the whole scratch fits the set-aside (POLAR_CUDA_L2_PERSIST unset or -1), 0 = never,
+// 1 = always (hit ratio = the share that fits).  The set-aside is per device and only ever grows to the largest scratch seen.
+void setup_l2_window(polar_code* c, const cudaDeviceProp& prop)
+{
+    static std::mutex mu;
+    static std::map<int, size_t> asideOf;
+    const int mode = env_int("POLAR_CUDA_L2_PERSIST", -1);
+    if (mode == 0 || !c->spillBytes || prop.persistingL2CacheMaxSize <= 0) return;
+    size_t cap = (size_t)prop.persistingL2CacheMaxSize;
+    if (const int mb = env_int("POLAR_CUDA_L2_PERSIST_MB", 0)) cap = std::min(cap, (size_t)mb << 20);
+    if (mode < 0 && c->spillBytes > cap) return;
+    const size_t want = std::min(cap, c->spillBytes);
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        size_t& cur = asideOf[c->device];
+        if (want > cur) {
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) != cudaSuccess) { cudaGetLastError(); return; }
+            cur = want;
+        }
+    }
+    c->l2WindowBytes = std::min(c->spillBytes, (size_t)prop.accessPolicyMaxWindowSize);
+    c->l2Persist = std::min(1.0f, (float)want / (float)c->l2WindowBytes);
 }
 
 int setup_decoder_geometry(polar_code* c)
@@ -331,9 +361,9 @@ int setup_decoder_geometry(polar_code* c)
         if (perWarp > (size_t)prop.sharedMemPerBlockOptin)
             return fail(POLAR_E_UNSUPPORTED, "code does not fit in shared memory (N x listSize too large)");
         int w = (int)std::min<size_t>(prop.sharedMemPerBlockOptin / perWarp, 32);
-        w = std::min(w, env_int("POLAR_CUDA_SCL_MAX_WARPS", 24)); // 64 registers spill: 24 warps at 80 registers is the widest useful block
+        w = std::min(w, env_int("POLAR_CUDA_SCL_MAX_WARPS", POLAR_SCL_MID_THREADS / 32)); // 64 registers spill: 24 warps at 80 registers is the widest useful block
         if (const int forceW = env_int("POLAR_CUDA_WARPS_PER_BLOCK", 0)) w = std::min(w, forceW);
-        const int maxT = w <= 16 ? 512 : w <= 24 ? 768 : 1024;
+        const int maxT = w <= 16 ? 512 : w <= POLAR_SCL_MID_THREADS / 32 ? POLAR_SCL_MID_THREADS : 1024;
         c->kernel = scl_i8_kernel_for(L, maxT);
         CUDA_TRY(cudaFuncSetAttribute((const void*)c->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)prop.sharedMemPerBlockOptin));
@@ -348,6 +378,8 @@ int setup_decoder_geometry(polar_code* c)
         if (g.spillWarpW) {
             const size_t words = (size_t)g.spillWarpW * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
             CUDA_TRY(cudaMalloc(&c->dSpill, words * sizeof(uint32_t)));
+            c->spillBytes = words * sizeof(uint32_t);
+            setup_l2_window(c, prop);
         }
         return POLAR_OK;
     }
@@ -383,6 +415,8 @@ int setup_decoder_geometry(polar_code* c)
     if (g.spillWarpW) {
         const size_t words = (size_t)g.spillWarpW * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
         CUDA_TRY(cudaMalloc(&c->dSpill, words * sizeof(uint32_t)));
+        c->spillBytes = words * sizeof(uint32_t);
+        setup_l2_window(c, prop);
     }
     return POLAR_OK;
 }
@@ -434,7 +468,7 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaFree(c->dFailIdx); cudaFree(c->dFailCount); cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
     if (c->hFailCount) cudaFreeHost(c->hFailCount);
     if (c->scratchFree) cudaEventDestroy(c->scratchFree);
-    delete c->encProg;
+    delete[] c->encProg;
     polar_cuda_code_destroy(c->fast);
     polar_cuda_code_destroy(c->list);
     for (int i = 0; i < 2; ++i) {
@@ -596,23 +630,26 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
             tab[nWords] = (uint32_t)runs.size();
             if (N >= 32 && N <= 1024 && (int)runs.size() <= ENC_MAX_RUNS && !env_int("POLAR_CUDA_ENC_V1", 0)) {
                 // the same runs for the bit-reversed words of encode_reg_kernel: source row, funnel shift, destination mask
-                EncodeProgram* g = new EncodeProgram();
-                memset(g, 0, sizeof(*g));
-                for (int w = 0; w < nWords; ++w) {
-                    g->first[w] = (uint16_t)tab[w];
-                    uint32_t rev = 0;
-                    for (int i = 0; i < 32; ++i) rev |= ((wordTab[w].x >> i) & 1u) << (31 - i);
-                    g->maskRev[w] = rev;
+                EncodeProgram* g2 = new EncodeProgram[2]; // [0]: one frame per thread, [1]: two (row strides differ)
+                memset(g2, 0, 2 * sizeof(EncodeProgram));
+                for (int fpt = 1; fpt <= 2; ++fpt) {
+                    EncodeProgram* g = g2 + (fpt - 1);
+                    for (int w = 0; w < nWords; ++w) {
+                        g->first[w] = (uint16_t)tab[w];
+                        uint32_t rev = 0;
+                        for (int i = 0; i < 32; ++i) rev |= ((wordTab[w].x >> i) & 1u) << (31 - i);
+                        g->maskRev[w] = rev;
+                    }
+                    for (int w = nWords; w < 34; ++w) g->first[w] = (uint16_t)runs.size();
+                    for (size_t r = 0; r < runs.size(); ++r) {
+                        const int b = runs[r] & 31u, len = (runs[r] >> 5) & 63u, k = runs[r] >> 11, s = k & 31, wi = k >> 5;
+                        const uint32_t hiRow = s >= b ? wi + 1 : wi, sh = s >= b ? s - b : 32 - (b - s);
+                        g->run[r].x = hiRow * (uint32_t)(ENC_REG_THREADS * fpt * 4);
+                        g->run[r].y = sh;
+                        g->run[r].z = (len == 32 ? 0xFFFFFFFFu : ((1u << len) - 1u)) << (32 - b - len);
+                    }
                 }
-                for (int w = nWords; w < 34; ++w) g->first[w] = (uint16_t)runs.size();
-                for (size_t r = 0; r < runs.size(); ++r) {
-                    const int b = runs[r] & 31u, len = (runs[r] >> 5) & 63u, k = runs[r] >> 11, s = k & 31, wi = k >> 5;
-                    const uint32_t hiRow = s >= b ? wi + 1 : wi, sh = s >= b ? s - b : 32 - (b - s);
-                    g->run[r].x = hiRow * (uint32_t)(ENC_ROW_WORDS * 4);
-                    g->run[r].y = sh;
-                    g->run[r].z = (len == 32 ? 0xFFFFFFFFu : ((1u << len) - 1u)) << (32 - b - len);
-                }
-                c->encProg = g;
+                c->encProg = g2;
             }
             tab.insert(tab.end(), runs.begin(), runs.end());
             c->nRuns = nWords + 1; // offset of the run entries inside the table
@@ -679,7 +716,22 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
     const long long warpsNeeded = ((long long)nFrames + framesPerWarp - 1) / framesPerWarp;
     const long long blocksNeeded = (warpsNeeded + c->warpsPerBlock - 1) / c->warpsPerBlock;
     const int grid = (int)std::min<long long>(blocksNeeded, (long long)c->blocksPerSM * c->numSMs);
-    c->kernel<<<grid, c->warpsPerBlock * 32, c->smemPerBlock, st>>>(p, c->sched);
+    if (c->dSpill && c->l2Persist > 0.f) {
+        // the scratch of the spilled stages as a persisting L2 window: the input streaming through the cache does not evict it
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(c->warpsPerBlock * 32); cfg.dynamicSmemBytes = c->smemPerBlock; cfg.stream = st;
+        cudaLaunchAttribute at{};
+        at.id = cudaLaunchAttributeAccessPolicyWindow;
+        at.val.accessPolicyWindow.base_ptr = c->dSpill;
+        at.val.accessPolicyWindow.num_bytes = c->l2WindowBytes;
+        at.val.accessPolicyWindow.hitRatio = c->l2Persist;
+        at.val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        at.val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        cfg.attrs = &at; cfg.numAttrs = 1;
+        CUDA_TRY(cudaLaunchKernelEx(&cfg, c->kernel, p, c->sched));
+    } else {
+        c->kernel<<<grid, c->warpsPerBlock * 32, c->smemPerBlock, st>>>(p, c->sched);
+    }
     c->launches++;
     CUDA_TRY(cudaGetLastError());
     if (c->dSpill || c->dQuant) { // batches of one handle on different streams must not share the scratch concurrently
@@ -1386,6 +1438,7 @@ int polar_cuda_sim_create(int device, int N, const uint32_t* frozen, int nFrozen
     *out = nullptr;
     if (decoderKind < POLAR_KIND_FASTSSC_I8 || decoderKind > POLAR_KIND_ADAPTIVE_MIXED) return fail(POLAR_E_ARG, "not a decoder kind");
     if (batchFrames < 1 || batchFrames > ((size_t)1 << 24)) return fail(POLAR_E_ARG, "batch must be 1 .. 2^24 frames");
+    if (N < 4) return fail(POLAR_E_UNSUPPORTED, "the link simulator draws four code positions per thread: block length >= 4");
     polar_sim* s = new polar_sim;
     s->device = device; s->N = N; s->batch = batchFrames;
     int rc = polar_cuda_code_create(device, POLAR_KIND_ENC, N, frozen, nFrozen, 1, systematic, crcBits, &s->enc);

@@ -18,7 +18,7 @@ static DecodeKernel pick(int L)
 DecodeKernel scl_i8_kernel_for(int L, int maxThreads)
 {
     if (maxThreads <= 512) return pick<512>(L);
-    if (maxThreads <= 768) return pick<768>(L);
+    if (maxThreads <= POLAR_SCL_MID_THREADS) return pick<POLAR_SCL_MID_THREADS>(L);
     return pick<1024>(L);
 }
 } // namespace polar

@@ -71,12 +71,12 @@ __global__ void __launch_bounds__(256) sim_payload_kernel(const SimParams p)
 // four code positions per thread: BPSK, AWGN (Box-Muller on two Philox pairs), amplification, quantiser
 __global__ void __launch_bounds__(256) sim_channel_kernel(const SimParams p)
 {
-    const int groups = p.N >> 2;
+    const int groups = p.N >> 2, lgGroups = 31 - __clz(groups); // N is a power of two: shifts, not a 64-bit division per thread
     const long long total = p.nFrames * groups;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        const long long f = i / groups;
-        const int j = (int)(i - f * groups);
+        const long long f = i >> lgGroups;
+        const int j = (int)(i & (groups - 1));
         const unsigned long long frame = p.firstFrame + (unsigned long long)f;
         const uint4 rnd = philox4x32_10(make_uint4((uint32_t)frame, (uint32_t)(frame >> 32), (uint32_t)j, SIM_STREAM_NOISE),
                                         make_uint2(p.seedLo, p.seedHi));

@@ -113,7 +113,9 @@ int polar_cuda_decode_batch_noalloc(polar_code_t code, const void* llr, int llrT
                                     uint8_t* ok_out, void* stream);
 
 /* Encoder::encode_vector over nFrames frames.  info: nFrames x K/8 bytes; like the reference the
- * trailing CRC bytes of every info block are overwritten in place.  code_out: nFrames x N/8. */
+ * trailing CRC bytes of every info block are overwritten in place.  code_out: nFrames x N/8.
+ * DEVICE buffers may have any alignment; the fast kernel (one thread per two frames, 128/256-bit row accesses) runs when
+ * the info rows are 4-byte and the codeword rows min(N/8, 32)-byte aligned, which every cudaMalloc'ed [nFrames][...] array is. */
 int polar_cuda_encode_batch(polar_code_t code, uint8_t* info, int mem, size_t nFrames, uint8_t* code_out,
                             void* stream);
 
