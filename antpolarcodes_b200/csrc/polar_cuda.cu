@@ -223,7 +223,9 @@ int setup_decoder_geometry(polar_code* c)
     g.prefetchNext = env_int("POLAR_CUDA_PREFETCH", 0);
     g.rootLeaf = 0;
     g.llrBase = 0; g.bitBase = 0; g.bitSpill = c->lgN + 1; g.spA = g.spB0 = g.spB1 = 0;
-    g.regStages = c->kind == POLAR_KIND_SCL_I8 ? std::min(env_int("POLAR_CUDA_REG_STAGES", 4), c->lgN - 2) : -1;
+    g.regStages = c->kind == POLAR_KIND_SCL_I8 ? std::min(env_int("POLAR_CUDA_REG_STAGES", 4), c->lgN - 2)
+                : c->kind == POLAR_KIND_SCL_F32 ? std::min(env_int("POLAR_CUDA_F32_REG_STAGES", 4), c->lgN - 2) : -1;
+    if (c->kind == POLAR_KIND_SCL_F32 && g.regStages < 1) g.regStages = 0; // 0 = every stage through the slots (round-1 layout)
     g.bitB1 = 0;
     g.spillWarpW = 0;
     g.chanRow = -1;
@@ -243,17 +245,20 @@ int setup_decoder_geometry(polar_code* c)
         // what sets the resident warp count; region A of the bit slots holds stages 0..lgN-1 (the root is
         // assembled by the epilogue), region B is a ping-pong pair.
         // (fp32 lists: one float per word, stage s at word 2^s - 1 of the slot)
-        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 10 ? (sclF32 ? 5 : (c->lgN >= 11 && L >= 16 ? 4 : 3)) : // N=2048, L=32: 8 -> 10 resident warps, 1.56 -> 1.67 Gbit/s
+        const bool f32Regs = sclF32 && g.regStages >= 1; // fp32 lists with the stages <= regStages in registers
+        int nSpill = env_int("POLAR_CUDA_SPILL", c->lgN >= 10 ? (sclF32 ? (f32Regs ? 4 : 5) : (c->lgN >= 11 && L >= 16 ? 4 : 3)) : // N=2048, L=32: 8 -> 10 resident warps, 1.56 -> 1.67 Gbit/s
                                                   c->lgN >= 9 ? (sclF32 ? 3 : 2) : (c->lgN >= 7 ? 1 : 0));
         nSpill = std::max(0, std::min(nSpill, c->lgN - 5));
         if (sclF32) // keep a warp's footprint within reach of a few resident warps per SM
-            while (nSpill < c->lgN - 5 && (size_t)32 * f32_woff(c->lgN - nSpill) * 4 > 96 * 1024) ++nSpill;
+            while (nSpill < c->lgN - 5 &&
+                   (size_t)32 * (f32_woff(c->lgN - nSpill) - (f32Regs ? f32_woff(g.regStages + 1) : 0)) * 4 > 96 * 1024)
+                ++nSpill;
         g.smemStages = c->lgN - nSpill;
         g.rootLeaf = (!c->ops.empty() && (int)POLAR_OP_STAGE(c->ops[0]) == c->lgN) ? 1 : 0;
         // int8 lists: the stages <= regStages never touch shared memory, so the slots only hold the stages above them
-        const int firstSm = sclF32 ? 0 : std::max(0, g.regStages + 1);
-        g.llrBase = sclF32 ? 0 : llr_woff(firstSm);
-        int slot = sclF32 ? f32_woff(g.smemStages) : std::max(1, llr_woff(g.smemStages) - g.llrBase);
+        const int firstSm = sclF32 ? (f32Regs ? g.regStages + 1 : 0) : std::max(0, g.regStages + 1);
+        g.llrBase = sclF32 ? f32_woff(firstSm) : llr_woff(firstSm);
+        int slot = sclF32 ? std::max(1, f32_woff(g.smemStages) - g.llrBase) : std::max(1, llr_woff(g.smemStages) - g.llrBase);
         while (slot % L != 1 % L) ++slot;
         g.slotW = slot;
         const int nW = std::max(1, c->N / 32);
@@ -292,9 +297,9 @@ int setup_decoder_geometry(polar_code* c)
             g.spillWarpW = 32 * words;
         }
         c->kernel = sclF32 ? scl_f32_kernel_for(L) : scl_i8_kernel_for(L, 512);
-        if (!sclF32) // dense handler ids for the kernel's jump table (the fp32 kernel decodes (code, stage) itself)
-            for (size_t i = 0; i < c->ops.size(); ++i)
-                c->sched.ops[i] = (c->ops[i] & 0xFFFFu) | (scl_handler_id(c->ops[i], g.regStages) << 16);
+        // dense handler ids for the kernels' jump tables
+        for (size_t i = 0; i < c->ops.size(); ++i)
+            c->sched.ops[i] = (c->ops[i] & 0xFFFFu) | (scl_handler_id(c->ops[i], g.regStages) << 16);
     } else if (c->kind == POLAR_KIND_FASTSSC_F32) {
         // fp32 Fast-SSC: same row stack, one float per word; stage s sits at row 2^s - 1.  Stages from 6 up
         // (64 floats and more) go to the L2-resident scratch.

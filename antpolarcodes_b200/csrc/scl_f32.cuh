@@ -384,6 +384,238 @@ POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSp
     scl_finish_leaf(c, s, isRight);
 }
 
+// ---------------------------------------------------------------- register stages (the fp32 version of scl_i8.cuh's)
+// Most steps of the tree work on blocks of at most 16 elements, always with lane = path.  A stage-s block (s <= 4) is
+// 2^s floats of the owning lane's registers (block of stage s at x[2^s - 1 ..]); its partial sums are the bit fields
+// ba / bb of the int8 kernel (rs_put_bits / rs_op_combine are shared).  Handlers are compiled per stage; a fork moves
+// the live register blocks with the lazy-copy vectors.  Float orders as in the generic handlers above.
+struct SclfRegs {
+    float x[31];
+};
+
+template <int S>
+POLAR_DEV void rsf_load_parent(const SclCtx& c, const SclfRegs& R, float (&a)[1 << S], float (&b)[1 << S])
+{
+    constexpr int n = 1 << S;
+    bool inRegs = false;
+    if constexpr (S < 4) inRegs = S + 1 <= c.P.regStages;
+    if (inRegs) {
+        if constexpr (S < 4) {
+            constexpr int PO = (2 << S) - 1;
+#pragma unroll
+            for (int i = 0; i < n; ++i) { a[i] = R.x[PO + i]; b[i] = R.x[PO + n + i]; }
+        }
+    } else {
+        const FWords src = sclf_llr_block(c, S + 1, (uint32_t)(c.llrPtr >> (5 * (S + 1))) & 31u);
+#pragma unroll
+        for (int i = 0; i < n; ++i) { a[i] = src(i); b[i] = src(i + n); }
+    }
+}
+
+template <int S, bool ISG>
+POLAR_DEV void rsf_op_fg(SclCtx& c, SclfRegs& R)
+{
+    constexpr int n = 1 << S, OFF = n - 1;
+    float a[n], b[n];
+    rsf_load_parent<S>(c, R, a, b);
+    if constexpr (ISG) {
+        const uint32_t lb = c.ba >> n; // left-child bits of stage S
+#pragma unroll
+        for (int i = 0; i < n; ++i) R.x[OFF + i] = g_f32(a[i], b[i], ((lb >> i) & 1u) << 31);
+    } else {
+#pragma unroll
+        for (int i = 0; i < n; ++i) R.x[OFF + i] = f_f32(a[i], b[i]);
+    }
+}
+
+template <int S>
+POLAR_DEV void rsf_adopt(SclCtx& c, SclfRegs& R, int outMet, int srcPath)
+{
+    const int src = c.fb + srcPath;
+    c.metric = outMet;
+    c.llrPtr = shfl64(c.llrPtr, src);
+    c.lbPtr = shfl64(c.lbPtr, src);
+    c.ba = __shfl_sync(FULL_MASK, c.ba, src);
+#pragma unroll
+    for (int i = (2 << S) - 1; i < 31; ++i) R.x[i] = __shfl_sync(FULL_MASK, R.x[i], src); // the blocks of the stages above S
+}
+
+// sclf_lane_reduce on a register block
+template <int S, class T>
+POLAR_DEV float rsf_lane_reduce(const float* x, T t)
+{
+    constexpr int n = 1 << S;
+    float l[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) l[j] = 0.0f;
+    if constexpr (n < 8) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (j < n) l[j] = __fadd_rn(0.0f, t(x[j]));
+    } else {
+#pragma unroll
+        for (int v = 0; v < n; v += 8) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) l[j] = __fadd_rn(l[j], t(x[v + j]));
+        }
+    }
+    float r = __fadd_rn(l[0], l[1]);
+#pragma unroll
+    for (int j = 2; j < 8; ++j) r = __fadd_rn(r, l[j]);
+    return r;
+}
+
+template <int L, int S>
+POLAR_DEV void rsf_leaf_r0(SclCtx& c, SclfRegs& R, bool isRight) // scl_avx_float.cpp:320-340
+{
+    const float pun = rsf_lane_reduce<S>(&R.x[(1 << S) - 1], [](float v) { return v < 0.0f ? v : 0.0f; });
+    c.metric = __float_as_int(__fadd_rn(sclf_metric(c), pun));
+    rs_put_bits<S>(c, 0u, isRight);
+}
+
+template <int L, int S>
+POLAR_DEV void rsf_leaf_rep(SclCtx& c, SclfRegs& R, int lgP, bool isRight) // scl_avx_float.cpp:432-481
+{
+    constexpr int lgL = Log2<L>::v;
+    const float* x = &R.x[(1 << S) - 1];
+    const float z = rsf_lane_reduce<S>(x, [](float v) { return v < 0.0f ? v : 0.0f; });
+    const float o = rsf_lane_reduce<S>(x, [](float v) { return v > 0.0f ? v : 0.0f; });
+    const float m = sclf_metric(c);
+    const float cand[2] = { __fadd_rn(m, z), __fadd_rn(m, -o) };
+    const int lgPo = min(lgL, lgP + 1);
+    float outMet;
+    int outIdx;
+    sclf_select<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
+    rsf_adopt<S>(c, R, __float_as_int(outMet), (outIdx >> 1) & (L - 1));
+    rs_put_bits<S>(c, (outIdx & 1) ? 0xFFFFFFFFu : 0u, isRight);
+}
+
+// sclf_weak_search on a register block: the K smallest |x| with their original positions, in the reference's order
+template <int S, int K>
+POLAR_DEV void rsf_weak_search(const float* x, float (&val)[K], int (&idx)[K])
+{
+    constexpr int n = 1 << S;
+    unsigned long long T[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) T[r] = ~0ull;
+#pragma unroll
+    for (int i = 4; i < n; ++i) { // the tail never moves: keep its K smallest (|x|, position) keys
+        unsigned long long key = ((unsigned long long)(fbits(x[i]) & 0x7FFFFFFFu) << 16) | (unsigned)i;
+#pragma unroll
+        for (int r = 0; r < K; ++r) {
+            const unsigned long long lo = key < T[r] ? key : T[r];
+            key = key < T[r] ? T[r] : key;
+            T[r] = lo;
+        }
+    }
+    uint32_t ha[4];
+    int cur[4];
+    bool alive[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        ha[e] = e < n ? (fbits(x[e < n ? e : 0]) & 0x7FFFFFFFu) : 0u;
+        cur[e] = e;
+        alive[e] = e < n;
+    }
+    int t = 0;
+#pragma unroll
+    for (int i = 0; i < K; ++i) {
+        if (i < n) {
+            unsigned long long best = ~0ull;
+#pragma unroll
+            for (int r = 0; r < K; ++r)
+                if (r == t) best = T[r];
+            int bw = -1;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const unsigned long long key = ((unsigned long long)ha[e] << 16) | (unsigned)cur[e];
+                if (alive[e] && key < best) { best = key; bw = e; }
+            }
+            const int bpos = (int)(best & 0xFFFFull);
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (alive[e] && cur[e] == i) cur[e] = bpos;
+            if (bw >= 0) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (e == bw) alive[e] = false;
+                idx[i] = bw;
+            } else {
+                idx[i] = bpos;
+                ++t;
+            }
+            val[i] = bitsf((uint32_t)(best >> 16));
+        } else {
+            idx[i] = 0;
+            val[i] = __int_as_float(0x7F800000);
+        }
+    }
+}
+
+// RateOne (scl_avx_float.cpp:356-419) and SPC (:498-617) on a register block
+template <int L, int S, bool SPC>
+POLAR_DEV void rsf_leaf_flip(SclCtx& c, SclfRegs& R, int lgP, bool isRight)
+{
+    constexpr int lgL = Log2<L>::v, n = 1 << S, lgF = SPC ? 3 : 2;
+    const float* x = &R.x[n - 1];
+    uint32_t sgn = 0;
+#pragma unroll
+    for (int i = 0; i < n; ++i) sgn |= (fbits(x[i]) >> 31) << i;
+    const int par = SPC ? (__popc(sgn) & 1) : 0;
+    float a[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
+    int idx[4] = { 0, 0, 0, 0 };
+    if constexpr (SPC) {
+        rsf_weak_search<S, 4>(x, a, idx);
+    } else {
+        float v2[2];
+        int i2[2];
+        rsf_weak_search<S, 2>(x, v2, i2);
+        a[0] = v2[0]; a[1] = v2[1];
+        idx[0] = i2[0]; idx[1] = i2[1];
+    }
+    float m = sclf_metric(c);
+    float cand[8];
+    auto sub = [](float p, float q) { return __fadd_rn(p, -q); };
+    if constexpr (SPC) {
+        const float inv = par ? 0.0f : 1.0f;
+        if (par) m = sub(m, a[0]);
+        const float mw = sub(m, __fmul_rn(inv, a[0]));
+        cand[0] = m;
+        cand[1] = sub(mw, a[1]);
+        cand[2] = sub(mw, a[2]);
+        cand[3] = sub(mw, a[3]);
+        cand[4] = sub(sub(m, a[1]), a[2]);
+        cand[5] = sub(sub(m, a[1]), a[3]);
+        cand[6] = sub(sub(m, a[2]), a[3]);
+        cand[7] = sub(sub(sub(mw, a[1]), a[2]), a[3]);
+    } else {
+        cand[0] = m;
+        cand[1] = sub(m, a[0]);
+        cand[2] = sub(m, a[1]);
+        cand[3] = sub(sub(m, a[0]), a[1]);
+        cand[4] = cand[5] = cand[6] = cand[7] = 0.0f;
+    }
+    const int lgPo = min(lgL, lgP + lgF);
+    float outMet;
+    int outIdx;
+    sclf_select<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
+    const int srcPath = (outIdx >> lgF) & (L - 1), kind = outIdx & ((1 << lgF) - 1);
+    // what the new path needs from its parent: the four weak positions (4 bits each), the parity and the sign bits
+    const uint32_t mine = (uint32_t)idx[0] | ((uint32_t)idx[1] << 4) | ((uint32_t)idx[2] << 8) | ((uint32_t)idx[3] << 12) |
+                          ((uint32_t)par << 16) | (sgn << 17);
+    const uint32_t got = __shfl_sync(FULL_MASK, mine, c.fb + srcPath);
+    uint32_t v = got >> 17;
+    if constexpr (S == 4) v |= (__shfl_sync(FULL_MASK, sgn >> 15, c.fb + srcPath) & 1u) << 15;
+    const int sp = (got >> 16) & 1;
+    const uint32_t table = SPC ? (sp ? 0xEDB78421u : 0xFCA69530u) : 0x3210u;
+    const uint32_t fm = (table >> (4 * kind)) & 15u;
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+        if ((fm >> t) & 1u) v ^= 1u << ((got >> (4 * t)) & 15u);
+    rsf_adopt<S>(c, R, __float_as_int(outMet), srcPath);
+    rs_put_bits<S>(c, v, isRight);
+}
+
 // ---------------------------------------------------------------- the kernel
 template <int L>
 __global__ void __launch_bounds__(512, 1) scl_f32_kernel(const __grid_constant__ DecodeParams p,
@@ -400,6 +632,9 @@ __global__ void __launch_bounds__(512, 1) scl_f32_kernel(const __grid_constant__
     const int fi = lane >> lgL;
     c.frame = base + fi * p.frameW;
     c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + c.fb : nullptr;
+    SclfRegs R;
+#pragma unroll
+    for (int i = 0; i < 31; ++i) R.x[i] = 0.0f;
 
     const long long nQuads = (p.nFrames + FPW - 1) / FPW;
     for (long long qb = blockIdx.x; qb * warpsPerBlock < nQuads; qb += gridDim.x) {
@@ -411,23 +646,42 @@ __global__ void __launch_bounds__(512, 1) scl_f32_kernel(const __grid_constant__
         c.llrPtr = 0ull;
         c.lbPtr = 0ull;
         int lgPfinal = 0;
+        c.ba = 0u;
+        c.bb[0] = c.bb[1] = 0u;
         for (int pc = 0;; ++pc) {
+            // op word: bits 31..16 hold the dense handler id written by the host (scl_handler_id), as in scl_i8_kernel
             const uint32_t op = sched.ops[pc];
-            const uint32_t code = POLAR_OP_CODE(op);
-            if (code == OP_END) break;
+            const uint32_t hid = op >> 16;
+            if (hid == SCL_H_END) break;
             const int s = (int)POLAR_OP_STAGE(op), lgP = (int)POLAR_OP_LGP(op);
             const bool isRight = (POLAR_OP_FLAGS(op) & OPF_RIGHT) != 0;
             if (p.lockstep && (pc & (p.lockstep - 1)) == 0) __syncthreads(); // lockstep = 2^k: a barrier every 2^k steps
-            switch (code) {
-            case OP_F: sclf_op_fg<L, false>(c, s, lgP); break;
-            case OP_G: sclf_op_fg<L, true>(c, s, lgP); break;
-            case OP_COMBINE: scl_op_combine<L>(c, s, lgP, isRight); break;
-            case OP_SCL_R0: sclf_leaf_r0<L>(c, s, lgP, isRight); lgPfinal = lgP; break;
-            case OP_SCL_REP: sclf_leaf_rep<L>(c, s, lgP, isRight); lgPfinal = min(lgL, lgP + 1); break;
-            case OP_SCL_R1: sclf_leaf_flip<L>(c, s, lgP, isRight, false); lgPfinal = min(lgL, lgP + 2); break;
-            case OP_SCL_SPC: sclf_leaf_flip<L>(c, s, lgP, isRight, true); lgPfinal = min(lgL, lgP + 3); break;
+#define POLAR_RSF_CASES(BASE, CALL)                \
+    case BASE + 0: { constexpr int S = 1; CALL; } break; \
+    case BASE + 1: { constexpr int S = 2; CALL; } break; \
+    case BASE + 2: { constexpr int S = 3; CALL; } break; \
+    case BASE + 3: { constexpr int S = 4; CALL; } break;
+            switch (hid) {
+            POLAR_RSF_CASES(SCL_H_RS_F, (rsf_op_fg<S, false>(c, R)))
+            POLAR_RSF_CASES(SCL_H_RS_G, (rsf_op_fg<S, true>(c, R)))
+            POLAR_RSF_CASES(SCL_H_RS_C, (rs_op_combine<S>(c, isRight)))
+            POLAR_RSF_CASES(SCL_H_RS_R0, (rsf_leaf_r0<L, S>(c, R, isRight)); lgPfinal = lgP)
+            case SCL_H_RS_REP + 0: rsf_leaf_rep<L, 1>(c, R, lgP, isRight); lgPfinal = min(lgL, lgP + 1); break; // blocks of 2 and 4 only
+            case SCL_H_RS_REP + 1: rsf_leaf_rep<L, 2>(c, R, lgP, isRight); lgPfinal = min(lgL, lgP + 1); break;
+            POLAR_RSF_CASES(SCL_H_RS_R1, (rsf_leaf_flip<L, S, false>(c, R, lgP, isRight)); lgPfinal = min(lgL, lgP + 2))
+            case SCL_H_RS_SPC + 1: rsf_leaf_flip<L, 2, true>(c, R, lgP, isRight); lgPfinal = min(lgL, lgP + 3); break; // an SPC leaf has >= 4 elements
+            case SCL_H_RS_SPC + 2: rsf_leaf_flip<L, 3, true>(c, R, lgP, isRight); lgPfinal = min(lgL, lgP + 3); break;
+            case SCL_H_RS_SPC + 3: rsf_leaf_flip<L, 4, true>(c, R, lgP, isRight); lgPfinal = min(lgL, lgP + 3); break;
+            case SCL_H_F: sclf_op_fg<L, false>(c, s, lgP); break;
+            case SCL_H_G: sclf_op_fg<L, true>(c, s, lgP); break;
+            case SCL_H_C: scl_op_combine<L>(c, s, lgP, isRight); break;
+            case SCL_H_R0: sclf_leaf_r0<L>(c, s, lgP, isRight); lgPfinal = lgP; break;
+            case SCL_H_REP: sclf_leaf_rep<L>(c, s, lgP, isRight); lgPfinal = min(lgL, lgP + 1); break;
+            case SCL_H_R1: sclf_leaf_flip<L>(c, s, lgP, isRight, false); lgPfinal = min(lgL, lgP + 2); break;
+            case SCL_H_SPC: sclf_leaf_flip<L>(c, s, lgP, isRight, true); lgPfinal = min(lgL, lgP + 3); break;
             default: break;
             }
+#undef POLAR_RSF_CASES
         }
         scl_extract_best_path<L>(p, c, base, scr, lane, live, quad, lgPfinal);
     }
