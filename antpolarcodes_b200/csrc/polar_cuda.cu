@@ -400,7 +400,7 @@ int setup_decoder_geometry(polar_code* c)
     // equal resident warps: wide blocks first (one or two lockstep domains per SM keep the instruction fetch shared)
     // (the Fast-SSC kernels take the widest block instead: one barrier domain per SM)
     static const int sclOrder[] = { 16, 8, 12, 6, 4, 10, 5, 7, 3, 2, 1, 9 }; // one barrier domain per SM first (10.39 -> 10.76 Gbit/s at N=1024, L=8)
-    static const int sclF32Order[] = { 4, 6, 8, 5, 7, 3, 2, 1, 12, 16, 10, 9 }; // measured: small blocks win here
+    static const int sclF32Order[] = { 8, 4, 6, 5, 7, 3, 2, 1, 12, 16, 10, 9 }; // measured (register stages): 8 x 2 4.64, 4 x 4 4.51, 16 x 1 4.13 Gbit/s
     static const int scOrder[] = { 16, 12, 8, 6, 4, 3, 2, 1, 14, 10, 7, 5 };
     for (int i = 0; i < 12; ++i) {
         const int w = sclF32 ? sclF32Order[i] : scl ? sclOrder[i] : scOrder[i];

@@ -128,20 +128,41 @@ POLAR_DEV float sclf_lane_reduce(const FWords& src, int n, T t)
 
 // findWeakLlrs(.., n, 4) on |llr| (arrayfuncs.h:209-231): values and original indices of the 4 smallest,
 // with the reference's swap displacement of elements 0..3 (see scl_weak_search in scl_i8.cuh)
-POLAR_DEV void sclf_weak_search(const FWords& src, int n, float (&val)[4], int (&idx)[4])
+POLAR_DEV void sclf_weak_search(const FWords& src, int n, float (&val)[4], int (&idx)[4], uint32_t& signXor)
 {
     unsigned long long T[4];
 #pragma unroll
     for (int r = 0; r < 4; ++r) T[r] = ~0ull;
-    for (int i = 4; i < n; ++i) { // the tail never moves: keep its 4 smallest (|x|, position) keys
-        unsigned long long key = ((unsigned long long)(fbits(src(i)) & 0x7FFFFFFFu) << 16) | (unsigned)i;
+    uint32_t px = 0u, thr = 0xFFFFFFFFu; // thr = |x| of the 4th smallest tail key so far: a key that is not below it changes nothing
+    auto take = [&](uint32_t u, int i) { // (positions come in ascending order, so on equal |x| the earlier one stays: strict <)
+        px ^= u;
+        const uint32_t a = u & 0x7FFFFFFFu;
+        if (a < thr) {
+            unsigned long long key = ((unsigned long long)a << 16) | (unsigned)i;
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const unsigned long long lo = key < T[r] ? key : T[r];
-            key = key < T[r] ? T[r] : key;
-            T[r] = lo;
+            for (int r = 0; r < 4; ++r) {
+                const unsigned long long lo = key < T[r] ? key : T[r];
+                key = key < T[r] ? T[r] : key;
+                T[r] = lo;
+            }
+            thr = (uint32_t)(T[3] >> 16);
         }
+    };
+    // the tail never moves: keep its 4 smallest (|x|, position) keys; eight loads in flight (the block may sit in the L2 scratch)
+    int i = 4;
+    for (; i < n && (i & 7); ++i) take(fbits(src(i)), i);
+    for (; i + 7 < n; i += 8) {
+        uint32_t u[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) u[t] = fbits(src(i + t));
+#pragma unroll
+        for (int t = 0; t < 8; ++t) take(u[t], i + t);
     }
+    for (; i < n; ++i) take(fbits(src(i)), i);
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+        if (e < n) px ^= fbits(src(e));
+    signXor = px;
     uint32_t ha[4];
     int cur[4];
     bool alive[4];
@@ -320,12 +341,9 @@ POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSp
     int idx[4] = { 0, 0, 0, 0 };
     int par = 0;
     if (g == 0) {
-        if (isSpc) {
-            uint32_t px = 0;
-            for (int i = 0; i < n; ++i) px ^= fbits(src(i));
-            par = (int)(px >> 31);
-        }
-        sclf_weak_search(src, n, a, idx);
+        uint32_t px = 0;
+        sclf_weak_search(src, n, a, idx, px); // one pass: the weak positions and the XOR of the signs
+        if (isSpc) par = (int)(px >> 31);
     }
     const int srcLane = c.fb + ((c.gl << lgG) & (L - 1));
 #pragma unroll
