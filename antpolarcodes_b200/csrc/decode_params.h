@@ -38,6 +38,7 @@ struct DecodeParams {
     int regStages;            // int8 list decoder: stages <= regStages live in registers (min(4, lgN - 2), or -1: none)
     // Fast-SSC (one frame per thread): rows of 32 words
     int llrRows, bitRows, tileRow, outRow, chanRow, nRuns;
+    int chanVec;              // the channel rows are 16-byte aligned (fp32 list decoder: 128-bit channel loads)
     int prefetchNext;         // Fast-SSC kernels: a warp prefetches the channel rows of its next frame group into L2
     int useTma, mbarRow;      // Fast-SSC int8: channel tiles filled by TMA bulk copies (one 128-byte row segment per lane)
 };

@@ -20,23 +20,30 @@
 
 namespace polar {
 
+// L2 scratch of the spilled stages: [group of 4 elements][32 columns][4] -- column = lane of the slot's owner, so a lane reads
+// four consecutive elements of its block with one 128-bit access and the 32 lanes of a warp touch one contiguous 512-byte row.
+// Element i of a block sits at p + (i >> 2) * 128 + (i & 3) floats (c.spill already points at the frame's first column).
 struct FWords {
     const float* p;
-    int stride;
-    bool cg;
-    POLAR_DEV float operator()(int i) const { return cg ? __ldcg(p + i * stride) : p[i * stride]; }
+    int stride; // 1: contiguous (shared-memory slot, channel row); 32: spilled block
+    bool cg;    // spilled block: read at L2 (the writers use st.cg, L1 is never involved)
+    POLAR_DEV float operator()(int i) const { return cg ? __ldcg(p + ((i >> 2) << 7) + (i & 3)) : p[i]; }
 };
 
 POLAR_DEV int sclf_spill_woff(const SclCtx& c, int stage) { return ((1 << stage) - (1 << c.P.smemStages)) << 5; }
+POLAR_DEV float* sclf_spill_block(const SclCtx& c, int stage, uint32_t slot)
+{
+    return reinterpret_cast<float*>(c.spill + sclf_spill_woff(c, stage) + 4 * slot);
+}
 POLAR_DEV FWords sclf_llr_block(const SclCtx& c, int stage, uint32_t slot)
 {
     if (stage == c.P.lgN) return FWords{ reinterpret_cast<const float*>(c.chan), 1, false };
-    if (stage >= c.P.smemStages) return FWords{ reinterpret_cast<const float*>(c.spill + sclf_spill_woff(c, stage) + slot), 32, true };
+    if (stage >= c.P.smemStages) return FWords{ sclf_spill_block(c, stage, slot), 32, true };
     return FWords{ reinterpret_cast<const float*>(c.llrp() + slot * c.P.slotW + f32_woff(stage)), 1, false };
 }
 POLAR_DEV void sclf_store(const SclCtx& c, int stage, uint32_t slot, int i, float v)
 {
-    if (stage >= c.P.smemStages) __stcg(reinterpret_cast<float*>(c.spill + sclf_spill_woff(c, stage) + slot) + i * 32, v);
+    if (stage >= c.P.smemStages) __stcg(sclf_spill_block(c, stage, slot) + ((i >> 2) << 7) + (i & 3), v);
     else reinterpret_cast<float*>(c.llrp() + slot * c.P.slotW + f32_woff(stage))[i] = v;
 }
 
@@ -67,6 +74,48 @@ POLAR_DEV void sclf_op_fg(SclCtx& c, int s, int lgP)
     const int lgG = Log2<L>::v - lgP, G = 1 << lgG, q = c.gl >> lgG, g = c.gl & (G - 1), n = 1 << s;
     const FWords src = sclf_llr_block(c, s + 1, scl_slot_of(c, c.llrPtr, s + 1, q, lgG));
     const BitBlk lb = scl_bits_a(c, scl_slot_of(c, c.lbPtr, s, q, lgG), s);
+    if (lgG == 0 && s >= 2 && s + 1 >= c.P.smemStages && (s + 1 < c.P.lgN || c.P.chanVec)) {
+        // a lane owns the path and the parent block sits in the L2 scratch or in the channel row: 128-bit accesses, four
+        // elements per step, eight loads in flight
+        const bool chan = (s + 1 == c.P.lgN);
+        const int vs = chan ? 1 : 32; // float4 stride between consecutive groups of four elements
+        const float4* A = reinterpret_cast<const float4*>(src.p);
+        const float4* B = A + (n >> 2) * vs;
+        const bool toSpill = s >= c.P.smemStages;
+        float4* dv = toSpill ? reinterpret_cast<float4*>(sclf_spill_block(c, s, (uint32_t)q)) : nullptr;
+        float* ds = reinterpret_cast<float*>(c.llrp() + q * c.P.slotW + f32_woff(s));
+        auto ld4 = [&](const float4* p4) { return chan ? __ldcs(p4) : __ldcg(p4); };
+        auto one = [&](const float4& a, const float4& b, int e0) { // elements e0 .. e0+3
+            float4 r;
+            if (ISG) {
+                const uint32_t lw = lb.ld(e0 >> 5) >> (e0 & 31);
+                r.x = g_f32(a.x, b.x, lw << 31);
+                r.y = g_f32(a.y, b.y, (lw >> 1) << 31);
+                r.z = g_f32(a.z, b.z, (lw >> 2) << 31);
+                r.w = g_f32(a.w, b.w, (lw >> 3) << 31);
+            } else {
+                r.x = f_f32(a.x, b.x); r.y = f_f32(a.y, b.y); r.z = f_f32(a.z, b.z); r.w = f_f32(a.w, b.w);
+            }
+            if (toSpill) {
+                __stcg(dv + (e0 >> 2) * 32, r);
+            } else {
+                ds[e0] = r.x; ds[e0 + 1] = r.y; ds[e0 + 2] = r.z; ds[e0 + 3] = r.w;
+            }
+        };
+        const int nv = n >> 2;
+        int v = 0;
+        for (; v + 3 < nv; v += 4) {
+            float4 a[4], b[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) { a[t] = ld4(A + (v + t) * vs); b[t] = ld4(B + (v + t) * vs); }
+#pragma unroll
+            for (int t = 0; t < 4; ++t) one(a[t], b[t], 4 * (v + t));
+        }
+        for (; v < nv; ++v) one(ld4(A + v * vs), ld4(B + v * vs), 4 * v);
+        scl_set_own(c.llrPtr, s, c.gl);
+        __syncwarp();
+        return;
+    }
     int i = g;
     if (s + 1 >= c.P.smemStages) { // parent block in the L2 scratch / global memory: 16 loads in flight
         for (; i + 7 * G < n; i += 8 * G) {
@@ -649,7 +698,7 @@ __global__ void __launch_bounds__(512, 1) scl_f32_kernel(const __grid_constant__
     c.fb = lane & ~(L - 1);
     const int fi = lane >> lgL;
     c.frame = base + fi * p.frameW;
-    c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + c.fb : nullptr;
+    c.spill = p.spill ? p.spill + (size_t)(blockIdx.x * warpsPerBlock + warp) * p.spillWarpW + 4 * c.fb : nullptr; // column = lane
     SclfRegs R;
 #pragma unroll
     for (int i = 0; i < 31; ++i) R.x[i] = 0.0f;

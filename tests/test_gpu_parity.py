@@ -229,6 +229,25 @@ def test_encoder_device_buffers_aligned_and_not(gpu, N, K, ctype, crc):
         assert int(raw_out[:off_out].sum()) == 0 and int(raw_out[off_out + n * nb:].sum()) == 0   # nothing outside the rows
 
 
+def test_scl_f32_llr_rows_not_16_byte_aligned(gpu):
+    """DEVICE float LLRs at an address that is only 4-byte aligned: the fp32 list decoder must not use its 128-bit channel loads."""
+    import torch
+    N, K, L, crc, n = 256, 128, 4, 8, 300
+    frozen = ap.frozen_bits(N, K, 0.0, "BB")
+    llr, _ = awgn_llrs(N, frozen, n, 2.0, crc, fmt="f32")
+    dec = ap.PolarDecoder(N, L, frozen, "float")
+    dec.setErrorDetection(crc)
+    want, wok = dec.decode_batch(llr)
+    raw = torch.zeros(n * N + 8, dtype=torch.float32, device="cuda")
+    for off in (1, 2, 3):
+        view = raw[off:off + n * N].view(n, N)
+        view.copy_(torch.from_numpy(llr))
+        got, gok = dec.decode_batch(view)
+        assert np.array_equal(got.cpu().numpy(), want) and np.array_equal(gok.cpu().numpy(), wok), off
+    eo, ek = oracle_decode(KIND_SCL_F32, N, frozen, llr, L, 1, crc)
+    assert np.array_equal(want, eo) and np.array_equal(wok, ek)
+
+
 def test_primitives_exhaustive(gpu):
     """F and G over all 256 x 256 int8 pairs, both bit values (superset of decodingtest.cpp:504-737)."""
     from polar_testlib import oracle
