@@ -717,7 +717,7 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
         p.llr = c->dQuant;
     }
     if (p.useTma && ((uintptr_t)p.llr & 15u)) p.useTma = 0; // bulk copies need 16-byte aligned rows: 4-byte cp.async tiles instead
-    p.chanVec = (((uintptr_t)p.llr & 15u) == 0 && ((size_t)c->N * 4) % 16 == 0) ? 1 : 0;
+    p.chanVec = (((uintptr_t)p.llr & 15u) == 0 && ((size_t)c->N * (f32Kind ? 4 : 1)) % 16 == 0) ? 1 : 0;
     const int framesPerWarp = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32) ? 32 / c->L : 32;
     const long long warpsNeeded = ((long long)nFrames + framesPerWarp - 1) / framesPerWarp;
     const long long blocksNeeded = (warpsNeeded + c->warpsPerBlock - 1) / c->warpsPerBlock;
@@ -1101,7 +1101,7 @@ int polar_cuda_decode_batch_noalloc(polar_code_t c, const void* llr, int llrType
     p.runs = c->dRuns;
     p.nRuns = c->nRuns;
     if (p.useTma && ((uintptr_t)p.llr & 15u)) p.useTma = 0;
-    p.chanVec = (((uintptr_t)p.llr & 15u) == 0 && ((size_t)c->N * 4) % 16 == 0) ? 1 : 0;
+    p.chanVec = (((uintptr_t)p.llr & 15u) == 0 && ((size_t)c->N * (f32Kind ? 4 : 1)) % 16 == 0) ? 1 : 0;
     const int framesPerWarp = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32) ? 32 / c->L : 32;
     const long long warpsNeeded = ((long long)nFrames + framesPerWarp - 1) / framesPerWarp;
     const long long blocksNeeded = (warpsNeeded + c->warpsPerBlock - 1) / c->warpsPerBlock;

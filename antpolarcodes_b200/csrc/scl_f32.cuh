@@ -322,6 +322,120 @@ POLAR_DEV void sclf_select(const SclCtx& c, const float (&cand)[FMAX], int lgF, 
     __syncwarp();
 }
 
+// Lists of at most 8 paths (M = P * F <= 64 candidates), as scl_select_k32 of the int8 kernel: the 64-bit key is
+// (ordered metric << 32) | (63 - CURRENT position) << 6 | ORIGINAL candidate index, so the winner of a step names the candidate
+// it came from: no swap history, no walk back.  Compiled once per (L, fan-out), steps unrolled, rows moved with vector accesses.
+// Returns the key of list entry gl: metric = f32_unordered(key >> 32), original candidate = key & 63.
+template <int L, int LGF>
+__device__ __noinline__ unsigned long long sclf_select_k64(uint32_t* sel, int gl, int lgP, int nOut, float c0, float c1, float c2,
+                                                           float c3, float c4, float c5, float c6, float c7)
+{
+    static_assert(L <= 8, "6 + 6 position bits");
+    constexpr int F = 1 << LGF;
+    constexpr int VW = (L < F ? L : F) < 4 ? (L < F ? L : F) : 4; // the frame's scratch is aligned to L words, a lane's row to min(L, F)
+    const float cand[8] = { c0, c1, c2, c3, c4, c5, c6, c7 };
+    uint32_t* klo = sel + (gl << LGF);
+    uint32_t* khi = klo + 8 * L;
+    const bool act = gl < (1 << lgP);
+    uint32_t lo[F], hi[F];
+    unsigned long long lmax = 0ull;
+#pragma unroll
+    for (int k = 0; k < F; ++k) {
+        const uint32_t pos = (uint32_t)(gl << LGF) + k;
+        hi[k] = act ? f32_ordered(__fadd_rn(cand[k], 0.0f)) : 0u; // -0.0 -> +0.0: equal floats, equal keys
+        lo[k] = act ? (((63u - pos) << 6) | pos) : 0u;
+        const unsigned long long key = ((unsigned long long)hi[k] << 32) | lo[k];
+        lmax = key > lmax ? key : lmax;
+    }
+    auto put = [&](uint32_t* dst, const uint32_t (&v)[F]) {
+        if constexpr (VW == 4) {
+#pragma unroll
+            for (int k = 0; k < F; k += 4) *reinterpret_cast<uint4*>(dst + k) = make_uint4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+        } else if constexpr (VW == 2) {
+#pragma unroll
+            for (int k = 0; k < F; k += 2) *reinterpret_cast<uint2*>(dst + k) = make_uint2(v[k], v[k + 1]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < F; ++k) dst[k] = v[k];
+        }
+    };
+    auto get = [&](const uint32_t* src, uint32_t (&v)[F]) {
+        if constexpr (VW == 4) {
+#pragma unroll
+            for (int k = 0; k < F; k += 4) {
+                const uint4 q = *reinterpret_cast<const uint4*>(src + k);
+                v[k] = q.x; v[k + 1] = q.y; v[k + 2] = q.z; v[k + 3] = q.w;
+            }
+        } else if constexpr (VW == 2) {
+#pragma unroll
+            for (int k = 0; k < F; k += 2) {
+                const uint2 q = *reinterpret_cast<const uint2*>(src + k);
+                v[k] = q.x; v[k + 1] = q.y;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < F; ++k) v[k] = src[k];
+        }
+    };
+    put(klo, lo);
+    put(khi, hi);
+    __syncwarp();
+    unsigned long long outKey = 0ull;
+    uint32_t* k0lo = sel;          // position-indexed views
+    uint32_t* k0hi = sel + 8 * L;
+#pragma unroll
+    for (int i = 0; i < L; ++i) {
+        if (i >= nOut) break;
+        const unsigned long long best = list_max64<L>(lmax);
+        if (gl == i) outKey = best;
+        const uint32_t pf = (uint32_t)best & 0xFC0u; // (63 - position of the winner) << 6
+        const int pos = 63 - (int)(pf >> 6), wl = pos >> LGF;
+        const int il = i >> LGF;
+        const uint32_t ilo = k0lo[i], ihi = k0hi[i]; // the element now at position i ...
+        __syncwarp();
+        if (gl == wl) { // ... moves to the winner's place
+            k0lo[pos] = (ilo & ~0xFC0u) | pf;
+            k0hi[pos] = ihi;
+        }
+        if (gl == il) { // position i is final
+            k0lo[i] = 0u;
+            k0hi[i] = 0u;
+        }
+        __syncwarp();
+        if (gl == wl || gl == il) {
+            get(klo, lo);
+            get(khi, hi);
+            lmax = 0ull;
+#pragma unroll
+            for (int k = 0; k < F; ++k) {
+                const unsigned long long key = ((unsigned long long)hi[k] << 32) | lo[k];
+                lmax = key > lmax ? key : lmax;
+            }
+        }
+    }
+    __syncwarp();
+    return outKey;
+}
+
+// Candidate pruning for any list size: keys with the origin inside for L <= 8, the swap-history version above else.
+template <int L, int FMAX>
+POLAR_DEV void sclf_prune(const SclCtx& c, const float (&cand)[FMAX], int lgF, int lgP, int nOut, float& outMet, int& outIdx)
+{
+    if constexpr (L <= 8) {
+        unsigned long long k;
+        if constexpr (FMAX == 2) {
+            k = sclf_select_k64<L, 1>(c.selp(), c.gl, lgP, nOut, cand[0], cand[1], 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
+        } else {
+            if (lgF == 3) k = sclf_select_k64<L, 3>(c.selp(), c.gl, lgP, nOut, cand[0], cand[1], cand[2], cand[3], cand[4], cand[5], cand[6], cand[7]);
+            else k = sclf_select_k64<L, 2>(c.selp(), c.gl, lgP, nOut, cand[0], cand[1], cand[2], cand[3], 0.f, 0.f, 0.f, 0.f);
+        }
+        outMet = f32_unordered((uint32_t)(k >> 32));
+        outIdx = (int)(k & 63ull);
+    } else {
+        sclf_select<L, FMAX>(c, cand, lgF, lgP, nOut, outMet, outIdx);
+    }
+}
+
 POLAR_DEV float sclf_metric(const SclCtx& c) { return __int_as_float(c.metric); }
 
 // sign bits of 32 consecutive LLRs (or the whole block when shorter), LSB first
@@ -370,7 +484,7 @@ POLAR_DEV void sclf_leaf_rep(SclCtx& c, int s, int lgP, bool isRight)
     const int lgPo = min(lgL, lgP + 1);
     float outMet;
     int outIdx;
-    sclf_select<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
+    sclf_prune<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
     scl_adopt(c, __float_as_int(outMet), (outIdx >> 1) & (L - 1));
     const int lgGo = lgL - lgPo, Go = 1 << lgGo, qo = c.gl >> lgGo, go = c.gl & (Go - 1);
     const int kq = __shfl_sync(FULL_MASK, outIdx & 1, c.fb + qo);
@@ -426,7 +540,7 @@ POLAR_DEV void sclf_leaf_flip(SclCtx& c, int s, int lgP, bool isRight, bool isSp
     const int lgPo = min(lgL, lgP + lgF);
     float outMet;
     int outIdx;
-    sclf_select<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
+    sclf_prune<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
     const int srcPath = (outIdx >> lgF) & (L - 1), kind = outIdx & ((1 << lgF) - 1);
     const uint32_t s01 = __shfl_sync(FULL_MASK, pk01, c.fb + srcPath), s23 = __shfl_sync(FULL_MASK, pk23, c.fb + srcPath);
     const int sp = __shfl_sync(FULL_MASK, par, c.fb + srcPath);
@@ -552,7 +666,7 @@ POLAR_DEV void rsf_leaf_rep(SclCtx& c, SclfRegs& R, int lgP, bool isRight) // sc
     const int lgPo = min(lgL, lgP + 1);
     float outMet;
     int outIdx;
-    sclf_select<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
+    sclf_prune<L, 2>(c, cand, 1, lgP, 1 << lgPo, outMet, outIdx);
     rsf_adopt<S>(c, R, __float_as_int(outMet), (outIdx >> 1) & (L - 1));
     rs_put_bits<S>(c, (outIdx & 1) ? 0xFFFFFFFFu : 0u, isRight);
 }
@@ -665,7 +779,7 @@ POLAR_DEV void rsf_leaf_flip(SclCtx& c, SclfRegs& R, int lgP, bool isRight)
     const int lgPo = min(lgL, lgP + lgF);
     float outMet;
     int outIdx;
-    sclf_select<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
+    sclf_prune<L, 8>(c, cand, lgF, lgP, 1 << lgPo, outMet, outIdx);
     const int srcPath = (outIdx >> lgF) & (L - 1), kind = outIdx & ((1 << lgF) - 1);
     // what the new path needs from its parent: the four weak positions (4 bits each), the parity and the sign bits
     const uint32_t mine = (uint32_t)idx[0] | ((uint32_t)idx[1] << 4) | ((uint32_t)idx[2] << 8) | ((uint32_t)idx[3] << 12) |
