@@ -798,8 +798,11 @@ POLAR_DEV void rsf_leaf_flip(SclCtx& c, SclfRegs& R, int lgP, bool isRight)
 }
 
 // ---------------------------------------------------------------- the kernel
+#ifndef POLAR_SCLF_MAXT
+#define POLAR_SCLF_MAXT 512 // launch bound = register budget (512 threads: 128 registers); A/B builds override it
+#endif
 template <int L>
-__global__ void __launch_bounds__(512, 1) scl_f32_kernel(const __grid_constant__ DecodeParams p,
+__global__ void __launch_bounds__(POLAR_SCLF_MAXT, 1) scl_f32_kernel(const __grid_constant__ DecodeParams p,
                                                       const __grid_constant__ Schedule sched)
 {
     constexpr int lgL = Log2<L>::v, FPW = 32 / L;
