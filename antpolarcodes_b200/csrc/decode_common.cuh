@@ -75,7 +75,11 @@ POLAR_DEV uint32_t gather_info_and_syndrome(const DecodeParams& p, const uint32_
 POLAR_DEV void store_info(const DecodeParams& p, long long frame, const uint32_t* outw, int lane)
 {
     uint8_t* dst = p.out + frame * p.kb;
-    if ((p.kb & 3) == 0) {
+    if ((p.kb & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) { // 16-byte packed stores (outw is 16-byte aligned)
+        const uint4* s16 = reinterpret_cast<const uint4*>(outw);
+        uint4* d16 = reinterpret_cast<uint4*>(dst);
+        for (int i = lane; i < (p.kb >> 4); i += 32) d16[i] = s16[i];
+    } else if ((p.kb & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 3u) == 0) {
         uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
         for (int i = lane; i < (p.kb >> 2); i += 32) d4[i] = outw[i];
     } else {
@@ -165,10 +169,17 @@ POLAR_DEV void thread_frame_epilogue(const DecodeParams& p, uint32_t* sm, int la
     const long long nHere = min(32LL, p.nFrames - frame0);
     uint8_t* dst = p.out + frame0 * p.kb;
     const long long bytes = nHere * p.kb;
-    if (wordOut) {
+    // the image is one contiguous run of bytes (16-byte aligned in shared memory): the widest store the caller's buffer allows
+    if ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+        uint4* d16 = reinterpret_cast<uint4*>(dst);
+        const uint4* s16 = reinterpret_cast<const uint4*>(img);
+        for (long long i = lane; i < (bytes >> 4); i += 32) d16[i] = s16[i];
+        for (long long i = (bytes & ~15LL) + lane; i < bytes; i += 32) dst[i] = img[i];
+    } else if ((reinterpret_cast<uintptr_t>(dst) & 3u) == 0) {
         uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
         const uint32_t* s4 = reinterpret_cast<const uint32_t*>(img);
         for (long long i = lane; i < (bytes >> 2); i += 32) d4[i] = s4[i];
+        for (long long i = (bytes & ~3LL) + lane; i < bytes; i += 32) dst[i] = img[i];
     } else {
         for (long long i = lane; i < bytes; i += 32) dst[i] = img[i];
     }

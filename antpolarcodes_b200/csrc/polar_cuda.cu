@@ -469,6 +469,7 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaSetDevice(c->device);
     cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab); cudaFree(c->dGenNib);
     cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
+    if (c->l2Persist > 0.f) cudaCtxResetPersistingL2Cache(); // the lines of the scratch window go back to normal before the memory is freed
     cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns); cudaFree(c->dSoftScratch);
     cudaFree(c->dFailIdx); cudaFree(c->dFailCount); cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
     if (c->hFailCount) cudaFreeHost(c->hFailCount);
@@ -697,6 +698,8 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
     p.spill = c->dSpill;
     p.runs = c->dRuns;
     p.nRuns = c->nRuns;
+    if ((reinterpret_cast<uintptr_t>(llr) & 3u) != 0) // the kernels read the rows as 32-bit words (float rows are aligned by type)
+        return fail(POLAR_E_ARG, "DEVICE LLR buffer must be 4-byte aligned");
     if (c->scratchBusy && c->scratchStream != st) CUDA_TRY(cudaStreamWaitEvent(st, c->scratchFree, 0));
     const bool f32Kind = (c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32);
     if (llrType == POLAR_LLR_F32 && !f32Kind) { // CharContainer::insertLlr(const float*): quantise once, decode the int8 copy

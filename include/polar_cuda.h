@@ -71,6 +71,8 @@ int polar_cuda_code_destroy(polar_code_t code);
  *   stream   : cudaStream_t (0 = default stream).  HOST buffers are copied synchronously;
  *              DEVICE buffers are processed asynchronously on the stream (adaptive kinds wait once on the
  *              stream for the count of failed frames before they launch the list decoder).
+ *              DEVICE llr must be 4-byte aligned (POLAR_E_ARG otherwise; 16-byte aligned rows take the 128-bit paths);
+ *              DEVICE info_out / ok_out may have any alignment (16-byte packed stores when info_out allows).
  * Adaptive kinds: ADAPTIVE_I8 takes int8 or float LLRs (float is quantised once, both decoders see the int8
  * copy, like AdaptiveChar::setSignal, adaptive_char.cpp:60-64); ADAPTIVE_F32 and ADAPTIVE_MIXED take float. */
 int polar_cuda_decode_batch(polar_code_t code, const void* llr, int llrType, int mem, size_t nFrames,

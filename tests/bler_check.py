@@ -115,8 +115,13 @@ def main():
         # of points outside the 95 % interval is reported next to its expectation
         print(json.dumps({"points": len(records), "points_failing_parity_or_ci": bad, "points_outside_cpu_wilson95": out95,
                           "expected_outside_wilson95": round(0.05 * sum(1 for r in records if r.get("subsample")), 1)}))
-        return 1 if bad else 0
-    return 0
+        rc = 1 if bad else 0
+    else:
+        rc = 0
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+    return rc
 
 
 if __name__ == "__main__":

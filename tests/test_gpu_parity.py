@@ -248,6 +248,29 @@ def test_scl_f32_llr_rows_not_16_byte_aligned(gpu):
     assert np.array_equal(want, eo) and np.array_equal(wok, ek)
 
 
+@pytest.mark.parametrize("L,crc,ctype", [(1, 0, "BB"), (8, 16, "5G")])
+def test_decode_device_out_any_alignment(gpu, L, crc, ctype):
+    """DEVICE output rows at 16-, 4- and 1-byte aligned addresses: the epilogues pick the widest store the buffer allows and
+    write nothing outside the rows."""
+    import torch
+    N, K, n = 1024, 512, 1000 + 7
+    frozen = ap.frozen_bits(N, K, 0.0, ctype)
+    llr, _ = awgn_llrs(N, frozen, n, 2.0, crc)
+    dec = ap.PolarDecoder(N, L, frozen, "char")
+    dec.setErrorDetection(crc)
+    want, wok = dec.decode_batch(llr)
+    d_llr = torch.from_numpy(llr).cuda()
+    kb = K // 8
+    for off in (0, 16, 4, 1, 7):
+        raw = torch.full((n * kb + 64,), 0xEE, dtype=torch.uint8, device="cuda")
+        out = raw[off:off + n * kb].view(n, kb)
+        ok = torch.empty(n, dtype=torch.uint8, device="cuda")
+        dec.decode_batch(d_llr, out=out, ok=ok)
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy(), want) and np.array_equal(ok.cpu().numpy(), wok), off
+        assert bool((raw[:off] == 0xEE).all()) and bool((raw[off + n * kb:] == 0xEE).all()), off
+
+
 def test_primitives_exhaustive(gpu):
     """F and G over all 256 x 256 int8 pairs, both bit values (superset of decodingtest.cpp:504-737)."""
     from polar_testlib import oracle
