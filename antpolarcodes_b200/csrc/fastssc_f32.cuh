@@ -86,6 +86,55 @@ POLAR_DEV void scf_load_tile(const ScfCtx& c, uint32_t* tile, int w0, int cw)
     }
 }
 
+// ---- 16-byte variant of the channel tiles (rows of 32 words, 16-byte aligned channel rows): tile row r = frame frame0 + r, its
+// 16-byte chunk q stored at chunk position q ^ (r & 7).  A lane copies one chunk of four rows per instruction (8 instead of 32
+// copies per tile) and reads its own row back with 128-bit loads: the eight lanes of a quarter warp hit eight different chunk
+// positions, i.e. all 32 banks -- no conflicts without the padding that would break the 16-byte alignment.
+POLAR_DEV void scf_load_tile_v(const ScfCtx& c, uint32_t* tile, int w0)
+{
+    const int rsub = c.lane >> 3, q = c.lane & 7;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int r = rsub + 4 * k;
+        const long long f = min(c.frame0 + r, c.lastFrame);
+        cp_async16(tile + r * 32 + ((q ^ (r & 7)) << 2), c.chan + f * c.nw + w0 + 4 * q);
+    }
+}
+struct ScfTilesV { // the lane's rows of both tiles
+    const uint32_t* ra;
+    const uint32_t* rb;
+    int sw; // lane & 7
+    POLAR_DEV float4 a4(int q) const { return *reinterpret_cast<const float4*>(ra + ((q ^ sw) << 2)); }
+    POLAR_DEV float4 b4(int q) const { return *reinterpret_cast<const float4*>(rb + ((q ^ sw) << 2)); }
+};
+// the 32 elements [i0, i0 + 32) of a top-level step out of the 16-byte tiles; dst = the lane's rows of the child stage
+template <int CODE>
+POLAR_DEV void scf_top_chunk_v(ScfCtx& c, const ScfTilesV& t, float* dst, int s, int pos, int i0)
+{
+    uint32_t lw = 0u, rw = 0u;
+    if (CODE == OP_G || CODE == OP_G_R1) lw = SCF_ROW(c, c.bitRow + ((pos + i0) >> 5)); // pos and i0 are multiples of 32 here
+#pragma unroll 2
+    for (int q = 0; q < 8; ++q) {
+        const float4 a = t.a4(q), b = t.b4(q);
+        const float av[4] = { a.x, a.y, a.z, a.w }, bv[4] = { b.x, b.y, b.z, b.w };
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int j = 4 * q + e;
+            float r;
+            if (CODE == OP_F) r = f_f32(av[e], bv[e]);
+            else if (CODE == OP_G_0R) r = __fadd_rn(av[e], bv[e]);
+            else r = g_f32(av[e], bv[e], (lw >> j) << 31);
+            if (CODE == OP_G_R1) rw |= (fbits(r) >> 31) << j;
+            else dst[(i0 + j) << 5] = r;
+        }
+    }
+    if (CODE == OP_G_R1) { // fastssc_avx_float.cpp:204-219: right bits = sign(right), left bits ^= right bits
+        const int h = 1 << s;
+        SCF_ROW(c, c.bitRow + ((pos + h + i0) >> 5)) = rw;
+        SCF_ROW(c, c.bitRow + ((pos + i0) >> 5)) = lw ^ rw;
+    }
+}
+
 // bit `i` of the block starting at absolute position pos, moved to the sign position
 POLAR_DEV uint32_t scf_bit_neg(const ScfCtx& c, int pos, int i)
 {
@@ -354,6 +403,19 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_f32_kernel(const 
                     else if (code == OP_G_0R) scf_add_range(src, dst, 0, n);
                     else if (code == OP_G) scf_g_range(c, src, dst, pos, 0, n);
                     else scf_g_r1_range(c, src, s, pos, 0, n);
+                } else if (p.chanVec && cw == 32) { // n == halfN >= 32, 16-byte aligned channel rows: 16-byte tiles
+                    const ScfTilesV tv{ tileA + lane * 32, tileB + lane * 32, lane & 7 };
+                    for (int i0 = 0; i0 < halfN; i0 += 32) {
+                        scf_load_tile_v(c, tileA, i0);
+                        scf_load_tile_v(c, tileB, halfN + i0);
+                        cp_async_wait_all();
+                        __syncwarp();
+                        if (code == OP_F) scf_top_chunk_v<OP_F>(c, tv, dst, s, pos, i0);
+                        else if (code == OP_G_0R) scf_top_chunk_v<OP_G_0R>(c, tv, dst, s, pos, i0);
+                        else if (code == OP_G) scf_top_chunk_v<OP_G>(c, tv, dst, s, pos, i0);
+                        else scf_top_chunk_v<OP_G_R1>(c, tv, dst, s, pos, i0);
+                        __syncwarp();
+                    }
                 } else { // n == halfN
                     for (int i0 = 0; i0 < halfN; i0 += cw) {
                         scf_load_tile(c, tileA, i0, cw);

@@ -106,6 +106,12 @@ POLAR_DEV void cp_async4(uint32_t* smemDst, const uint32_t* globalSrc)
     const unsigned sa = (unsigned)__cvta_generic_to_shared(smemDst);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(globalSrc) : "memory");
 }
+// 16-byte variant (L2 only: streaming data; both addresses 16-byte aligned)
+POLAR_DEV void cp_async16(uint32_t* smemDst, const uint32_t* globalSrc)
+{
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(globalSrc) : "memory");
+}
 POLAR_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // ---- L2 prefetch of a contiguous byte range by one warp (the next frame group's channel rows: the top-level steps of the
