@@ -82,6 +82,46 @@ POLAR_DEV void sc_load_tile(const ScCtx& c, uint32_t* tile, int w0, int cw)
     }
 }
 
+// ---- 16-byte variant of the channel tiles (rows of 32 words, 16-byte aligned channel rows): tile row r = frame frame0 + r, its
+// 16-byte chunk q stored at chunk position q ^ (r & 7).  A lane copies one chunk of four rows per instruction (8 instead of 32
+// copies per tile) and reads its own row back with 128-bit loads: the eight lanes of a quarter warp hit eight different chunk
+// positions, i.e. all 32 banks -- no conflicts without the padding that would break the 16-byte alignment.
+POLAR_DEV void sc_load_tile_v(const ScCtx& c, uint32_t* tile, int w0)
+{
+    const int rsub = c.lane >> 3, q = c.lane & 7;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int r = rsub + 4 * k;
+        const long long f = min(c.frame0 + r, c.lastFrame);
+        cp_async16(tile + r * 32 + ((q ^ (r & 7)) << 2), c.chan + f * (c.P.N >> 2) + w0 + 4 * q);
+    }
+}
+// the 32 words [w0, w0 + 32) of a top-level step out of the 16-byte tiles
+template <int CODE>
+POLAR_DEV void sc_top_chunk_v(ScCtx& c, const uint32_t* tileA, const uint32_t* tileB, uint32_t* dst, int pos, int w0)
+{
+    const uint32_t* ra = tileA + c.lane * 32;
+    const uint32_t* rb = tileB + c.lane * 32;
+    const int sw = c.lane & 7;
+    const uint32_t* bits = c.smLane + ((c.P.llrRows + (pos >> 5)) << 5);
+#pragma unroll 2
+    for (int q = 0; q < 8; ++q) {
+        const uint4 a = *reinterpret_cast<const uint4*>(ra + ((q ^ sw) << 2));
+        const uint4 b = *reinterpret_cast<const uint4*>(rb + ((q ^ sw) << 2));
+        uint32_t nb = 0u; // left bits of the four words (four bits per word)
+        if constexpr (CODE == OP_G) nb = bits[((w0 + 4 * q) >> 3) << 5] >> ((q & 1) * 16);
+        const uint32_t av[4] = { a.x, a.y, a.z, a.w }, bv[4] = { b.x, b.y, b.z, b.w };
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            uint32_t v;
+            if constexpr (CODE == OP_F) v = f4(av[e], bv[e]);
+            else if constexpr (CODE == OP_G_0R) v = adds4(av[e], bv[e]);
+            else v = g4(av[e], bv[e], nibble_to_msb(nb >> (4 * e)));
+            dst[(w0 + 4 * q + e) << 5] = v;
+        }
+    }
+}
+
 // ---- TMA variant of the channel tiles (N >= 256): tile[r * 32 + i] = channel word (w0 + i) of frame (frame0 + r), filled by
 // 32 bulk copies of 128 bytes (lane r copies the row segment of frame r; SASS UBLKCP) that complete on the warp's mbarrier.
 // Rows are 128-byte aligned, so the transposing read is done ROTATED: at step i lane l takes word (i + l) & 31 of its row,
@@ -685,6 +725,17 @@ __global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_i8_kernel(const _
                         if (code == OP_F) sc_top_rot<OP_F>(c, tileA, tileB, dst, pos, w0);
                         else if (code == OP_G_0R) sc_top_rot<OP_G_0R>(c, tileA, tileB, dst, pos, w0);
                         else sc_top_rot<OP_G>(c, tileA, tileB, dst, pos, w0);
+                        __syncwarp();
+                    }
+                } else if (p.chanVec && cw == 32 && code != OP_G_R1) { // words == halfW >= 32, 16-byte aligned rows: 16-byte tiles
+                    for (int w0 = 0; w0 < halfW; w0 += 32) {
+                        sc_load_tile_v(c, tileA, w0);
+                        sc_load_tile_v(c, tileB, halfW + w0);
+                        cp_async_wait_all();
+                        __syncwarp();
+                        if (code == OP_F) sc_top_chunk_v<OP_F>(c, tileA, tileB, dst, pos, w0);
+                        else if (code == OP_G_0R) sc_top_chunk_v<OP_G_0R>(c, tileA, tileB, dst, pos, w0);
+                        else sc_top_chunk_v<OP_G>(c, tileA, tileB, dst, pos, w0);
                         __syncwarp();
                     }
                 } else { // words == halfW
