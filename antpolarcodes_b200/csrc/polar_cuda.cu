@@ -135,6 +135,7 @@ struct polar_code {
     polar::EncodeProgram* encProg = nullptr; // encoder, 32 <= N <= 1024: the scatter program of encode_reg_kernel (kernel parameter)
     uint32_t* dSpill = nullptr;    // list decoders: L2-resident scratch for the top LLR stage
     size_t spillBytes = 0, l2WindowBytes = 0;
+    uint32_t* dSpill2 = nullptr;   // HOST pipeline: the second stream's scratch (allocated on first use)
     float l2Persist = 0.f;         // > 0: the scratch is launched as a persisting L2 access-policy window with this hit ratio
     int8_t* dQuant = nullptr;      // int8 copy of fp32 LLRs (quantiser pre-pass)
     size_t quantBytes = 0;
@@ -470,7 +471,7 @@ int polar_cuda_code_destroy(polar_code_t c)
     cudaFree(c->dInfoPos); cudaFree(c->dWordTab); cudaFree(c->dSynTab); cudaFree(c->dGenTab); cudaFree(c->dGenNib);
     cudaFree(c->dLlr); cudaFree(c->dOut); cudaFree(c->dOk); cudaFree(c->dInfo);
     if (c->l2Persist > 0.f) cudaCtxResetPersistingL2Cache(); // the lines of the scratch window go back to normal before the memory is freed
-    cudaFree(c->dSpill); cudaFree(c->dQuant); cudaFree(c->dRuns); cudaFree(c->dSoftScratch);
+    cudaFree(c->dSpill); cudaFree(c->dSpill2); cudaFree(c->dQuant); cudaFree(c->dRuns); cudaFree(c->dSoftScratch);
     cudaFree(c->dFailIdx); cudaFree(c->dFailCount); cudaFree(c->dGather); cudaFree(c->dOutC); cudaFree(c->dOkC);
     if (c->hFailCount) cudaFreeHost(c->hFailCount);
     if (c->scratchFree) cudaEventDestroy(c->scratchFree);
@@ -685,8 +686,10 @@ int polar_cuda_code_create(int device, int kind, int N, const uint32_t* frozen, 
 }
 
 // One batch with DEVICE buffers on stream st: optional quantiser pre-pass + the decoder kernel.
+// spillOverride: the HOST pipeline gives each of its two streams a scratch of its own, so the kernels of consecutive chunks may
+// overlap (the caller then owns the ordering: the handle's cross-stream guard is skipped)
 static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t nFrames, uint8_t* out, uint8_t* ok,
-                            cudaStream_t st, uint8_t* cand = nullptr)
+                            cudaStream_t st, uint8_t* cand = nullptr, uint32_t* spillOverride = nullptr, bool ownOrdering = false)
 {
     DecodeParams p = c->geo;
     p.cand = cand;
@@ -695,12 +698,12 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
     p.crcInit = c->synInit;
     p.nFrames = (long long)nFrames;
     p.llr = llr; p.out = out; p.ok = ok;
-    p.spill = c->dSpill;
+    p.spill = spillOverride ? spillOverride : c->dSpill;
     p.runs = c->dRuns;
     p.nRuns = c->nRuns;
     if ((reinterpret_cast<uintptr_t>(llr) & 3u) != 0) // the kernels read the rows as 32-bit words (float rows are aligned by type)
         return fail(POLAR_E_ARG, "DEVICE LLR buffer must be 4-byte aligned");
-    if (c->scratchBusy && c->scratchStream != st) CUDA_TRY(cudaStreamWaitEvent(st, c->scratchFree, 0));
+    if (!ownOrdering && c->scratchBusy && c->scratchStream != st) CUDA_TRY(cudaStreamWaitEvent(st, c->scratchFree, 0));
     const bool f32Kind = (c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32);
     if (llrType == POLAR_LLR_F32 && !f32Kind) { // CharContainer::insertLlr(const float*): quantise once, decode the int8 copy
         const size_t need = nFrames * (size_t)c->N;
@@ -725,13 +728,13 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
     const long long warpsNeeded = ((long long)nFrames + framesPerWarp - 1) / framesPerWarp;
     const long long blocksNeeded = (warpsNeeded + c->warpsPerBlock - 1) / c->warpsPerBlock;
     const int grid = (int)std::min<long long>(blocksNeeded, (long long)c->blocksPerSM * c->numSMs);
-    if (c->dSpill && c->l2Persist > 0.f) {
+    if (p.spill && c->l2Persist > 0.f) {
         // the scratch of the spilled stages as a persisting L2 window: the input streaming through the cache does not evict it
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(grid); cfg.blockDim = dim3(c->warpsPerBlock * 32); cfg.dynamicSmemBytes = c->smemPerBlock; cfg.stream = st;
         cudaLaunchAttribute at{};
         at.id = cudaLaunchAttributeAccessPolicyWindow;
-        at.val.accessPolicyWindow.base_ptr = c->dSpill;
+        at.val.accessPolicyWindow.base_ptr = p.spill;
         at.val.accessPolicyWindow.num_bytes = c->l2WindowBytes;
         at.val.accessPolicyWindow.hitRatio = c->l2Persist;
         at.val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
@@ -743,7 +746,7 @@ static int decode_on_device(polar_code* c, const void* llr, int llrType, size_t 
     }
     c->launches++;
     CUDA_TRY(cudaGetLastError());
-    if (c->dSpill || c->dQuant) { // batches of one handle on different streams must not share the scratch concurrently
+    if (!ownOrdering && (c->dSpill || c->dQuant)) { // batches of one handle on different streams must not share the scratch concurrently
         if (!c->scratchFree) CUDA_TRY(cudaEventCreateWithFlags(&c->scratchFree, cudaEventDisableTiming));
         CUDA_TRY(cudaEventRecord(c->scratchFree, st));
         c->scratchStream = st;
@@ -938,6 +941,17 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
         }
     }
     CUDA_TRY(cudaStreamSynchronize(st)); // work queued before this call on the caller's stream comes first
+    // Two scratches (one per pipeline stream) let the kernel of chunk k+1 start on the SMs that the tail of chunk k has left;
+    // with one shared scratch the kernels are chained by events.  Not with the quantiser pre-pass (its scratch is shared too) and
+    // not while the scratch is pinned in L2 (two windows would fight for the set-aside).
+    const bool nativeType = llrType == ((c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32) ? POLAR_LLR_F32 : POLAR_LLR_I8);
+    bool overlap = depth == 2 && nativeType && c->l2Persist <= 0.f && env_int("POLAR_CUDA_OVERLAP", 1) != 0;
+    if (overlap && c->dSpill && !c->dSpill2 && cudaMalloc(&c->dSpill2, c->spillBytes) != cudaSuccess) {
+        cudaGetLastError();
+        c->dSpill2 = nullptr;
+        overlap = false;
+    }
+    if (overlap && c->scratchBusy) CUDA_TRY(cudaEventSynchronize(c->scratchFree)); // a DEVICE-buffer batch on another stream still owns the scratch
     const uint8_t* src = static_cast<const uint8_t*>(llr);
     for (size_t k = 0; k < nChunks; ++k) {
         const size_t f0 = chunks[k].first, n = chunks[k].second;
@@ -947,8 +961,9 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
         uint8_t* dO = c->dOut + (size_t)h * largest * c->kb;
         uint8_t* dK = c->dOk + (size_t)h * largest;
         CUDA_TRY(cudaMemcpyAsync(dL, src + f0 * rowBytes, n * rowBytes, cudaMemcpyHostToDevice, s));
-        if (depth == 2 && k > 0) CUDA_TRY(cudaStreamWaitEvent(s, c->pipeDone[h ^ 1], 0)); // kernel k-1 has finished
-        rc = decode_on_device(c, dL, llrType, n, dO, dK, s);
+        if (depth == 2 && k > 0 && !overlap) CUDA_TRY(cudaStreamWaitEvent(s, c->pipeDone[h ^ 1], 0)); // kernel k-1 has finished
+        rc = overlap ? decode_on_device(c, dL, llrType, n, dO, dK, s, nullptr, h ? c->dSpill2 : c->dSpill, true)
+                     : decode_on_device(c, dL, llrType, n, dO, dK, s);
         if (rc) return rc;
         if (depth == 2) CUDA_TRY(cudaEventRecord(c->pipeDone[h], s));
         CUDA_TRY(cudaMemcpyAsync(info_out + f0 * c->kb, dO, n * (size_t)c->kb, cudaMemcpyDeviceToHost, s));
