@@ -338,7 +338,7 @@ POLAR_DEV uint32_t scf_first_min(const float* src, int n, uint32_t& parity)
 // WIDE: blocks of up to 16 warps at 128 registers (the lockstep barrier then spans every resident warp of the
 // SM); otherwise blocks of up to 8 warps with the full register budget.
 template <bool WIDE>
-__global__ void __launch_bounds__(WIDE ? 512 : 256, 1) fastssc_f32_kernel(const __grid_constant__ DecodeParams p,
+__global__ void __launch_bounds__(WIDE ? POLAR_SC_WIDE_THREADS : 256, 1) fastssc_f32_kernel(const __grid_constant__ DecodeParams p,
                                                             const __grid_constant__ Schedule sched)
 {
     extern __shared__ __align__(16) uint32_t smem[];

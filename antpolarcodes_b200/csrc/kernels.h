@@ -9,6 +9,11 @@
 #define POLAR_SCL_MID_THREADS 768
 #endif
 
+// launch bound of the wide Fast-SSC kernels (512 threads = 16 warps at 128 registers; A/B builds override it)
+#ifndef POLAR_SC_WIDE_THREADS
+#define POLAR_SC_WIDE_THREADS 512
+#endif
+
 namespace polar {
 
 typedef void (*DecodeKernel)(const DecodeParams, const Schedule);

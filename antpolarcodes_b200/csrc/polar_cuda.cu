@@ -406,7 +406,7 @@ int setup_decoder_geometry(polar_code* c)
     for (int i = 0; i < 12; ++i) {
         const int w = sclF32 ? sclF32Order[i] : scl ? sclOrder[i] : scOrder[i];
         if (forceW && w != forceW) continue;
-        if (!scl && w > (wide ? 16 : 8)) continue; // launch bounds of the Fast-SSC kernels
+        if (!scl && w > (wide ? POLAR_SC_WIDE_THREADS / 32 : 8)) continue; // launch bounds of the Fast-SSC kernels
         const size_t smem = perWarp * w;
         if (smem > (size_t)prop.sharedMemPerBlockOptin) continue;
         int nb = 0;
