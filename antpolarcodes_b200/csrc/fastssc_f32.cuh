@@ -135,6 +135,43 @@ POLAR_DEV void scf_top_chunk_v(ScfCtx& c, const ScfTilesV& t, float* dst, int s,
     }
 }
 
+// ---- F / G / G-0R steps whose parent (stage S + 1 <= 5) and child blocks both sit in the lane's shared-memory rows, compiled
+// per stage: compile-time trip counts and row offsets, one load of the left bits (most steps of a tree are this small)
+template <int S, int CODE>
+POLAR_DEV void scf_fg_small(ScfCtx& c, int pos)
+{
+    constexpr int n = 1 << S, CH = n < 8 ? n : 8;
+    const float* src = reinterpret_cast<const float*>(c.smLane + (f32_woff(S + 1) << 5));
+    float* dst = reinterpret_cast<float*>(c.smLane + (f32_woff(S) << 5));
+    uint32_t lw = 0u;
+    if (CODE == OP_G) lw = SCF_ROW(c, c.bitRow + (pos >> 5)) >> (pos & 31); // the block's bits sit inside one word (n <= 16)
+#pragma unroll
+    for (int i0 = 0; i0 < n; i0 += CH) {
+        float a[CH], b[CH];
+#pragma unroll
+        for (int t = 0; t < CH; ++t) { a[t] = src[(i0 + t) << 5]; b[t] = src[(i0 + t + n) << 5]; }
+#pragma unroll
+        for (int t = 0; t < CH; ++t) {
+            float r;
+            if (CODE == OP_F) r = f_f32(a[t], b[t]);
+            else if (CODE == OP_G_0R) r = __fadd_rn(a[t], b[t]);
+            else r = g_f32(a[t], b[t], (lw >> (i0 + t)) << 31);
+            dst[(i0 + t) << 5] = r;
+        }
+    }
+}
+template <int CODE>
+POLAR_DEV void scf_fg_small_s(ScfCtx& c, int s, int pos)
+{
+    switch (s) {
+    case 0: scf_fg_small<0, CODE>(c, pos); break;
+    case 1: scf_fg_small<1, CODE>(c, pos); break;
+    case 2: scf_fg_small<2, CODE>(c, pos); break;
+    case 3: scf_fg_small<3, CODE>(c, pos); break;
+    default: scf_fg_small<4, CODE>(c, pos); break;
+    }
+}
+
 // bit `i` of the block starting at absolute position pos, moved to the sign position
 POLAR_DEV uint32_t scf_bit_neg(const ScfCtx& c, int pos, int i)
 {
@@ -396,6 +433,12 @@ __global__ void __launch_bounds__(WIDE ? POLAR_SC_WIDE_THREADS : 256, 1) fastssc
             case OP_G:      // avx_float.h:146-162
             case OP_G_0R:   // avx_float.h:164-173
             case OP_G_R1: { // fastssc_avx_float.cpp:204-219
+                if (!top && s <= 4 && s + 1 < c.smemStages && code != OP_G_R1) { // small step inside shared memory
+                    if (code == OP_F) scf_fg_small_s<OP_F>(c, s, pos);
+                    else if (code == OP_G) scf_fg_small_s<OP_G>(c, s, pos);
+                    else scf_fg_small_s<OP_G_0R>(c, s, pos);
+                    break;
+                }
                 float* dst = scf_stage(c, s);
                 if (!top) {
                     const ScfRows src{ scf_stage(c, s + 1), n };
