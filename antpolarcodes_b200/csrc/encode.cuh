@@ -377,8 +377,11 @@ inline int launch_encode_reg_cap(const EncodeParams& p, const EncodeProgramT<CAP
     constexpr int rowWords = ENC_REG_THREADS * FPT;
     const int kbw = p.kb >> 2;
     const size_t smem = (size_t)rowWords * (kbw + 2) * 4 + (p.crcBits ? (size_t)kbw * 512 : 0);
+    // the limit belongs to the kernel function, not to the handle: always the same value (the largest footprint of this
+    // instantiation: kb = 128 with a CRC), so handles and host threads cannot lower it for each other
+    constexpr int maxSmem = rowWords * (32 + 2) * 4 + 32 * 512;
     if (smem > 48 * 1024 &&
-        cudaFuncSetAttribute((const void*)encode_reg_kernel<W, FPT, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        cudaFuncSetAttribute((const void*)encode_reg_kernel<W, FPT, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxSmem) != cudaSuccess)
         return -1;
     const long long nBlocks = (p.nFrames + rowWords - 1) / rowWords;
     const int grid = (int)std::min<long long>(nBlocks, (long long)numSMs * 16);
