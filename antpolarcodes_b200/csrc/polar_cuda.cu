@@ -913,7 +913,12 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     const int framesPerWarp = (c->kind == POLAR_KIND_SCL_I8 || c->kind == POLAR_KIND_SCL_F32) ? 32 / c->L : 32;
     const size_t wave = (size_t)framesPerWarp * c->warpsPerBlock * c->blocksPerSM * c->numSMs;
     const size_t rowBytes = (size_t)c->N * eb;
-    const size_t maxChunk = std::max<size_t>(1, (((size_t)env_int("POLAR_CUDA_CHUNK_MB", 128) << 20) / rowBytes) / wave) * wave;
+    // with a scratch per stream (below) the kernels of consecutive chunks overlap, a launch costs nothing and the last chunk is what
+    // stays exposed: chunks of about two waves (32 MB) are best then (headline e2e 14.25 -> 14.4, fp32 lists 5.19 -> 5.41 Gbit/s;
+    // one-wave chunks 13.8); chained kernels keep the large launches
+    const bool nativeType = llrType == ((c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32) ? POLAR_LLR_F32 : POLAR_LLR_I8);
+    const bool mayOverlap = nativeType && c->l2Persist <= 0.f && env_int("POLAR_CUDA_OVERLAP", 1) != 0;
+    const size_t maxChunk = std::max<size_t>(1, (((size_t)env_int("POLAR_CUDA_CHUNK_MB", mayOverlap ? 32 : 128) << 20) / rowBytes) / wave) * wave;
     const size_t firstChunk = std::max<size_t>(1, (((size_t)env_int("POLAR_CUDA_FIRST_CHUNK_MB", 8) << 20) / rowBytes) / wave) * wave;
     std::vector<std::pair<size_t, size_t>> chunks; // (first frame, frames)
     if (std::min(firstChunk, maxChunk) * 2 > nFrames || !env_int("POLAR_CUDA_PIPELINE", 1)) {
@@ -944,8 +949,7 @@ int polar_cuda_decode_batch(polar_code_t c, const void* llr, int llrType, int me
     // Two scratches (one per pipeline stream) let the kernel of chunk k+1 start on the SMs that the tail of chunk k has left;
     // with one shared scratch the kernels are chained by events.  Not with the quantiser pre-pass (its scratch is shared too) and
     // not while the scratch is pinned in L2 (two windows would fight for the set-aside).
-    const bool nativeType = llrType == ((c->kind == POLAR_KIND_FASTSSC_F32 || c->kind == POLAR_KIND_SCL_F32) ? POLAR_LLR_F32 : POLAR_LLR_I8);
-    bool overlap = depth == 2 && nativeType && c->l2Persist <= 0.f && env_int("POLAR_CUDA_OVERLAP", 1) != 0;
+    bool overlap = depth == 2 && mayOverlap;
     if (overlap && c->dSpill && !c->dSpill2 && cudaMalloc(&c->dSpill2, c->spillBytes) != cudaSuccess) {
         cudaGetLastError();
         c->dSpill2 = nullptr;
