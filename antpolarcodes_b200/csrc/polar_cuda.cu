@@ -219,7 +219,7 @@ int setup_decoder_geometry(polar_code* c)
     // lines, rarely enough that they do not wait for each other at every short step (measured per kernel on B200:
     // SCL int8 1 -> 64: 10.05 -> 10.42 Gbit/s, Fast-SSC int8 1 -> 128: 130 -> 145.5, Fast-SSC fp32 1 -> 64: 77 -> 88.2,
     // SCL fp32 1 -> 8: 4.11 -> 4.19; without any barrier the kernels stall on instruction fetch)
-    g.lockstep = env_int("POLAR_CUDA_LOCKSTEP", c->kind == POLAR_KIND_FASTSSC_I8 ? 128 : c->kind == POLAR_KIND_SCL_F32 ? 8 : 64);
+    g.lockstep = env_int("POLAR_CUDA_LOCKSTEP", c->kind == POLAR_KIND_FASTSSC_I8 ? 256 : c->kind == POLAR_KIND_SCL_F32 ? 8 : 64); // (Fast-SSC int8 after the 16-byte tiles: 32 -> 188.7, 64 -> 192.2, 128 -> 193.8, 256 -> 196.3 Gbit/s)
     if (g.lockstep & (g.lockstep - 1)) g.lockstep = 1; // the kernels test pc & (lockstep - 1)
     g.prefetchNext = env_int("POLAR_CUDA_PREFETCH", 0);
     g.rootLeaf = 0;
